@@ -1,0 +1,151 @@
+/* ppls_b200.h -- C ABI of the B200-native engine for the PPLS_simult EM loop.
+ *
+ * Drop-in boundary for ONE path of selbouhaddani/PPLS: the loop body of
+ *   PPLS_simult(X, Y, a, EMsteps, atol, type, ...)   Package/PPLS/R/EM_W_multi.R:758-807
+ * i.e. lines :780-802 (Expect_M :637-717 fast branch, Maximiz_M :729-742, logl_W :297-323
+ * and the only native call on that path, loglC_fast, Package/PPLS/src/loglC.cpp:319-338,
+ * bound today through .Call('PPLS_loglC_fast', ...) Package/PPLS/R/RcppExports.R:32-34 /
+ * RcppExport SEXP PPLS_loglC_fast(...) Package/PPLS/src/RcppExports.cpp:79-99).
+ *
+ * Because E- and M-step are R code in the reference, the seam is the loop, not one symbol:
+ * an Rcpp shim (r/ppls_b200_shim.cpp) marshals R matrices into the
+ * calls below.  Plain C types only: no C++/R/torch types, no exceptions cross this line.
+ *
+ * Conventions
+ *  - All matrices passed by the caller are host memory, column-major FP64 (R / Eigen
+ *    layout), caller-owned, read-only unless documented as output.  Outputs are
+ *    caller-allocated.
+ *  - Every function returns PPLS_OK (0) or a negative PPLS_E_* code; the message of the
+ *    last failure on this thread is ppls_last_error().
+ *  - A context is used by one host thread at a time (R's C API is single-threaded).
+ *  - There is no CPU fallback: without a CUDA device every compute entry point fails
+ *    with PPLS_E_CUDA.
+ */
+#ifndef PPLS_B200_H
+#define PPLS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PPLS_OK              0
+#define PPLS_E_INVALID      -1   /* bad argument / shape (R side: stopifnot) */
+#define PPLS_E_CUDA         -2   /* CUDA runtime failure, or no device        */
+#define PPLS_E_NCCL         -3   /* NCCL failure / libnccl.so.2 not loadable  */
+#define PPLS_E_OOM          -4   /* device or host allocation failed          */
+#define PPLS_E_NONFINITE    -5   /* a parameter became NaN/Inf during EM      */
+#define PPLS_E_UNSUPPORTED  -6   /* shape outside what the kernels cover      */
+
+#define PPLS_MAX_R           8   /* nr_comp supported by the streaming kernel */
+#define PPLS_NCCL_ID_BYTES 128
+
+#define PPLS_ORTH_SVD 0          /* type = "SVD" (default, EM_W_multi.R:758,761) */
+#define PPLS_ORTH_QR  1          /* type = "QR"                                  */
+
+#define PPLS_F_TIMING      1u    /* record CUDA events around every streaming launch */
+#define PPLS_F_DIRECT_RES  2u    /* (reserved) direct residual sums, debug mode      */
+
+typedef struct ppls_ctx  ppls_ctx;   /* device, stream, NCCL communicator, workspaces */
+typedef struct ppls_data ppls_data;  /* device-resident row shard of [X Y]            */
+typedef struct ppls_fit  ppls_fit;   /* state of one EM run (parameters, trace)       */
+
+/* Arguments of PPLS_simult that reach the loop (EM_W_multi.R:758). */
+typedef struct {
+  int32_t  r;            /* a / nr_comp                                            */
+  int32_t  max_steps;    /* EMsteps                                                */
+  int32_t  orth_type;    /* PPLS_ORTH_SVD | PPLS_ORTH_QR                           */
+  int32_t  check_every;  /* passes enqueued between host convergence checks; 0 = default */
+  double   atol;         /* break when loglik[i]-loglik[i-1] < atol (signed, :792) */
+  uint32_t flags;        /* PPLS_F_*                                               */
+  uint32_t reserved;
+} ppls_opts;
+
+/* The state (W., C., B., sigE., sigF., sigH., sigT.) of EM_W_multi.R:765-771 / :783-789.
+ * B and sigT are diagonal in the model; only the diagonals cross the ABI. */
+typedef struct {
+  double* W;      /* p x r, column-major */
+  double* C;      /* q x r, column-major */
+  double* B;      /* r  (diag)           */
+  double* sigT;   /* r  (diag)           */
+  double  sigE, sigF, sigH;
+} ppls_params;
+
+/* Device-time accounting of one fit (PPLS_F_TIMING). */
+typedef struct {
+  double  stream_ms;      /* sum of streaming-kernel (K1) launch durations       */
+  int64_t stream_launches;
+  double  loop_ms;        /* first-to-last event of all iterate() calls          */
+  int64_t kernel_launches;/* every kernel of ours launched by this fit           */
+  int64_t passes;         /* data passes done                                    */
+  int64_t bytes_per_pass; /* algorithmic bytes of one pass on this rank: 8*N*(p+q) */
+} ppls_timing;
+
+const char* ppls_version(void);
+const char* ppls_last_error(void);
+
+/* ---- context ------------------------------------------------------------------------- */
+int ppls_ctx_create(ppls_ctx** out, int device);
+/* One rank of a row-sharded multi-GPU run (one process per GPU).  `nccl_id` is the
+ * PPLS_NCCL_ID_BYTES blob made by ppls_nccl_unique_id() on rank 0 and handed to the other
+ * ranks by the caller (torch.distributed, MPI, a file ...). */
+int ppls_nccl_unique_id(void* id_out, size_t nbytes);
+int ppls_ctx_create_dist(ppls_ctx** out, int device, int rank, int world,
+                         const void* nccl_id, size_t nbytes);
+int ppls_ctx_destroy(ppls_ctx* ctx);
+int ppls_ctx_info(const ppls_ctx* ctx, int* device, int* rank, int* world, int* sm_count);
+/* Synchronise the context's stream (for callers that time with their own clock). */
+int ppls_ctx_sync(ppls_ctx* ctx);
+
+/* ---- data ---------------------------------------------------------------------------- */
+/* Copy this rank's rows of X (n x p, leading dimension ldX) and Y (n x q, ldY) to the
+ * device and re-tile them into the engine's row-major layout.  Replaces the by-value
+ * Eigen::MatrixXd copies of RcppExports.cpp:87-88,96 -- done once, not once per iteration. */
+int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
+                        int64_t n, int64_t p, int64_t q, ppls_data** out);
+/* Generate rows row0 .. row0+n-1 of the synthetic PPLS sample on the device (model of
+ * simulC, loglC.cpp:288-311, orthogonal parts zero; counter-based, so identical bits for
+ * any sharding).  `truth` holds the generating parameters with r components. */
+int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
+                        uint64_t seed, const ppls_params* truth, ppls_data** out);
+/* Copy rows row0 .. row0+n-1 (local numbering) back to column-major host arrays. */
+int ppls_data_export(ppls_ctx* ctx, const ppls_data* d, int64_t row0, int64_t n,
+                     double* X, int64_t ldX, double* Y, int64_t ldY);
+/* Local shape and the (global, all ranks) sums of squares ||X||_F^2, ||Y||_F^2. */
+int ppls_data_info(const ppls_data* d, int64_t* n, int64_t* p, int64_t* q, int64_t* n_total,
+                   double* ssqX, double* ssqY);
+int ppls_data_destroy(ppls_data* d);
+
+/* ---- one EM run, stepwise -------------------------------------------------------------- */
+/* Enter the loop at EM_W_multi.R:780 with an explicit start state (the reference's random
+ * start, :762-778, stays on the caller's side). */
+int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts,
+                    const ppls_params* init, ppls_fit** out);
+/* Enqueue up to `n_passes` data passes.  Pass k (k = 0, 1, ...) streams X and Y once with
+ * the parameters theta_k and yields loglik(theta_k) (= loglik[k], k >= 1; logl_W at :791)
+ * and the E-step at theta_k (:782); unless the break rule (:792) or k == max_steps ends
+ * the run, the M-step then makes theta_{k+1}.  Returns the number of passes done so far
+ * and whether the run has ended. */
+int ppls_fit_iterate(ppls_fit* fit, int32_t n_passes, int32_t* passes_done, int32_t* finished);
+/* Final state in LOOP order (the sign/order normalisation of :794-799 is the caller's,
+ * on these tiny outputs), loglik[0 .. steps_done-1], the second moments of the final
+ * E-step (:802) as Ctt[r], Cuu[r], Cut[r], Cee, Cff, Chh[r*r column-major]
+ * (3r + 2 + r*r doubles), and mu_T / mu_U (local n x r, column-major; NULL to skip). */
+int ppls_fit_result(ppls_fit* fit, ppls_params* est, double* loglik, int32_t* steps_done,
+                    double* moments, double* mu_T, double* mu_U);
+int ppls_fit_timing(const ppls_fit* fit, ppls_timing* out);
+int ppls_fit_destroy(ppls_fit* fit);
+
+/* ---- one EM run, one call (what the Rcpp shim binds) ----------------------------------- */
+/* Equivalent to fit_create + fit_iterate until finished + fit_result + fit_destroy:
+ * EM_W_multi.R:780-802 from the start state `init`. */
+int ppls_simult_run(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts,
+                    const ppls_params* init, ppls_params* est, double* loglik,
+                    int32_t* steps_done, double* moments, double* mu_T, double* mu_U);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PPLS_B200_H */
