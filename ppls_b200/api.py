@@ -1,0 +1,284 @@
+"""Host-side mirror of the reference's R interface for the PPLS_simult path, over the C ABI.
+
+R is not installed on the build or GPU boxes, so this module plays the role of the R
+wrapper + Rcpp shim (r/PPLS_simult_b200.R, r/ppls_b200_shim.cpp): same
+function name, argument meaning, defaults, returned list structure and warnings as
+Package/PPLS/R/EM_W_multi.R:758-807.  All arithmetic on X and Y happens in libppls_b200.so
+on the GPU; only r-sized bookkeeping (the sign/order normalisation, :773-778 and :794-799)
+is done here, exactly as the C ABI header assigns it to the caller.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import warnings
+from typing import Optional
+
+import numpy as np
+
+from . import _lib as L
+
+__all__ = ["Context", "Data", "Fit", "PPLS_simult", "normalise", "default_init", "default_context"]
+
+
+def _f64(a, order="F"):
+    return np.require(np.asarray(a, dtype=np.float64), dtype=np.float64, requirements=[order, "A"])
+
+
+def _diagvec(M, r):
+    M = np.asarray(M, dtype=np.float64)
+    v = np.diag(M).copy() if M.ndim == 2 else np.atleast_1d(M).astype(np.float64).copy()
+    if v.shape != (r,):
+        raise ValueError(f"expected {r} diagonal entries, got shape {v.shape}")
+    return v
+
+
+class _ParamsBuf:
+    """Owns numpy storage for a ppls_params struct."""
+
+    def __init__(self, p, q, r, W=None, C_=None, B=None, sigT=None, sigE=0.0, sigF=0.0, sigH=0.0):
+        self.W = _f64(W if W is not None else np.zeros((p, r))).reshape(p, r, order="F")
+        self.C = _f64(C_ if C_ is not None else np.zeros((q, r))).reshape(q, r, order="F")
+        if self.W.shape != (p, r) or self.C.shape != (q, r):
+            raise ValueError("W must be p x r and C must be q x r")
+        self.W = np.asfortranarray(self.W.copy()); self.C = np.asfortranarray(self.C.copy())
+        self.B = _diagvec(B if B is not None else np.zeros(r), r)
+        self.sigT = _diagvec(sigT if sigT is not None else np.zeros(r), r)
+        self.struct = L.Params(self.W.ctypes.data_as(L.c_double_p), self.C.ctypes.data_as(L.c_double_p),
+                               self.B.ctypes.data_as(L.c_double_p), self.sigT.ctypes.data_as(L.c_double_p),
+                               float(sigE), float(sigF), float(sigH))
+
+
+class Context:
+    """ppls_ctx: one GPU (and, for row-sharded runs, one rank of the NCCL communicator)."""
+
+    def __init__(self, device: int = 0, rank: int = 0, world: int = 1, nccl_id: Optional[bytes] = None):
+        self._h = C.c_void_p()
+        lib = L.lib()
+        if world > 1:
+            if nccl_id is None or len(nccl_id) < L.PPLS_NCCL_ID_BYTES:
+                raise ValueError("a 128-byte NCCL id from Context.nccl_unique_id() is required for world > 1")
+            buf = C.create_string_buffer(bytes(nccl_id), L.PPLS_NCCL_ID_BYTES)
+            L.check(lib.ppls_ctx_create_dist(C.byref(self._h), device, rank, world, buf, L.PPLS_NCCL_ID_BYTES))
+        else:
+            L.check(lib.ppls_ctx_create(C.byref(self._h), device))
+        self.device, self.rank, self.world = device, rank, world
+        sm = C.c_int()
+        L.check(lib.ppls_ctx_info(self._h, None, None, None, C.byref(sm)))
+        self.sm_count = sm.value
+
+    @staticmethod
+    def nccl_unique_id() -> bytes:
+        buf = C.create_string_buffer(L.PPLS_NCCL_ID_BYTES)
+        L.check(L.lib().ppls_nccl_unique_id(buf, L.PPLS_NCCL_ID_BYTES))
+        return buf.raw
+
+    def sync(self):
+        L.check(L.lib().ppls_ctx_sync(self._h))
+
+    def close(self):
+        if self._h:
+            L.lib().ppls_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default_ctx: Optional[Context] = None
+
+
+def default_context() -> Context:
+    global _default_ctx
+    if _default_ctx is None:
+        _default_ctx = Context(0)
+    return _default_ctx
+
+
+class Data:
+    """ppls_data: a device-resident row shard of [X Y]."""
+
+    def __init__(self, ctx: Context, handle):
+        self.ctx, self._h = ctx, handle
+        n, p, q, nt = C.c_int64(), C.c_int64(), C.c_int64(), C.c_int64()
+        sx, sy = C.c_double(), C.c_double()
+        L.check(L.lib().ppls_data_info(self._h, C.byref(n), C.byref(p), C.byref(q), C.byref(nt), C.byref(sx), C.byref(sy)))
+        self.n, self.p, self.q, self.n_total = n.value, p.value, q.value, nt.value
+        self.ssqX, self.ssqY = sx.value, sy.value
+
+    @classmethod
+    def from_host(cls, ctx: Context, X, Y) -> "Data":
+        X = np.asarray(X); Y = np.asarray(Y)
+        if X.ndim != 2 or Y.ndim != 2 or X.shape[0] != Y.shape[0]:
+            raise ValueError("X and Y must be matrices with the same number of rows")
+        Xf, Yf = _f64(X), _f64(Y)
+        n, p = Xf.shape; q = Yf.shape[1]
+        h = C.c_void_p()
+        L.check(L.lib().ppls_data_from_host(ctx._h, Xf.ctypes.data, max(n, 1), Yf.ctypes.data, max(n, 1), n, p, q, C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def synthetic(cls, ctx: Context, n: int, p: int, q: int, truth: dict, seed: int, row0: int = 0) -> "Data":
+        r = np.asarray(truth["W"]).shape[1]
+        pb = _ParamsBuf(p, q, r, truth["W"], truth["C"], truth["B"], truth["sigT"], truth["sigE"], truth["sigF"], truth["sigH"])
+        h = C.c_void_p()
+        L.check(L.lib().ppls_data_synthetic(ctx._h, n, row0, p, q, r, seed, C.byref(pb.struct), C.byref(h)))
+        return cls(ctx, h)
+
+    def export(self, row0: int = 0, n: Optional[int] = None):
+        n = self.n - row0 if n is None else n
+        X = np.empty((n, self.p), order="F"); Y = np.empty((n, self.q), order="F")
+        L.check(L.lib().ppls_data_export(self.ctx._h, self._h, row0, n, X.ctypes.data, max(n, 1), Y.ctypes.data, max(n, 1)))
+        return X, Y
+
+    def close(self):
+        if self._h:
+            L.lib().ppls_data_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Fit:
+    """ppls_fit: one EM run entered at EM_W_multi.R:780 with an explicit start state."""
+
+    def __init__(self, data: Data, init: dict, a: int, EMsteps: int = 10, atol: float = 1e-4, type: str = "SVD",
+                 timing: bool = False, check_every: int = 0):
+        if type not in ("SVD", "QR"):
+            raise ValueError("'arg' should be one of 'SVD', 'QR'")       # match.arg(type), :761
+        self.data, self.r, self.EMsteps = data, int(a), int(EMsteps)
+        self.opts = L.Opts(int(a), int(EMsteps), L.PPLS_ORTH_SVD if type == "SVD" else L.PPLS_ORTH_QR,
+                           int(check_every), float(atol), L.PPLS_F_TIMING if timing else 0, 0)
+        pb = _ParamsBuf(data.p, data.q, self.r, init["W"], init["C"], init["B"], init["sigT"],
+                        init["sigE"], init["sigF"], init["sigH"])
+        self._h = C.c_void_p()
+        L.check(L.lib().ppls_fit_create(data.ctx._h, data._h, C.byref(self.opts), C.byref(pb.struct), C.byref(self._h)))
+
+    def iterate(self, n_passes: int):
+        done, fin = C.c_int32(), C.c_int32()
+        L.check(L.lib().ppls_fit_iterate(self._h, int(n_passes), C.byref(done), C.byref(fin)))
+        return done.value, bool(fin.value)
+
+    def run(self):
+        fin = False
+        while not fin:
+            _, fin = self.iterate(self.EMsteps + 1)
+
+    def result(self, want_mu: bool = True) -> dict:
+        d, r = self.data, self.r
+        est = _ParamsBuf(d.p, d.q, r)
+        loglik = np.zeros(max(self.EMsteps, 1))
+        steps = C.c_int32()
+        mom = np.zeros(3 * r + 2 + r * r)
+        muT = np.empty((d.n, r), order="F") if want_mu else None
+        muU = np.empty((d.n, r), order="F") if want_mu else None
+        L.check(L.lib().ppls_fit_result(self._h, C.byref(est.struct), loglik.ctypes.data, C.byref(steps), mom.ctypes.data,
+                                        muT.ctypes.data if want_mu else None, muU.ctypes.data if want_mu else None))
+        return dict(W=est.W, C=est.C, B=est.B, sigT=est.sigT, sigE=est.struct.sigE, sigF=est.struct.sigF,
+                    sigH=est.struct.sigH, loglik=loglik[:steps.value].copy(), steps=steps.value,
+                    Ctt=mom[:r].copy(), Cuu=mom[r:2 * r].copy(), Cut=mom[2 * r:3 * r].copy(), Cee=mom[3 * r], Cff=mom[3 * r + 1],
+                    Chh=mom[3 * r + 2:].reshape(r, r, order="F").copy(), mu_T=muT, mu_U=muU)
+
+    def timing(self) -> dict:
+        t = L.Timing()
+        L.check(L.lib().ppls_fit_timing(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in L.Timing._fields_}
+
+    def close(self):
+        if self._h:
+            L.lib().ppls_fit_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def normalise(W, C_, B, sigT):
+    """Sign/order normalisation of EM_W_multi.R:773-778 (start values) and :794-799 (result),
+    quirk included: for W and C the sign vector is applied after the column permutation
+    without being permuted; for B it is applied before."""
+    W = np.asarray(W, dtype=np.float64); C_ = np.asarray(C_, dtype=np.float64)
+    r = W.shape[1]
+    b = _diagvec(B, r); t = _diagvec(sigT, r)
+    signLoad = np.sign(t * b)
+    rotLoad = np.argsort(-(t * b * signLoad), kind="stable")      # order(decreasing=TRUE) is stable
+    return (W[:, rotLoad] * signLoad[None, :], C_[:, rotLoad] * signLoad[None, :],
+            np.diag((b * signLoad)[rotLoad]), np.diag(t[rotLoad]))
+
+
+def default_init(p: int, q: int, a: int) -> dict:
+    """Deterministic start state used when the caller gives none.
+
+    DEVIATION (documented in DESIGN.md): the reference draws its start from 20 EM steps of
+    the sequential PPLS(..., 'random') fit (EM_W_multi.R:762-771), which is R-RNG dependent
+    and not on this path.  Here: the first `a` cosine basis vectors (orthonormal), B = I,
+    sigT = I with a mild decay, sigE = 1/sqrt(p), sigF = 1/sqrt(q), sigH = 0.1."""
+    def basis(n):
+        j = (np.arange(n) + 0.5)[:, None]
+        k = np.arange(1, a + 1)[None, :]
+        M = np.cos(np.pi * j * k / n)
+        Q, _ = np.linalg.qr(M)
+        return Q
+    return dict(W=basis(p), C=basis(q), B=np.ones(a), sigT=np.exp(-0.1 * np.arange(a)),
+                sigE=1.0 / np.sqrt(p), sigF=1.0 / np.sqrt(q), sigH=0.1)
+
+
+def PPLS_simult(X, Y, a, EMsteps=10, atol=1e-4, type="SVD", init: Optional[dict] = None,
+                ctx: Optional[Context] = None, data: Optional[Data] = None, want_mu: bool = True, **kwargs):
+    """Simultaneous PPLS fit -- drop-in for PPLS_simult (Package/PPLS/R/EM_W_multi.R:758-807).
+
+    Returns {'Expectations': {mu_T, mu_U, Ctt, Cuu, Cut, Cee, Cff, Chh}, 'loglik', 'estimates':
+    {W, C, B, sigE, sigF, sigH, sigT}} with the reference's shapes (B, sigT, Ctt, Cuu, Cut
+    r x r diagonal matrices; Cee, Cff 1 x 1).  `init` replaces the random start (:762-771).
+    `debug=` (the dense Expect_M, :643-667) is accepted and ignored with a warning: the dense
+    form is O((p+q)^3) and exists in this repo only inside the CPU oracle."""
+    if isinstance(type, (tuple, list)):
+        type = type[0]                                   # c("SVD","QR") default -> "SVD"
+    if kwargs.pop("debug", False):
+        warnings.warn("debug=TRUE (dense Expect_M) is not part of the GPU path; using the fast E-step")
+    if kwargs:
+        raise TypeError(f"unused arguments: {sorted(kwargs)}")
+    a = int(a)
+    if a <= 0:
+        raise ValueError("#components must be >0")
+    if int(EMsteps) < 1:
+        raise ValueError("EMsteps must be a strictly positive integer")
+    ctx = ctx or (data.ctx if data is not None else default_context())
+    own_data = data is None
+    if data is None:
+        data = Data.from_host(ctx, X, Y)
+    try:
+        if init is None:
+            init = default_init(data.p, data.q, a)
+        W0, C0, B0, T0 = normalise(init["W"], init["C"], init["B"], init["sigT"])          # :773-778
+        start = dict(W=W0, C=C0, B=B0, sigT=T0, sigE=init["sigE"], sigF=init["sigF"], sigH=init["sigH"])
+        fit = Fit(data, start, a, EMsteps, atol, type)
+        try:
+            fit.run()                                                                      # :780-793
+            res = fit.result(want_mu=want_mu)                                              # :802
+        finally:
+            fit.close()
+    finally:
+        if own_data:
+            data.close()
+    Wn, Cn, Bn, Tn = normalise(res["W"], res["C"], res["B"], res["sigT"])                  # :794-799
+    loglik = res["loglik"]
+    if np.any(np.diff(loglik) < 0):
+        warnings.warn("Negative increments of likelihood")                                 # :801
+    I = np.eye(a)
+    Eout = dict(mu_T=res["mu_T"], mu_U=res["mu_U"], Ctt=np.diag(res["Ctt"]), Cuu=np.diag(res["Cuu"]),
+                Cut=np.diag(res["Cut"]), Cee=np.array([[res["Cee"]]]), Cff=np.array([[res["Cff"]]]), Chh=res["Chh"])
+    outp = dict(W=Wn, C=Cn, B=Bn, sigE=res["sigE"], sigF=res["sigF"], sigH=res["sigH"], sigT=Tn)
+    return dict(Expectations=Eout, loglik=loglik, estimates=outp,
+                loop_state=dict(W=res["W"], C=res["C"], B=np.diag(res["B"]), sigT=np.diag(res["sigT"]),
+                                sigE=res["sigE"], sigF=res["sigF"], sigH=res["sigH"]),
+                **{"class": "PPLS_simult"})

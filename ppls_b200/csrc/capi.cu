@@ -1,0 +1,602 @@
+// libppls_b200.so -- C ABI (include/ppls_b200.h) and host orchestration of the EM loop.
+// Host side of PPLS_simult's loop, Package/PPLS/R/EM_W_multi.R:780-802, in C++: dataset
+// residency, the pass loop with a device-side break flag, the NCCL exchange between the
+// streaming kernel and the update kernel.  No CPU fallback: every compute entry point needs
+// a CUDA device and fails with PPLS_E_CUDA otherwise.
+#include "common.cuh"
+#include <dlfcn.h>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <new>
+
+using namespace ppls;
+
+// ---- errors ---------------------------------------------------------------------------------
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e__ = (call);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(e__ == cudaErrorMemoryAllocation ? PPLS_E_OOM : PPLS_E_CUDA,            \
+                  std::string(#call) + ": " + cudaGetErrorString(e__));                   \
+  } while (0)
+
+// ---- NCCL, loaded lazily (single-GPU use needs no libnccl) -----------------------------------
+namespace {
+typedef struct { char internal[128]; } nccl_uid;
+typedef void* nccl_comm;
+struct NcclApi {
+  void* handle = nullptr;
+  int (*GetUniqueId)(nccl_uid*) = nullptr;
+  int (*CommInitRank)(nccl_comm*, int, nccl_uid, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, nccl_comm, cudaStream_t) = nullptr;
+  int (*CommDestroy)(nccl_comm) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+const int kNcclFloat64 = 8, kNcclSum = 0;
+
+int load_nccl() {
+  if (g_nccl.handle) return PPLS_OK;
+  const char* names[] = {getenv("PPLS_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+  void* h = nullptr;
+  for (const char* nm : names) {
+    if (!nm || !*nm) continue;
+    h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+    if (h) break;
+  }
+  if (!h) return fail(PPLS_E_NCCL, std::string("cannot load libnccl.so.2: ") + dlerror());
+  g_nccl.GetUniqueId = (int (*)(nccl_uid*))dlsym(h, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(nccl_comm*, int, nccl_uid, int))dlsym(h, "ncclCommInitRank");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, nccl_comm, cudaStream_t))dlsym(h, "ncclAllReduce");
+  g_nccl.CommDestroy = (int (*)(nccl_comm))dlsym(h, "ncclCommDestroy");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy)
+    return fail(PPLS_E_NCCL, "libnccl.so.2 lacks a required symbol");
+  g_nccl.handle = h;
+  return PPLS_OK;
+}
+int nccl_fail(int rc, const char* what) {
+  return fail(PPLS_E_NCCL, std::string(what) + ": " + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error"));
+}
+}  // namespace
+
+// ---- objects ----------------------------------------------------------------------------------
+struct ppls_ctx {
+  int device = 0, rank = 0, world = 1, sm_count = 0;
+  cudaStream_t stream = nullptr;
+  nccl_comm comm = nullptr;
+  double* d_small = nullptr;   // 8 doubles of device scratch for tiny collectives
+};
+
+struct ppls_data {
+  ppls_ctx* ctx = nullptr;
+  DataShape s{};
+  double* D = nullptr;
+  double ssq[2] = {0, 0};      // global
+  int64_t n_total = 0;         // global
+};
+
+static int ctx_activate(const ppls_ctx* ctx) {
+  if (!ctx) return fail(PPLS_E_INVALID, "null context");
+  CU(cudaSetDevice(ctx->device));
+  return PPLS_OK;
+}
+
+extern "C" const char* ppls_version(void) { return "ppls_b200 0.1 (sm_100a)"; }
+extern "C" const char* ppls_last_error(void) { return g_err.c_str(); }
+
+static int ctx_create_common(ppls_ctx** out, int device) {
+  if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(PPLS_E_CUDA, std::string("no CUDA device (there is no CPU fallback): ") + cudaGetErrorString(e));
+  if (device < 0 || device >= ndev) return fail(PPLS_E_INVALID, "device index out of range");
+  CU(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CU(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10)
+    return fail(PPLS_E_UNSUPPORTED, "this library is built for sm_100a (B200) only");
+  ppls_ctx* c = new (std::nothrow) ppls_ctx();
+  if (!c) return fail(PPLS_E_OOM, "host allocation failed");
+  c->device = device;
+  c->sm_count = prop.multiProcessorCount;
+  cudaError_t e1 = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  cudaError_t e2 = (e1 == cudaSuccess) ? cudaMalloc(&c->d_small, 8 * sizeof(double)) : e1;
+  if (e2 != cudaSuccess) {
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return fail(PPLS_E_CUDA, std::string("context setup: ") + cudaGetErrorString(e2));
+  }
+  *out = c;
+  return PPLS_OK;
+}
+
+extern "C" int ppls_ctx_create(ppls_ctx** out, int device) { return ctx_create_common(out, device); }
+
+extern "C" int ppls_nccl_unique_id(void* id_out, size_t nbytes) {
+  if (!id_out || nbytes < PPLS_NCCL_ID_BYTES) return fail(PPLS_E_INVALID, "id buffer must hold 128 bytes");
+  int rc = load_nccl();
+  if (rc) return rc;
+  nccl_uid id;
+  int nr = g_nccl.GetUniqueId(&id);
+  if (nr) return nccl_fail(nr, "ncclGetUniqueId");
+  memcpy(id_out, &id, sizeof(id));
+  return PPLS_OK;
+}
+
+extern "C" int ppls_ctx_create_dist(ppls_ctx** out, int device, int rank, int world, const void* nccl_id,
+                                    size_t nbytes) {
+  if (world < 1 || rank < 0 || rank >= world) return fail(PPLS_E_INVALID, "bad rank/world");
+  int rc = ctx_create_common(out, device);
+  if (rc) return rc;
+  (*out)->rank = rank; (*out)->world = world;
+  if (world == 1) return PPLS_OK;
+  if (!nccl_id || nbytes < PPLS_NCCL_ID_BYTES) { ppls_ctx_destroy(*out); *out = nullptr; return fail(PPLS_E_INVALID, "missing NCCL id"); }
+  rc = load_nccl();
+  if (rc) { ppls_ctx_destroy(*out); *out = nullptr; return rc; }
+  nccl_uid id;
+  memcpy(&id, nccl_id, sizeof(id));
+  int nr = g_nccl.CommInitRank(&(*out)->comm, world, id, rank);
+  if (nr) { ppls_ctx_destroy(*out); *out = nullptr; return nccl_fail(nr, "ncclCommInitRank"); }
+  return PPLS_OK;
+}
+
+extern "C" int ppls_ctx_destroy(ppls_ctx* ctx) {
+  if (!ctx) return PPLS_OK;
+  cudaSetDevice(ctx->device);
+  if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+  if (ctx->d_small) cudaFree(ctx->d_small);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return PPLS_OK;
+}
+
+extern "C" int ppls_ctx_info(const ppls_ctx* ctx, int* device, int* rank, int* world, int* sm_count) {
+  if (!ctx) return fail(PPLS_E_INVALID, "null context");
+  if (device) *device = ctx->device;
+  if (rank) *rank = ctx->rank;
+  if (world) *world = ctx->world;
+  if (sm_count) *sm_count = ctx->sm_count;
+  return PPLS_OK;
+}
+
+extern "C" int ppls_ctx_sync(ppls_ctx* ctx) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(ctx->stream));
+  return PPLS_OK;
+}
+
+// sum `count` doubles (device, in place) over all ranks
+static int allreduce_sum(ppls_ctx* ctx, double* dbuf, size_t count) {
+  if (ctx->world == 1) return PPLS_OK;
+  int nr = g_nccl.AllReduce(dbuf, dbuf, count, kNcclFloat64, kNcclSum, ctx->comm, ctx->stream);
+  if (nr) return nccl_fail(nr, "ncclAllReduce");
+  return PPLS_OK;
+}
+
+// ---- data ---------------------------------------------------------------------------------------
+static int shape_init(DataShape* s, int64_t n, int64_t p, int64_t q) {
+  if (n < 1 || p < 1 || q < 1) return fail(PPLS_E_INVALID, "X and Y need at least one row and one column");
+  if (p > (1 << 24) || q > (1 << 24)) return fail(PPLS_E_UNSUPPORTED, "too many columns");
+  s->n = n; s->p = (int32_t)p; s->q = (int32_t)q;
+  s->p2 = (int32_t)((p + 1) & ~(int64_t)1); s->q2 = (int32_t)((q + 1) & ~(int64_t)1);
+  s->ld = s->p2 + s->q2;
+  return PPLS_OK;
+}
+
+// ||X||^2, ||Y||^2 and the row count, summed over ranks
+static int data_finalize(ppls_ctx* ctx, ppls_data* d) {
+  const int nblocks = ctx->sm_count * 4;
+  double* scratch = nullptr;
+  CU(cudaMalloc(&scratch, sizeof(double) * 2 * nblocks));
+  cudaError_t e = launch_ssq(d->D, d->s, ctx->d_small, scratch, nblocks, ctx->stream);
+  if (e != cudaSuccess) { cudaFree(scratch); return fail(PPLS_E_CUDA, std::string("ssq kernel: ") + cudaGetErrorString(e)); }
+  double nloc = (double)d->s.n;
+  e = cudaMemcpyAsync(ctx->d_small + 2, &nloc, sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+  int rc = (e == cudaSuccess) ? allreduce_sum(ctx, ctx->d_small, 3) : fail(PPLS_E_CUDA, cudaGetErrorString(e));
+  double h[3] = {0, 0, 0};
+  if (!rc) {
+    e = cudaMemcpyAsync(h, ctx->d_small, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) rc = fail(PPLS_E_CUDA, std::string("ssq readback: ") + cudaGetErrorString(e));
+  }
+  cudaFree(scratch);
+  if (rc) return rc;
+  d->ssq[0] = h[0]; d->ssq[1] = h[1]; d->n_total = (int64_t)llround(h[2]);
+  return PPLS_OK;
+}
+
+extern "C" int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
+                                   int64_t n, int64_t p, int64_t q, ppls_data** out) {
+  if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+  *out = nullptr;
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!X || !Y) return fail(PPLS_E_INVALID, "null X or Y");
+  if (ldX < n || ldY < n) return fail(PPLS_E_INVALID, "leading dimension smaller than the row count");
+  ppls_data* d = new (std::nothrow) ppls_data();
+  if (!d) return fail(PPLS_E_OOM, "host allocation failed");
+  d->ctx = ctx;
+  rc = shape_init(&d->s, n, p, q);
+  if (rc) { delete d; return rc; }
+  const size_t bytes = (size_t)n * d->s.ld * sizeof(double);
+  cudaError_t e = cudaMalloc(&d->D, bytes);
+  if (e != cudaSuccess) { delete d; return fail(PPLS_E_OOM, std::string("device allocation of the data shard: ") + cudaGetErrorString(e)); }
+  // staging: chunks of rows, column-major as they lie in the caller's arrays
+  const size_t stage_budget = (size_t)256 << 20;
+  int64_t cr = (int64_t)(stage_budget / (sizeof(double) * (size_t)(p + q)));
+  if (cr > n) cr = n;
+  if (cr < 32) cr = (n < 32) ? n : 32;
+  double* stg = nullptr;
+  e = cudaMalloc(&stg, sizeof(double) * (size_t)cr * (size_t)(p + q));
+  if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_OOM, "device allocation of the staging buffer"); }
+  double* stgX = stg;
+  double* stgY = stg + (size_t)cr * p;
+  for (int64_t i0 = 0; i0 < n && e == cudaSuccess; i0 += cr) {
+    const int64_t rows = (n - i0 < cr) ? (n - i0) : cr;
+    e = cudaMemcpy2DAsync(stgX, rows * sizeof(double), X + i0, ldX * sizeof(double), rows * sizeof(double), (size_t)p,
+                          cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(stgY, rows * sizeof(double), Y + i0, ldY * sizeof(double), rows * sizeof(double), (size_t)q,
+                            cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = launch_retile(stgX, rows, rows, (int)p, d->D, d->s.ld, 0, i0, ctx->stream);
+    if (e == cudaSuccess) e = launch_retile(stgY, rows, rows, (int)q, d->D, d->s.ld, d->s.p2, i0, ctx->stream);
+  }
+  if (e == cudaSuccess) e = launch_zero_pad(d->D, d->s, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(stg);
+  if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_CUDA, std::string("upload: ") + cudaGetErrorString(e)); }
+  rc = data_finalize(ctx, d);
+  if (rc) { cudaFree(d->D); delete d; return rc; }
+  *out = d;
+  return PPLS_OK;
+}
+
+// loadings in the engine layout: L[ld][R] row-major, W rows then C rows, pad rows zero
+static void pack_loadings(const DataShape& s, int R, const double* W, const double* C, std::vector<double>& L) {
+  L.assign((size_t)s.ld * R, 0.0);
+  for (int k = 0; k < R; ++k) {
+    for (int j = 0; j < s.p; ++j) L[(size_t)j * R + k] = W[j + (size_t)k * s.p];
+    for (int j = 0; j < s.q; ++j) L[(size_t)(s.p2 + j) * R + k] = C[j + (size_t)k * s.q];
+  }
+}
+
+static int check_params(const ppls_params* P, const char* what) {
+  if (!P || !P->W || !P->C || !P->B || !P->sigT) return fail(PPLS_E_INVALID, std::string(what) + ": null parameter pointer");
+  return PPLS_OK;
+}
+
+extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
+                                   uint64_t seed, const ppls_params* truth, ppls_data** out) {
+  if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+  *out = nullptr;
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  rc = check_params(truth, "truth");
+  if (rc) return rc;
+  if (r < 1 || r > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
+  if (row0 < 0) return fail(PPLS_E_INVALID, "negative row offset");
+  ppls_data* d = new (std::nothrow) ppls_data();
+  if (!d) return fail(PPLS_E_OOM, "host allocation failed");
+  d->ctx = ctx;
+  rc = shape_init(&d->s, n, p, q);
+  if (rc) { delete d; return rc; }
+  cudaError_t e = cudaMalloc(&d->D, (size_t)n * d->s.ld * sizeof(double));
+  if (e != cudaSuccess) { delete d; return fail(PPLS_E_OOM, std::string("device allocation of the data shard: ") + cudaGetErrorString(e)); }
+  std::vector<double> L;
+  pack_loadings(d->s, r, truth->W, truth->C, L);
+  double *dL = nullptr, *dbt = nullptr;
+  e = cudaMalloc(&dL, L.size() * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&dbt, 2 * MAXR * sizeof(double));
+  double bt[2 * MAXR] = {0};
+  for (int k = 0; k < r; ++k) { bt[k] = truth->B[k]; bt[MAXR + k] = truth->sigT[k]; }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(dL, L.data(), L.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(dbt, bt, sizeof(bt), cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess)
+    e = launch_synth(d->D, d->s, row0, r, seed, dL, dbt, dbt + MAXR, truth->sigE, truth->sigF, truth->sigH, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (dL) cudaFree(dL);
+  if (dbt) cudaFree(dbt);
+  if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_CUDA, std::string("synthetic generator: ") + cudaGetErrorString(e)); }
+  rc = data_finalize(ctx, d);
+  if (rc) { cudaFree(d->D); delete d; return rc; }
+  *out = d;
+  return PPLS_OK;
+}
+
+extern "C" int ppls_data_export(ppls_ctx* ctx, const ppls_data* d, int64_t row0, int64_t n, double* X, int64_t ldX,
+                                double* Y, int64_t ldY) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!d || !X || !Y) return fail(PPLS_E_INVALID, "null argument");
+  if (row0 < 0 || n < 0 || row0 + n > d->s.n || ldX < n || ldY < n) return fail(PPLS_E_INVALID, "row range / leading dimension");
+  if (n == 0) return PPLS_OK;
+  const int p = d->s.p, q = d->s.q;
+  int64_t cr = (int64_t)(((size_t)64 << 20) / (sizeof(double) * (size_t)(p + q)));
+  if (cr > n) cr = n;
+  if (cr < 32) cr = (n < 32) ? n : 32;
+  double* stg = nullptr;
+  CU(cudaMalloc(&stg, sizeof(double) * (size_t)cr * (size_t)(p + q)));
+  cudaError_t e = cudaSuccess;
+  for (int64_t i0 = 0; i0 < n && e == cudaSuccess; i0 += cr) {
+    const int64_t rows = (n - i0 < cr) ? (n - i0) : cr;
+    double* sX = stg; double* sY = stg + (size_t)cr * p;
+    e = launch_untile(d->D, d->s.ld, 0, row0 + i0, rows, p, sX, rows, ctx->stream);
+    if (e == cudaSuccess) e = launch_untile(d->D, d->s.ld, d->s.p2, row0 + i0, rows, q, sY, rows, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(X + i0, ldX * sizeof(double), sX, rows * sizeof(double), rows * sizeof(double), (size_t)p,
+                            cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(Y + i0, ldY * sizeof(double), sY, rows * sizeof(double), rows * sizeof(double), (size_t)q,
+                            cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  }
+  cudaFree(stg);
+  if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("export: ") + cudaGetErrorString(e));
+  return PPLS_OK;
+}
+
+extern "C" int ppls_data_info(const ppls_data* d, int64_t* n, int64_t* p, int64_t* q, int64_t* n_total, double* ssqX,
+                              double* ssqY) {
+  if (!d) return fail(PPLS_E_INVALID, "null data handle");
+  if (n) *n = d->s.n;
+  if (p) *p = d->s.p;
+  if (q) *q = d->s.q;
+  if (n_total) *n_total = d->n_total;
+  if (ssqX) *ssqX = d->ssq[0];
+  if (ssqY) *ssqY = d->ssq[1];
+  return PPLS_OK;
+}
+
+extern "C" int ppls_data_destroy(ppls_data* d) {
+  if (!d) return PPLS_OK;
+  if (d->ctx) cudaSetDevice(d->ctx->device);
+  if (d->D) cudaFree(d->D);
+  delete d;
+  return PPLS_OK;
+}
+
+// ---- one EM run -----------------------------------------------------------------------------------
+struct ppls_fit {
+  ppls_ctx* ctx = nullptr;
+  const ppls_data* data = nullptr;
+  ppls_opts opts{};
+  StreamPlan plan{};
+  int R = 0;
+  int64_t veclen = 0;
+  double *L = nullptr, *Lscratch = nullptr, *partials = nullptr, *momvec = nullptr, *trace = nullptr;
+  FitState* st = nullptr;        // device
+  FitState* st_host = nullptr;   // pinned mirror
+  bool finished = false;
+  int32_t passes = 0;
+  // timing
+  std::vector<cudaEvent_t> ev_free;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_k1;
+  ppls_timing tm{};
+};
+
+static void fit_free(ppls_fit* f) {
+  if (!f) return;
+  if (f->ctx) cudaSetDevice(f->ctx->device);
+  for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  for (auto e : f->ev_free) cudaEventDestroy(e);
+  cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
+  cudaFree(f->st);
+  if (f->st_host) cudaFreeHost(f->st_host);
+  delete f;
+}
+
+extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
+                               ppls_fit** out) {
+  if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+  *out = nullptr;
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!d || !opts) return fail(PPLS_E_INVALID, "null data or options");
+  if (d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
+  rc = check_params(init, "init");
+  if (rc) return rc;
+  const int R = opts->r;
+  if (R < 1 || R > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
+  if (R > d->s.p || R > d->s.q) return fail(PPLS_E_INVALID, "nr_comp exceeds ncol(X) or ncol(Y)");
+  if (opts->max_steps < 0) return fail(PPLS_E_INVALID, "EMsteps must be >= 0");
+  if (opts->orth_type != PPLS_ORTH_SVD && opts->orth_type != PPLS_ORTH_QR) return fail(PPLS_E_INVALID, "type must be SVD or QR");
+  ppls_fit* f = new (std::nothrow) ppls_fit();
+  if (!f) return fail(PPLS_E_OOM, "host allocation failed");
+  f->ctx = ctx; f->data = d; f->opts = *opts; f->R = R;
+  const char* why = "";
+  cudaError_t e = plan_stream(d->s, R, ctx->sm_count, &f->plan, &why);
+  if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_UNSUPPORTED, std::string("streaming-kernel plan: ") + why); }
+  f->veclen = momvec_len(d->s.ld, R);
+  const size_t Lbytes = (size_t)d->s.ld * R * sizeof(double);
+  e = cudaMalloc(&f->L, Lbytes);
+  if (e == cudaSuccess) e = cudaMalloc(&f->Lscratch, Lbytes);
+  if (e == cudaSuccess) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&f->momvec, (size_t)f->veclen * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&f->trace, (size_t)(opts->max_steps + 1) * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc(&f->st, sizeof(FitState));
+  if (e == cudaSuccess) e = cudaMallocHost(&f->st_host, sizeof(FitState));
+  if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_OOM, std::string("fit workspace: ") + cudaGetErrorString(e)); }
+  std::vector<double> L;
+  pack_loadings(d->s, R, init->W, init->C, L);
+  FitState* h = f->st_host;
+  memset(h, 0, sizeof(FitState));
+  for (int k = 0; k < R; ++k) { h->b[k] = init->B[k]; h->t[k] = init->sigT[k]; }
+  h->sigE = init->sigE; h->sigF = init->sigF; h->sigH = init->sigH;
+  h->ssqX = d->ssq[0]; h->ssqY = d->ssq[1]; h->Ntot = (double)d->n_total;
+  h->max_steps = opts->max_steps; h->orth_type = opts->orth_type; h->R = R; h->atol = opts->atol;
+  e = cudaMemcpyAsync(f->L, L.data(), Lbytes, cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(f->st, h, sizeof(FitState), cudaMemcpyHostToDevice, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(f->trace, 0, (size_t)(opts->max_steps + 1) * sizeof(double), ctx->stream);
+  if (e == cudaSuccess) e = launch_em_prepare(d->s, R, f->L, f->st, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // L (host vector) must outlive the copy
+  if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_CUDA, std::string("fit setup: ") + cudaGetErrorString(e)); }
+  f->tm.kernel_launches = 1;
+  f->tm.bytes_per_pass = (int64_t)8 * d->s.n * ((int64_t)d->s.p + d->s.q);
+  *out = f;
+  return PPLS_OK;
+}
+
+static cudaEvent_t fit_event(ppls_fit* f) {
+  if (!f->ev_free.empty()) { cudaEvent_t e = f->ev_free.back(); f->ev_free.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+// read the control block back (after a stream sync) and fold finished timings
+static int fit_poll(ppls_fit* f) {
+  ppls_ctx* ctx = f->ctx;
+  CU(cudaMemcpyAsync(f->st_host, f->st, sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  for (auto& pr : f->ev_k1) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) { f->tm.stream_ms += ms; f->tm.stream_launches += 1; }
+    f->ev_free.push_back(pr.first); f->ev_free.push_back(pr.second);
+  }
+  f->ev_k1.clear();
+  f->finished = f->st_host->done != 0;
+  if (f->st_host->status != PPLS_OK)
+    return fail(f->st_host->status, "a parameter became non-finite during EM (degenerate data or start values)");
+  return PPLS_OK;
+}
+
+extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_done, int32_t* finished) {
+  if (!f) return fail(PPLS_E_INVALID, "null fit handle");
+  int rc = ctx_activate(f->ctx);
+  if (rc) return rc;
+  ppls_ctx* ctx = f->ctx;
+  const DataShape& s = f->data->s;
+  const bool timing = (f->opts.flags & PPLS_F_TIMING) != 0;
+  int check_every = f->opts.check_every > 0 ? f->opts.check_every : 16;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  if (timing) { ev0 = fit_event(f); ev1 = fit_event(f); cudaEventRecord(ev0, ctx->stream); }
+  int32_t since_check = 0;
+  // passes the device may still run: it stops by itself (done flag), the host only bounds the queue
+  for (int32_t i = 0; i < n_passes && !f->finished; ++i) {
+    if (f->passes > f->opts.max_steps) break;
+    cudaEvent_t a = nullptr, b = nullptr;
+    if (timing) { a = fit_event(f); b = fit_event(f); cudaEventRecord(a, ctx->stream); }
+    cudaError_t e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream);
+    if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+    if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
+    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
+    rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
+    if (rc) return rc;
+    e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, ctx->stream);
+    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
+    f->tm.kernel_launches += 3;
+    f->passes += 1;
+    if (++since_check >= check_every) {
+      rc = fit_poll(f);
+      if (rc) return rc;
+      since_check = 0;
+    }
+  }
+  if (timing) cudaEventRecord(ev1, ctx->stream);
+  rc = fit_poll(f);
+  if (rc) return rc;
+  if (timing) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) f->tm.loop_ms += ms;
+    f->ev_free.push_back(ev0); f->ev_free.push_back(ev1);
+  }
+  // passes actually executed on the device (later launches were no-ops once done was set)
+  const int32_t dev_passes = f->st_host->done ? f->st_host->steps_done + 1 : f->st_host->pass;
+  f->tm.passes = dev_passes;
+  if (passes_done) *passes_done = dev_passes;
+  if (finished) *finished = f->finished ? 1 : 0;
+  return PPLS_OK;
+}
+
+extern "C" int ppls_fit_result(ppls_fit* f, ppls_params* est, double* loglik, int32_t* steps_done, double* moments,
+                               double* mu_T, double* mu_U) {
+  if (!f) return fail(PPLS_E_INVALID, "null fit handle");
+  int rc = ctx_activate(f->ctx);
+  if (rc) return rc;
+  ppls_ctx* ctx = f->ctx;
+  const DataShape& s = f->data->s;
+  const int R = f->R;
+  rc = fit_poll(f);
+  if (rc) return rc;
+  const FitState* h = f->st_host;
+  if (!f->finished) return fail(PPLS_E_INVALID, "the run has not ended yet: call ppls_fit_iterate until finished");
+  if ((mu_T == nullptr) != (mu_U == nullptr)) return fail(PPLS_E_INVALID, "pass both mu_T and mu_U or neither");
+  if (est) {
+    rc = check_params(est, "est");
+    if (rc) return rc;
+    std::vector<double> L((size_t)s.ld * R);
+    CU(cudaMemcpyAsync(L.data(), f->L, L.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < R; ++k) {
+      for (int j = 0; j < s.p; ++j) est->W[j + (size_t)k * s.p] = L[(size_t)j * R + k];
+      for (int j = 0; j < s.q; ++j) est->C[j + (size_t)k * s.q] = L[(size_t)(s.p2 + j) * R + k];
+      est->B[k] = h->b[k]; est->sigT[k] = h->t[k];
+    }
+    est->sigE = h->sigE; est->sigF = h->sigF; est->sigH = h->sigH;
+  }
+  if (steps_done) *steps_done = h->steps_done;
+  if (loglik && h->steps_done > 0) {
+    CU(cudaMemcpyAsync(loglik, f->trace, (size_t)h->steps_done * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
+  if (moments) {
+    double* m = moments;
+    for (int k = 0; k < R; ++k) m[k] = h->Ctt[k];
+    for (int k = 0; k < R; ++k) m[R + k] = h->Cuu[k];
+    for (int k = 0; k < R; ++k) m[2 * R + k] = h->Cut[k];
+    m[3 * R] = h->Cee; m[3 * R + 1] = h->Cff;
+    for (int e = 0; e < R * R; ++e) m[3 * R + 2 + e] = h->Chh[e];
+  }
+  if (mu_T) {
+    // One more pass with the final parameters writes the posterior means (EM_W_multi.R:802).
+    double* dmu = nullptr;
+    CU(cudaMalloc(&dmu, (size_t)2 * s.n * R * sizeof(double)));
+    cudaError_t e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, dmu, dmu + (size_t)s.n * R, 1, ctx->stream);
+    f->tm.kernel_launches += 1;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(mu_T, dmu, (size_t)s.n * R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(mu_U, dmu + (size_t)s.n * R, (size_t)s.n * R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(dmu);
+    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("posterior-means pass: ") + cudaGetErrorString(e));
+  }
+  return PPLS_OK;
+}
+
+extern "C" int ppls_fit_timing(const ppls_fit* f, ppls_timing* out) {
+  if (!f || !out) return fail(PPLS_E_INVALID, "null argument");
+  *out = f->tm;
+  return PPLS_OK;
+}
+
+extern "C" int ppls_fit_destroy(ppls_fit* f) {
+  fit_free(f);
+  return PPLS_OK;
+}
+
+extern "C" int ppls_simult_run(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
+                               ppls_params* est, double* loglik, int32_t* steps_done, double* moments, double* mu_T,
+                               double* mu_U) {
+  ppls_fit* f = nullptr;
+  int rc = ppls_fit_create(ctx, d, opts, init, &f);
+  if (rc) return rc;
+  int32_t done = 0, fin = 0;
+  while (!fin) {
+    rc = ppls_fit_iterate(f, opts->max_steps + 1, &done, &fin);
+    if (rc) { fit_free(f); return rc; }
+    if (!fin && done > opts->max_steps) { fit_free(f); return fail(PPLS_E_CUDA, "EM loop did not terminate"); }
+  }
+  rc = ppls_fit_result(f, est, loglik, steps_done, moments, mu_T, mu_U);
+  fit_free(f);
+  return rc;
+}

@@ -1,0 +1,91 @@
+// Internal declarations shared by the translation units of libppls_b200.so.
+// Not part of the C ABI (that is include/ppls_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/ppls_b200.h"
+
+namespace ppls {
+
+constexpr int MAXR = PPLS_MAX_R;
+
+// ---------------------------------------------------------------------------------------
+// HBM layout of a data shard (DESIGN.md "Data layout"):
+//   D[n][ld] row-major FP64, ld = p2 + q2, p2 = p rounded up to even, q2 likewise.
+//   Row i = [ x_i (p values) | 0-pad | y_i (q values) | 0-pad ].  A tile of T rows is one
+//   contiguous T*ld*8-byte block -> one cp.async.bulk per tile, perfectly sequential DRAM.
+// Loadings live in the same column space: L[ld][R] row-major (W rows then C rows).
+// ---------------------------------------------------------------------------------------
+struct DataShape {
+  int64_t n;        // local rows
+  int32_t p, q;     // logical columns
+  int32_t p2, q2;   // padded (even)
+  int32_t ld;       // p2 + q2
+};
+
+// Layout of the per-CTA partial vector and of the reduced vector ("moment vector"):
+//   [ G (ld x R, row-major: G1 rows then G2 rows) | Gxx (R x R) | Gxy (R x R) | Gyy (R x R) ]
+// Gxx[k][l] = sum_i Xw[i,k] Xw[i,l];  Gxy[k][l] = sum_i Xw[i,k] Yc[i,l];  Gyy likewise.
+__host__ __device__ inline int64_t momvec_len(int ld, int R) { return (int64_t)ld * R + 3 * R * R; }
+
+// Device-resident state of one EM run.  Written only by the update kernel (K2).
+struct FitState {
+  // parameters theta_k (loop order)
+  double b[MAXR], t[MAXR];
+  double sigE, sigF, sigH;
+  // coefficients the streaming kernel needs for theta_k:
+  //   mu_T[:,k] = aT[k] Xw[:,k] + bT[k] Yc[:,k];  mu_U[:,k] = aU[k] Xw[:,k] + bU[k] Yc[:,k]
+  double aT[MAXR], bT[MAXR], aU[MAXR], bU[MAXR];
+  // Gram matrices of the current loadings (exact algebraic residuals for any W, C)
+  double WtW[MAXR * MAXR], CtC[MAXR * MAXR];
+  // E-step second moments at the parameters of the last pass
+  double Ctt[MAXR], Cuu[MAXR], Cut[MAXR], Cee, Cff, Chh[MAXR * MAXR];
+  double loglik_last;
+  // data constants
+  double ssqX, ssqY;     // global ||X||_F^2, ||Y||_F^2
+  double Ntot;           // global row count
+  // control
+  int32_t pass;          // index k of the NEXT pass to run
+  int32_t done;          // 1 once the break rule or max_steps ended the run
+  int32_t steps_done;    // EM steps completed (= length of the loglik trace)
+  int32_t status;        // PPLS_OK or PPLS_E_NONFINITE
+  int32_t max_steps, orth_type, R, pad_;
+  double atol;
+};
+
+// ---- launchers (host functions defined in the .cu files) -------------------------------
+struct StreamPlan {          // how K1 is launched for one shape
+  int R, M, T, nstage;
+  int nwX, nwY;              // warps owning X column chunks / Y column chunks
+  int threads, grid, ctas_per_sm;
+  size_t smem_bytes;
+  int64_t ntiles;
+};
+
+cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* plan, const char** why);
+// One data pass: per-CTA partials -> `partials` [grid][momvec_len].
+cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const double* D,
+                             const double* L, const FitState* st, double* partials,
+                             double* muT, double* muU, int write_mu, cudaStream_t stream);
+// Sum the per-CTA partials in CTA order -> momvec.
+cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t len, double* momvec,
+                                   const FitState* st, cudaStream_t stream);
+// K2: loglik, E-step moments, break rule, M-step, next coefficients.
+cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
+                             FitState* st, double* trace, cudaStream_t stream);
+// Prepare coefficients + Gram matrices for the start state (pass 0).
+cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream);
+
+// data.cu
+cudaError_t launch_retile(const double* colmajor, int64_t ldc, int64_t nrows, int ncols,
+                          double* D, int ld, int col0, int64_t row0, cudaStream_t stream);
+cudaError_t launch_untile(const double* D, int ld, int col0, int64_t row0, int64_t nrows, int ncols,
+                          double* colmajor, int64_t ldc, cudaStream_t stream);
+cudaError_t launch_zero_pad(double* D, const DataShape& s, cudaStream_t stream);
+cudaError_t launch_ssq(const double* D, const DataShape& s, double* out2, double* scratch, int nblocks,
+                       cudaStream_t stream);
+cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, int R, uint64_t seed,
+                         const double* Ltruth /*[ld][R]*/, const double* b, const double* t,
+                         double sigE, double sigF, double sigH, cudaStream_t stream);
+
+}  // namespace ppls

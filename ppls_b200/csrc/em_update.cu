@@ -1,0 +1,493 @@
+// K2 "em_update": the tiny replicated update between two data passes, FP64, sm_100a.
+// Compiled with -fmad=false: the closed-form coefficients below cancel catastrophically
+// for small noise variances and must be evaluated exactly as the reference writes them.
+//
+// From the reduced moment vector of pass k (parameters theta_k) it computes
+//   loglik(theta_k)            logl_W, Package/PPLS/R/EM_W_multi.R:297-323 (coefficients :312-320)
+//                              + loglC_fast, Package/PPLS/src/loglC.cpp:331-336
+//   E-step second moments      Expect_M fast branch, EM_W_multi.R:672-680, :696-712, masks :715-716
+//   the break rule             PPLS_simult, :792 (signed increment, i > 1)
+//   M-step -> theta_{k+1}      Maximiz_M, :729-742; orth() = OmicsPLS::orth (polar factor /
+//                              Householder QR, historical copy Package/functions.R:252-260)
+//   coefficients of mu_T, mu_U for the next pass (:691-694 with the diagonal algebra collapsed)
+#include "common.cuh"
+#include <math.h>
+
+namespace ppls {
+
+constexpr int UPD_THREADS = 512;
+constexpr int UPD_WARPS = UPD_THREADS / 32;
+
+// Closed-form inverse coefficients.  squared_g = false: as Expect_M evaluates them (:672-680);
+// squared_g = true: as logl_W does (:312-320; g is stored as a square root and re-squared).
+__device__ void closed_form_coef(bool sqrt_g, double b, double t, double sE, double sF, double sH,
+                                 double* c1, double* c2, double* c3, double* Kc_out) {
+  const double t2 = t * t, t4 = pow(t, 4.0), t6 = pow(t, 6.0), b2 = b * b;
+  const double sE2 = sE * sE, sF2 = sF * sF, sH2 = sH * sH;
+  double g = t2 * b2 + sH2;
+  if (sqrt_g) { g = sqrt(g); g = g * g; }
+  const double Kw = t2 - t4 * b2 / sF2 + t4 * b2 * g / (sF2 * (g + sF2));
+  const double Kc = g - t4 * b2 / sE2 + t6 * b2 / (sE2 * (t2 + sE2));
+  const double Kwc = t2 * b / (sE2 * sF2) - Kc * t2 * b / (sE2 * sF2 * (Kc + sF2)) -
+                     t4 * b / (sE2 * sF2 * (t2 + sE2)) +
+                     Kc * t4 * b / (sE2 * sF2 * (Kc + sF2) * (t2 + sE2));
+  *c1 = Kw / (sE2 * (Kw + sE2));
+  *c3 = Kc / (sF2 * (Kc + sF2));
+  *c2 = Kwc;
+  *Kc_out = Kc;
+}
+
+// Coefficients of the posterior means for the streaming kernel (EM_W_multi.R:691-694):
+//   mu_T[:,k] = aT Xw[:,k] + bT Yc[:,k],  mu_U[:,k] = aU Xw[:,k] + bU Yc[:,k]
+__device__ void posterior_coef(FitState* st, int R) {
+  const double sE = st->sigE, sF = st->sigF, sH = st->sigH;
+  const double isE2 = pow(sE, -2.0), isF2 = pow(sF, -2.0);
+  for (int k = 0; k < R; ++k) {
+    const double b = st->b[k], t = st->t[k];
+    double c1, c2, c3, Kc;
+    closed_form_coef(false, b, t, sE, sF, sH, &c1, &c2, &c3, &Kc);
+    const double t2 = t * t, varU = t2 * (b * b) + sH * sH;
+    st->aT[k] = isE2 * t2 - c1 * t2 - c2 * t2 * b;
+    st->bT[k] = isF2 * (t2 * b) - c2 * t2 - c3 * b * t2;
+    st->aU[k] = isE2 * (t2 * b) - c1 * t2 * b - c2 * varU;
+    st->bU[k] = isF2 * varU - c2 * t2 * b - c3 * varU;
+  }
+}
+
+// ---- deterministic block reductions (fixed thread partition, fixed tree) -------------------
+// Sums nv (<= 36) per-thread values over the CTA; result in out[0..nv) (shared), all threads sync.
+__device__ void block_reduce_vec(double* vals, int nv, double* out, double* scratch /*[UPD_WARPS*36]*/) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int v = 0; v < nv; ++v) {
+    double x = vals[v];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) scratch[warp * 36 + v] = x;
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < nv) {
+    double s = 0.0;
+    for (int w = 0; w < UPD_WARPS; ++w) s += scratch[w * 36 + threadIdx.x];
+    out[threadIdx.x] = s;
+  }
+  __syncthreads();
+}
+
+// Gram matrix A'A of A [n][R] row-major -> S (shared, R*R, symmetric, both triangles).
+template <int R>
+__device__ void block_gram(const double* A, int n, double* S, double* scratch) {
+  constexpr int NV = R * (R + 1) / 2;
+  double v[NV];
+#pragma unroll
+  for (int e = 0; e < NV; ++e) v[e] = 0.0;
+  for (int j = threadIdx.x; j < n; j += UPD_THREADS) {
+    double row[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) row[k] = A[(size_t)j * R + k];
+    int e = 0;
+#pragma unroll
+    for (int k = 0; k < R; ++k)
+#pragma unroll
+      for (int l = k; l < R; ++l) v[e++] += row[k] * row[l];
+  }
+  __shared__ double packed[36];
+  block_reduce_vec(v, NV, packed, scratch);
+  if (threadIdx.x == 0) {
+    int e = 0;
+    for (int k = 0; k < R; ++k)
+      for (int l = k; l < R; ++l) { S[k * R + l] = packed[e]; S[l * R + k] = packed[e]; ++e; }
+  }
+  __syncthreads();
+}
+
+// Cyclic Jacobi eigen-decomposition of a symmetric R x R matrix (one thread).
+// On exit A is (numerically) diagonal and the columns of V are the eigenvectors.
+template <int R>
+__device__ void jacobi_eig(double* A, double* V) {
+  for (int i = 0; i < R; ++i)
+    for (int j = 0; j < R; ++j) V[i * R + j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < R; ++i) {
+      diag += A[i * R + i] * A[i * R + i];
+      for (int j = i + 1; j < R; ++j) off += A[i * R + j] * A[i * R + j];
+    }
+    if (off <= 1e-40 * diag || off == 0.0) break;
+    for (int p = 0; p < R - 1; ++p)
+      for (int q = p + 1; q < R; ++q) {
+        const double apq = A[p * R + q];
+        if (apq == 0.0) continue;
+        const double theta = (A[q * R + q] - A[p * R + p]) / (2.0 * apq);
+        const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(tt * tt + 1.0), s = tt * c;
+        for (int k = 0; k < R; ++k) {  // A <- A J
+          const double akp = A[k * R + p], akq = A[k * R + q];
+          A[k * R + p] = c * akp - s * akq;
+          A[k * R + q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < R; ++k) {  // A <- J' A
+          const double apk = A[p * R + k], aqk = A[q * R + k];
+          A[p * R + k] = c * apk - s * aqk;
+          A[q * R + k] = s * apk + c * aqk;
+        }
+        for (int k = 0; k < R; ++k) {
+          const double vkp = V[k * R + p], vkq = V[k * R + q];
+          V[k * R + p] = c * vkp - s * vkq;
+          V[k * R + q] = s * vkp + c * vkq;
+        }
+      }
+  }
+}
+
+// out[j][:] = A[j][:] * Mat (R x R, shared) for all rows j.
+template <int R>
+__device__ void rows_times(const double* A, int n, const double* Mat, double* out) {
+  for (int j = threadIdx.x; j < n; j += UPD_THREADS) {
+    double row[R], res[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) row[k] = A[(size_t)j * R + k];
+#pragma unroll
+    for (int l = 0; l < R; ++l) {
+      double s = 0.0;
+#pragma unroll
+      for (int k = 0; k < R; ++k) s += row[k] * Mat[k * R + l];
+      res[l] = s;
+    }
+#pragma unroll
+    for (int l = 0; l < R; ++l) out[(size_t)j * R + l] = res[l];
+  }
+  __syncthreads();
+}
+
+// orth(G, "SVD"): the polar factor U V' = G (G'G)^{-1/2}, then one Newton-Schulz step
+// W <- W (3I - W'W)/2 that restores orthonormality to rounding regardless of cond(G)^2 lost
+// in the Gram matrix.  G, out: [n][R] row-major (out may alias neither G nor itself).
+template <int R>
+__device__ void orth_polar(const double* G, int n, double* out, double* S, double* Mat,
+                           double* scratch) {
+  block_gram<R>(G, n, S, scratch);
+  if (threadIdx.x == 0) {
+    double A[R * R], V[R * R];
+    for (int e = 0; e < R * R; ++e) A[e] = S[e];
+    jacobi_eig<R>(A, V);
+    for (int i = 0; i < R; ++i)
+      for (int j = 0; j < R; ++j) {
+        double s = 0.0;
+        for (int k = 0; k < R; ++k) s += V[i * R + k] * (1.0 / sqrt(A[k * R + k])) * V[j * R + k];
+        Mat[i * R + j] = s;
+      }
+  }
+  __syncthreads();
+  rows_times<R>(G, n, Mat, out);
+  block_gram<R>(out, n, S, scratch);
+  if (threadIdx.x == 0)
+    for (int i = 0; i < R; ++i)
+      for (int j = 0; j < R; ++j) Mat[i * R + j] = (i == j ? 1.5 : 0.0) - 0.5 * S[i * R + j];
+  __syncthreads();
+  rows_times<R>(out, n, Mat, out);
+}
+
+// orth(G, "QR"): qr.Q(qr(G)) with the Householder sign convention R_ll = -sign(x_ll)||x_l||
+// (LINPACK dqrdc2 and LAPACK dgeqr2 agree on it), times sign(e[,1]'G[,1]) = sign(R_11).
+// A: working copy of G [n][R] (destroyed), Q: output [n][R].
+template <int R>
+__device__ void orth_qr(double* A, int n, double* Q, double* scratch) {
+  __shared__ double tau[R], beta0, red[36];
+  for (int l = 0; l < R; ++l) {
+    double v[1 + R];
+    for (int e = 0; e <= R; ++e) v[e] = 0.0;
+    for (int j = l + 1 + threadIdx.x; j < n; j += UPD_THREADS) v[0] += A[(size_t)j * R + l] * A[(size_t)j * R + l];
+    block_reduce_vec(v, 1, red, scratch);
+    const double alpha = A[(size_t)l * R + l], xnorm2 = red[0];
+    __syncthreads();
+    double beta, tl, scale;
+    if (xnorm2 == 0.0) { beta = alpha; tl = 0.0; scale = 0.0; }
+    else {
+      beta = -copysign(sqrt(alpha * alpha + xnorm2), alpha);
+      tl = (beta - alpha) / beta;
+      scale = 1.0 / (alpha - beta);
+    }
+    for (int j = l + 1 + threadIdx.x; j < n; j += UPD_THREADS) A[(size_t)j * R + l] *= scale;
+    __syncthreads();
+    if (threadIdx.x == 0) { tau[l] = tl; if (l == 0) beta0 = beta; A[(size_t)l * R + l] = beta; }
+    // apply H_l to the trailing columns
+    for (int e = 0; e <= R; ++e) v[e] = 0.0;
+    for (int j = l + threadIdx.x; j < n; j += UPD_THREADS) {
+      const double vj = (j == l) ? 1.0 : A[(size_t)j * R + l];
+      for (int c = l + 1; c < R; ++c) v[c] += vj * A[(size_t)j * R + c];
+    }
+    block_reduce_vec(v, R, red, scratch);
+    for (int j = l + threadIdx.x; j < n; j += UPD_THREADS) {
+      const double vj = (j == l) ? 1.0 : A[(size_t)j * R + l];
+      for (int c = l + 1; c < R; ++c) A[(size_t)j * R + c] -= tl * vj * red[c];
+    }
+    __syncthreads();
+  }
+  // Q = H_0 ... H_{R-1} [I; 0]
+  for (int j = threadIdx.x; j < n; j += UPD_THREADS)
+    for (int c = 0; c < R; ++c) Q[(size_t)j * R + c] = (j == c) ? 1.0 : 0.0;
+  __syncthreads();
+  for (int l = R - 1; l >= 0; --l) {
+    double v[1 + R];
+    for (int e = 0; e <= R; ++e) v[e] = 0.0;
+    for (int j = l + threadIdx.x; j < n; j += UPD_THREADS) {
+      const double vj = (j == l) ? 1.0 : A[(size_t)j * R + l];
+      for (int c = l; c < R; ++c) v[c] += vj * Q[(size_t)j * R + c];
+    }
+    block_reduce_vec(v, R, red, scratch);
+    const double tl = tau[l];
+    for (int j = l + threadIdx.x; j < n; j += UPD_THREADS) {
+      const double vj = (j == l) ? 1.0 : A[(size_t)j * R + l];
+      for (int c = l; c < R; ++c) Q[(size_t)j * R + c] -= tl * vj * red[c];
+    }
+    __syncthreads();
+  }
+  const double sgn = (beta0 > 0.0) ? 1.0 : (beta0 < 0.0 ? -1.0 : 0.0);
+  for (int j = threadIdx.x; j < n; j += UPD_THREADS)
+    for (int c = 0; c < R; ++c) Q[(size_t)j * R + c] *= sgn;
+  __syncthreads();
+}
+
+struct UpdateArgs {
+  const double* momvec;   // [ld*R | Gxx | Gxy | Gyy]
+  double* L;              // [ld][R] loadings, overwritten with theta_{k+1}
+  double* Lscratch;       // [ld][R] work space (QR)
+  FitState* st;
+  double* trace;          // [max_steps]
+  int32_t p, q, p2, q2, ld;
+};
+
+__device__ inline bool finite_d(double x) { return isfinite(x); }
+
+// Scalar part (one thread): loglik(theta_k), E-step moments, break rule, M-step scalars.
+// Returns 1 when the run ends with this pass.
+template <int R>
+__device__ int update_scalars(const UpdateArgs& a) {
+  FitState* st = a.st;
+  const double* Gxx = a.momvec + (size_t)a.ld * R;
+  const double* Gxy = Gxx + R * R;
+  const double* Gyy = Gxy + R * R;
+  const double N = st->Ntot, p = (double)a.p, q = (double)a.q;
+  const double sE = st->sigE, sF = st->sigF, sH = st->sigH;
+  const double sE2 = sE * sE, sF2 = sF * sF, sH2 = sH * sH;
+  const int k_pass = st->pass;
+
+  // ---- log-likelihood at theta_k: logl_W :312-320 + loglC_fast loglC.cpp:331-336 ----------
+  {
+    double Logdiag = 0.0, sumT = 0.0, sumK = 0.0;
+    double traceL = 1.0 / sE2 * st->ssqX + 1.0 / sF2 * st->ssqY;
+    for (int k = 0; k < R; ++k) {
+      double c1, c2, c3, Kc;
+      closed_form_coef(true, st->b[k], st->t[k], sE, sF, sH, &c1, &c2, &c3, &Kc);
+      sumT += log(sE2 + st->t[k] * st->t[k]);
+      sumK += log(sF2 + Kc);
+      traceL += -c1 * Gxx[k * R + k] - 2.0 * c2 * Gxy[k * R + k] - c3 * Gyy[k * R + k];
+    }
+    Logdiag = sumT + (p - R) * log(sE2) + sumK + (q - R) * log(sF2);
+    const double ll = -0.5 * N * (p + q) * log(2.0 * 3.14159265358979323846) - 0.5 * N * Logdiag - 0.5 * traceL;
+    st->loglik_last = ll;
+    if (k_pass >= 1) a.trace[k_pass - 1] = ll;
+  }
+
+  // ---- E-step second moments at theta_k: Expect_M :672-712 ----------------------------------
+  const double isE2 = pow(sE, -2.0), isF2 = pow(sF, -2.0);
+  const double sE4 = pow(sE, 4.0), sF4 = pow(sF, 4.0), sH4 = pow(sH, 4.0);
+  double c1v[R], c2v[R], c3v[R];
+  double sumc1 = 0.0, sumc3 = 0.0;
+  for (int k = 0; k < R; ++k) {
+    double Kc;
+    closed_form_coef(false, st->b[k], st->t[k], sE, sF, sH, &c1v[k], &c2v[k], &c3v[k], &Kc);
+    sumc1 += c1v[k]; sumc3 += c3v[k];
+  }
+  for (int k = 0; k < R; ++k) {
+    const double b = st->b[k], t = st->t[k], t2 = t * t, t4 = pow(t, 4.0), b2 = b * b;
+    const double varU = t2 * b2 + sH2;
+    const double c1 = c1v[k], c2 = c2v[k], c3 = c3v[k];
+    const double aT = st->aT[k], bT = st->bT[k], aU = st->aU[k], bU = st->bU[k];
+    const double xx = Gxx[k * R + k], xy = Gxy[k * R + k], yy = Gyy[k * R + k];
+    const double mTT = aT * aT * xx + 2.0 * aT * bT * xy + bT * bT * yy;     // crossprod(mu_T)[k,k]
+    const double mUU = aU * aU * xx + 2.0 * aU * bU * xy + bU * bU * yy;     // crossprod(mu_U)[k,k]
+    const double mUT = aU * aT * xx + (aU * bT + bU * aT) * xy + bU * bT * yy;
+    const double Ctt = t2 - isE2 * t4 - isF2 * (t4 * b2) + t4 * c1 + 2.0 * t4 * b * c2 + t4 * b2 * c3 + mTT / N;
+    const double Cuu = varU - isE2 * (t4 * b2) - isF2 * (varU * varU) + t4 * b2 * c1 +
+                       2.0 * t2 * b * varU * c2 + varU * varU * c3 + mUU / N;
+    const double Cut = t2 * b - isE2 * (t4 * b) - isF2 * (t2 * b * varU) + t4 * b * c1 + t2 * varU * c2 +
+                       t4 * b2 * c2 + t2 * b * varU * c3 + mUT / N;
+    st->Ctt[k] = fabs(Ctt);     // masks of :715-716
+    st->Cuu[k] = fabs(Cuu);
+    st->Cut[k] = Cut;
+  }
+  // residual sums of squares, algebraically from the Gram matrices (exact for any W, C):
+  //   mu_E = X - M W',  M = Xw diag(sE2 c1) + Yc diag(sE2 c2)                      (:703)
+  //   ||mu_E||^2 = ||X||^2 - 2 tr(M'Xw) + tr(M'M W'W)
+  double ssqE = st->ssqX, ssqF = st->ssqY;
+  for (int k = 0; k < R; ++k) {
+    const double Ak = sE2 * c1v[k], Bk = sE2 * c2v[k];       // on Xw, on Yc
+    const double Fk = sF2 * c3v[k], Hk = sF2 * c2v[k];       // mu_F: on Yc, on Xw     (:708)
+    ssqE -= 2.0 * (Ak * Gxx[k * R + k] + Bk * Gxy[k * R + k]);
+    ssqF -= 2.0 * (Fk * Gyy[k * R + k] + Hk * Gxy[k * R + k]);
+    for (int l = 0; l < R; ++l) {
+      const double Al = sE2 * c1v[l], Bl = sE2 * c2v[l];
+      const double Fl = sF2 * c3v[l], Hl = sF2 * c2v[l];
+      const double MtM = Ak * Al * Gxx[k * R + l] + Ak * Bl * Gxy[k * R + l] + Bk * Al * Gxy[l * R + k] +
+                         Bk * Bl * Gyy[k * R + l];
+      const double MtMf = Fk * Fl * Gyy[k * R + l] + Fk * Hl * Gxy[l * R + k] + Hk * Fl * Gxy[k * R + l] +
+                          Hk * Hl * Gxx[k * R + l];
+      ssqE += MtM * st->WtW[l * R + k];
+      ssqF += MtMf * st->CtC[l * R + k];
+    }
+  }
+  const double Cee = (p * sE2 - p * sE2 + sE4 * sumc1 + ssqE / N) / p;     // :706
+  const double Cff = (q * sF2 - q * sF2 + sF4 * sumc3 + ssqF / N) / q;     // :709
+  st->Cee = Cee; st->Cff = Cff;
+  // Chh (:711-712): mu_H[:,k] = hX_k Xw[:,k] + hY_k Yc[:,k]; full r x r, abs, not masked
+  double trChh = 0.0;
+  for (int k = 0; k < R; ++k)
+    for (int l = 0; l < R; ++l) {
+      const double hXk = -sH2 * c2v[k], hYk = isF2 * sH2 - sH2 * c3v[k];
+      const double hXl = -sH2 * c2v[l], hYl = isF2 * sH2 - sH2 * c3v[l];
+      double v = (hXk * hXl * Gxx[k * R + l] + hXk * hYl * Gxy[k * R + l] + hYk * hXl * Gxy[l * R + k] +
+                  hYk * hYl * Gyy[k * R + l]) / N;
+      if (k == l) v += (sH2 - sH4 / sF2) + sH4 * c3v[k];
+      v = fabs(v);
+      st->Chh[k + l * R] = v;
+      if (k == l) trChh += v;
+    }
+
+  // ---- break rule (:792) / EMsteps exhausted -------------------------------------------------
+  bool done = (k_pass >= st->max_steps);
+  if (k_pass >= 2 && (a.trace[k_pass - 1] - a.trace[k_pass - 2]) < st->atol) done = true;
+  if (!finite_d(st->loglik_last)) { st->status = PPLS_E_NONFINITE; done = true; }
+  if (done) { st->done = 1; st->steps_done = k_pass; return 1; }
+
+  // ---- M-step scalars (:734-738) -> theta_{k+1} -----------------------------------------------
+  bool ok = true;
+  for (int k = 0; k < R; ++k) {
+    const double bn = st->Cut[k] * (1.0 / st->Ctt[k]);       // Cut %*% solve(Ctt) * I
+    const double tn = sqrt(st->Ctt[k]);
+    st->b[k] = bn; st->t[k] = tn;
+    ok = ok && finite_d(bn) && finite_d(tn);
+  }
+  st->sigE = sqrt(Cee); st->sigF = sqrt(Cff); st->sigH = sqrt(trChh / R);
+  ok = ok && finite_d(st->sigE) && finite_d(st->sigF) && finite_d(st->sigH);
+  posterior_coef(st, R);
+  for (int k = 0; k < R; ++k) ok = ok && finite_d(st->aT[k]) && finite_d(st->bT[k]) && finite_d(st->aU[k]) && finite_d(st->bU[k]);
+  st->pass = k_pass + 1;
+  if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = k_pass; return 1; }
+  return 0;
+}
+
+template <int R>
+__global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateArgs a) {
+  __shared__ double scratch[UPD_WARPS * 36], S[R * R], Mat[R * R];
+  __shared__ int s_done;
+  FitState* st = a.st;
+  if (st->done) return;
+  if (threadIdx.x == 0) s_done = update_scalars<R>(a);
+  __syncthreads();
+  if (s_done) return;
+  // ---- loadings: W = orth(t(X) mu_T), C = orth(t(Y) mu_U)  (:732-733) ----------------------------
+  const double* G1 = a.momvec;
+  const double* G2 = a.momvec + (size_t)a.p2 * R;
+  double* Wn = a.L;
+  double* Cn = a.L + (size_t)a.p2 * R;
+  if (st->orth_type == PPLS_ORTH_QR) {
+    for (size_t e = threadIdx.x; e < (size_t)a.ld * R; e += UPD_THREADS) a.Lscratch[e] = a.momvec[e];
+    __syncthreads();
+    orth_qr<R>(a.Lscratch, a.p2, Wn, scratch);
+    orth_qr<R>(a.Lscratch + (size_t)a.p2 * R, a.q2, Cn, scratch);
+  } else {
+    orth_polar<R>(G1, a.p2, Wn, S, Mat, scratch);
+    orth_polar<R>(G2, a.q2, Cn, S, Mat, scratch);
+  }
+  block_gram<R>(Wn, a.p2, S, scratch);
+  if (threadIdx.x < R * R) st->WtW[threadIdx.x] = S[threadIdx.x];
+  __syncthreads();
+  block_gram<R>(Cn, a.q2, S, scratch);
+  if (threadIdx.x < R * R) st->CtC[threadIdx.x] = S[threadIdx.x];
+  if (threadIdx.x == 0) {
+    bool ok = true;
+    for (int e = 0; e < R * R; ++e) ok = ok && finite_d(st->WtW[e]) && finite_d(S[e]);
+    if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = st->pass - 1; }
+  }
+}
+
+// Start state: coefficients and Gram matrices for theta_0.
+template <int R>
+__global__ void __launch_bounds__(UPD_THREADS, 1) em_prepare_kernel(const UpdateArgs a) {
+  __shared__ double scratch[UPD_WARPS * 36], S[R * R];
+  FitState* st = a.st;
+  block_gram<R>(a.L, a.p2, S, scratch);
+  if (threadIdx.x < R * R) st->WtW[threadIdx.x] = S[threadIdx.x];
+  __syncthreads();
+  block_gram<R>(a.L + (size_t)a.p2 * R, a.q2, S, scratch);
+  if (threadIdx.x < R * R) st->CtC[threadIdx.x] = S[threadIdx.x];
+  if (threadIdx.x == 0) {
+    posterior_coef(st, R);
+    st->pass = 0; st->done = 0; st->steps_done = 0; st->status = PPLS_OK;
+    bool ok = true;
+    for (int k = 0; k < R; ++k) ok = ok && finite_d(st->aT[k]) && finite_d(st->bT[k]) && finite_d(st->aU[k]) && finite_d(st->bU[k]);
+    if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; }
+  }
+}
+
+// out[e] = sum over CTAs (in CTA order) of partials[c][e]
+__global__ void reduce_partials_kernel(const double* __restrict__ partials, int nparts, int64_t len,
+                                       double* __restrict__ out, const FitState* st) {
+  if (st->done) return;
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= len) return;
+  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+  int c = 0;
+  for (; c + 3 < nparts; c += 4) {
+    s0 += partials[(size_t)c * len + e];
+    s1 += partials[(size_t)(c + 1) * len + e];
+    s2 += partials[(size_t)(c + 2) * len + e];
+    s3 += partials[(size_t)(c + 3) * len + e];
+  }
+  for (; c < nparts; ++c) s0 += partials[(size_t)c * len + e];
+  out[e] = (s0 + s1) + (s2 + s3);
+}
+
+cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t len, double* momvec,
+                                   const FitState* st, cudaStream_t stream) {
+  const int threads = 128;
+  reduce_partials_kernel<<<(unsigned)((len + threads - 1) / threads), threads, 0, stream>>>(partials, nparts, len, momvec, st);
+  return cudaGetLastError();
+}
+
+template <int R>
+static void launch_update_R(const UpdateArgs& a, bool prepare, cudaStream_t stream) {
+  if (prepare) em_prepare_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
+  else em_update_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
+}
+
+static cudaError_t dispatch_update(const DataShape& s, int R, const double* momvec, double* L,
+                                   double* Lscratch, FitState* st, double* trace, bool prepare,
+                                   cudaStream_t stream) {
+  UpdateArgs a;
+  a.momvec = momvec; a.L = L; a.Lscratch = Lscratch; a.st = st; a.trace = trace;
+  a.p = s.p; a.q = s.q; a.p2 = s.p2; a.q2 = s.q2; a.ld = s.ld;
+  switch (R) {
+    case 1: launch_update_R<1>(a, prepare, stream); break;
+    case 2: launch_update_R<2>(a, prepare, stream); break;
+    case 3: launch_update_R<3>(a, prepare, stream); break;
+    case 4: launch_update_R<4>(a, prepare, stream); break;
+    case 5: launch_update_R<5>(a, prepare, stream); break;
+    case 6: launch_update_R<6>(a, prepare, stream); break;
+    case 7: launch_update_R<7>(a, prepare, stream); break;
+    case 8: launch_update_R<8>(a, prepare, stream); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
+                             FitState* st, double* trace, cudaStream_t stream) {
+  return dispatch_update(s, R, momvec, L, Lscratch, st, trace, false, stream);
+}
+cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream) {
+  return dispatch_update(s, R, nullptr, const_cast<double*>(L), nullptr, st, nullptr, true, stream);
+}
+
+}  // namespace ppls

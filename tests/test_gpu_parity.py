@@ -1,0 +1,132 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the golden vectors of
+the CPU oracle and against the oracle run on fresh seeded inputs."""
+import numpy as np
+import pytest
+
+from helpers import (TOL_PARAM, golden_cases, init_of, load_golden, loglik_tol, moment_tol, relmax)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from ppls_b200 import Context
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def _run(ctx, X, Y, init, r, steps, atol, typ, want_mu=True):
+    from ppls_b200 import Data, Fit
+    d = Data.from_host(ctx, X, Y)
+    f = Fit(d, init, r, steps, atol, typ)
+    f.run()
+    res = f.result(want_mu=want_mu)
+    f.close(); d.close()
+    return res
+
+
+def _compare(res, g, name):
+    assert res["steps"] == len(g["loglik"]), (res["steps"], len(g["loglik"]))
+    assert relmax(res["loglik"], g["loglik"]) < loglik_tol(name)
+    for key, ref in (("W", "loop_W"), ("C", "loop_C"), ("B", "loop_B"), ("sigT", "loop_sigT")):
+        assert relmax(res[key], g[ref]) < TOL_PARAM, key
+    # est_sig holds (sigE, sigF, sigH) of the final state
+    for key, ref in (("sigE", 0), ("sigF", 1), ("sigH", 2)):
+        assert abs(res[key] / float(g["est_sig"][ref]) - 1) < TOL_PARAM, key
+    mt = moment_tol(name)
+    for key in ("Ctt", "Cuu", "Cut", "Chh", "mu_T", "mu_U"):
+        assert relmax(res[key], g[key]) < mt, key
+    assert abs(res["Cee"] / float(g["Cee"]) - 1) < mt and abs(res["Cff"] / float(g["Cff"]) - 1) < mt
+
+
+@pytest.mark.parametrize("name", golden_cases())
+def test_golden(ctx, name):
+    """Same inputs, same start, same number of EM steps as the oracle: parameters <= 1e-8,
+    log-likelihood <= 1e-10 relative (BASELINE.json north_star)."""
+    g = load_golden(name)
+    if str(g["type"]) == "QR":
+        res = _run(ctx, g["X"], g["Y"], init_of(g), int(g["r"]), int(g["EMsteps"]), float(g["atol"]), "QR")
+    else:
+        res = _run(ctx, g["X"], g["Y"], init_of(g), int(g["r"]), int(g["EMsteps"]), float(g["atol"]), "SVD")
+    _compare(res, g, name)
+
+
+def test_public_api_matches_reference_structure(ctx):
+    """PPLS_simult(X, Y, a, EMsteps, atol, type): same list structure and normalised estimates."""
+    from ppls_b200 import PPLS_simult
+    g = load_golden("c1_wellcond_1000")
+    out = PPLS_simult(g["X"], g["Y"], int(g["r"]), EMsteps=1000, atol=-np.inf, type=("SVD", "QR"), init=init_of(g), ctx=ctx)
+    assert set(out["Expectations"]) == {"mu_T", "mu_U", "Ctt", "Cuu", "Cut", "Cee", "Cff", "Chh"}
+    assert set(out["estimates"]) == {"W", "C", "B", "sigE", "sigF", "sigH", "sigT"}
+    assert out["class"] == "PPLS_simult"
+    assert relmax(out["estimates"]["W"], g["est_W"]) < TOL_PARAM
+    assert relmax(out["estimates"]["C"], g["est_C"]) < TOL_PARAM
+    assert relmax(np.diag(out["estimates"]["B"]), g["est_B"]) < TOL_PARAM
+    assert relmax(np.diag(out["estimates"]["sigT"]), g["est_sigT"]) < TOL_PARAM
+    assert out["estimates"]["B"].shape == (2, 2) and out["Expectations"]["Cee"].shape == (1, 1)
+    assert relmax(out["loglik"], g["loglik"]) < 1e-10
+
+
+def test_synthetic_generator_bit_exact(ctx, oracle_lib):
+    """Device generator == host restatement, bit for bit, for any row offset (sharding)."""
+    from oracle import cbind
+    from ppls_b200 import Data, synth
+    truth = synth.truth_params(37, 14, 3)
+    d = Data.synthetic(ctx, 1000, 37, 14, truth, seed=99, row0=12345)
+    X, Y = d.export()
+    Xo, Yo = cbind.gen_data(oracle_lib, 99, 12345, 1000, truth)
+    assert np.array_equal(X, Xo) and np.array_equal(Y, Yo)
+    sx, sy = float(np.sum(Xo * Xo)), float(np.sum(Yo * Yo))
+    assert abs(d.ssqX / sx - 1) < 1e-13 and abs(d.ssqY / sy - 1) < 1e-13
+    d.close()
+
+
+def test_export_roundtrip(ctx):
+    from ppls_b200 import Data
+    rng = np.random.default_rng(0)
+    X = rng.standard_normal((301, 33)); Y = rng.standard_normal((301, 7))
+    d = Data.from_host(ctx, X, Y)
+    X2, Y2 = d.export()
+    assert np.array_equal(X, X2) and np.array_equal(Y, Y2)
+    X3, Y3 = d.export(100, 57)
+    assert np.array_equal(X[100:157], X3) and np.array_equal(Y[100:157], Y3)
+    d.close()
+
+
+@pytest.mark.parametrize("shape", [(20000, 500, 100, 3), (5003, 1000, 200, 3), (4099, 257, 63, 5), (9000, 64, 64, 4)])
+def test_fresh_inputs_vs_fused_oracle(ctx, oracle_lib, shape):
+    """Device-generated data at bench-like row widths, a few EM steps, against the fused CPU
+    restatement run on the exported data."""
+    from oracle import ppls_fused as F
+    from ppls_b200 import Data, Fit, synth
+    N, p, q, r = shape
+    truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
+    d = Data.synthetic(ctx, N, p, q, truth, seed=4242)
+    st = synth.start_params(truth, 3)
+    f = Fit(d, st, r, 6, -np.inf, "SVD")
+    f.run()
+    res = f.result()
+    X, Y = d.export()
+    o = F.fused_loop(oracle_lib, X, Y, st["W"], st["C"], st["B"], st["sigE"], st["sigF"], st["sigH"], st["sigT"],
+                     EMsteps=6, atol=-np.inf)
+    assert relmax(res["loglik"], o["loglik"]) < 1e-10
+    for k in ("W", "C", "B", "sigT", "Ctt", "Cuu", "Cut", "Chh", "mu_T", "mu_U"):
+        assert relmax(res[k], o[k]) < TOL_PARAM, k
+    f.close(); d.close()
+
+
+def test_error_behaviour(ctx):
+    """Argument checks mirror the reference's stopifnot()s (EM_W_multi.R:237-240)."""
+    from ppls_b200 import Data, Fit, PPLSError, default_init
+    rng = np.random.default_rng(1)
+    d = Data.from_host(ctx, rng.standard_normal((50, 6)), rng.standard_normal((50, 4)))
+    with pytest.raises(PPLSError):
+        Fit(d, default_init(6, 4, 5), 5)              # nr_comp > ncol(Y)
+    with pytest.raises(ValueError):
+        Fit(d, default_init(6, 4, 2), 2, type="PCA")
+    with pytest.raises(ValueError):
+        Data.from_host(ctx, np.zeros((5, 3)), np.zeros((6, 2)))
+    d.close()
