@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""Benchmark of the PPLS_simult EM loop: FP64 EM iterations/s and fraction of the HBM roofline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c2|...]
+
+A "step" is one EM iteration = one pass of the streaming kernel over the resident data plus the
+tiny update.  Default workload = BASELINE.json's headline shape (very tall N=1e7, p=1000, q=200,
+r=3; 96 GB, resident in one B200's HBM).  With N GPUs the SAME total shape is row-sharded
+(strong scaling), one process per GPU (torchrun), one NCCL allreduce of (p+q)r+3r^2 doubles per
+iteration inside the library.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (N, p, q, r)   -- BASELINE.json configs
+    "c1": (500, 20, 10, 2),
+    "c2": (1_000_000, 500, 100, 3),
+    "c3": (10_000_000, 1000, 200, 3),
+    "c5shape": (100_000, 200, 50, 2),
+}
+METRIC = "FP64 EM iterations/sec at N x p x q x r; achieved HBM GB/s vs peak"
+UNIT = "EM iterations/s"
+SEED = 20261106
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons during the timed region (pynvml, 100 ms)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        self.index = index
+        self._t = None
+
+    def start(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+            return
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=2)
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def shard_rows(N, rank, world):
+    lo, hi = N * rank // world, N * (rank + 1) // world
+    return lo, hi - lo
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from ppls_b200 import Context, Data, Fit, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(Context.nccl_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        ctx = Context(local, rank, world, bytes(idt.cpu().numpy().tobytes()))
+    else:
+        ctx = Context(local)
+
+    N, p, q, r = WORKLOADS[args.workload]
+    if args.rows:
+        N = args.rows
+    free_b, _ = torch.cuda.mem_get_info(dev)
+    row0, n_local = shard_rows(N, rank, world)
+    need = 8 * n_local * (p + q + 4) + (2 << 30)
+    if need > free_b:
+        raise SystemExit(f"workload {args.workload} needs {need/2**30:.1f} GiB per GPU, {free_b/2**30:.1f} free")
+    truth = synth.truth_params(p, q, r)
+    start = synth.start_params(truth, seed=1)
+    t0 = time.perf_counter()
+    data = Data.synthetic(ctx, n_local, p, q, truth, seed=SEED, row0=row0)
+    gen_s = time.perf_counter() - t0
+
+    K, W = args.steps, max(args.warmup, 0)
+
+    def barrier():
+        ctx.sync()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    fit = Fit(data, start, r, EMsteps=W + K + 8, atol=-float("inf"), type="SVD", timing=True, check_every=W + K + 8)
+    if W:
+        fit.iterate(W)
+    tm0 = fit.timing()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    h0 = time.perf_counter()
+    done, fin = fit.iterate(K)
+    barrier()
+    wall_ms = (time.perf_counter() - h0) * 1e3
+    clocks = sampler.stop()
+    tm1 = fit.timing()
+    assert done == W + K and not fin, (done, fin)
+    loop_ms = tm1["loop_ms"] - tm0["loop_ms"]
+    k1_ms = (tm1["stream_ms"] - tm0["stream_ms"]) / max(tm1["stream_launches"] - tm0["stream_launches"], 1)
+    launches = tm1["kernel_launches"] - tm0["kernel_launches"]
+    if world > 1:
+        t = torch.tensor([loop_ms, k1_ms, wall_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        loop_ms, k1_ms, wall_ms = (float(x) for x in t.cpu())
+    fit.close()
+
+    # ---- e2e: the public call with HOST buffers (upload + K steps + download), on a row sample ----
+    e2e = None
+    if not args.no_e2e:
+        ns = min(n_local, args.e2e_rows)
+        Xh, Yh = data.export(0, ns)                      # product API; gives the host-side inputs
+        Xp = torch.empty((p, ns), dtype=torch.float64, pin_memory=True)
+        Yp = torch.empty((q, ns), dtype=torch.float64, pin_memory=True)
+        Xn, Yn = Xp.numpy().T, Yp.numpy().T               # column-major views (R layout), pinned
+        Xn[...] = Xh; Yn[...] = Yh
+        del Xh, Yh
+        barrier()
+        e0 = time.perf_counter()
+        d2 = Data.from_host(ctx, Xn, Yn)
+        f2 = Fit(d2, start, r, EMsteps=K, atol=-float("inf"), type="SVD")
+        f2.run()
+        res = f2.result(want_mu=False)
+        ctx.sync()
+        e_s = time.perf_counter() - e0
+        f2.close(); d2.close()
+        if world > 1:
+            t = torch.tensor([e_s], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e_s = float(t.cpu()[0])
+        scale = n_local / ns
+        e2e = {"value": K / (e_s * scale), "unit": UNIT, "h2d_bytes_per_step": int(8 * ns * (p + q) * scale / K),
+               "d2h_bytes_per_step": int(8 * ((p + q) * r + 2 * r + 3 + K) / K),
+               "sample": f"one PPLS_simult-style call (upload {ns} rows/GPU from pinned host memory, {K} EM steps, "
+                         f"download estimates+loglik), time scaled x{scale:.1f} to the full shard",
+               "seconds_sample": e_s, "loglik_last": float(res["loglik"][-1])}
+        del Xp, Yp
+    data.close()
+
+    if rank != 0:
+        return
+    peak, peak_src = measured_peak()
+    bytes_pass = 8 * n_local * (p + q)                    # algorithmic bytes one launch reads (this rank)
+    achieved = bytes_pass / (k1_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "k1_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            tj = json.load(open(tpath))
+            if tj.get("workload") == args.workload and tj.get("gpus", 1) == world:
+                traffic = tj.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    out = {
+        "metric": METRIC, "value": K / (loop_ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": loop_ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.workload}: N={N} p={p} q={q} r={r} (row-sharded {world}x{n_local})",
+                   "l2": "inputs larger than L2 (no flush needed)" if bytes_pass > (256 << 20) else "inputs fit L2: L2-resident between iterations",
+                   "generate_s": round(gen_s, 2), "wall_ms_per_step": wall_ms / K},
+        "clocks": clocks, "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": traffic, "peak_source": peak_src, "kernel": "em_stream_kernel",
+                     "kernel_ms": k1_ms, "algorithmic_bytes_per_launch": bytes_pass,
+                     "frac_of_nominal_8000": achieved / 8000.0},
+    }
+    if e2e:
+        out["e2e"] = e2e
+    if not args.no_cpu and world == 1:
+        out["cpu_baseline"] = cpu_baseline(args, truth, start, N, p, q, r, K)
+    print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_reference_time(X, Y, start, steps):
+    """Time `steps` EM iterations of the op-for-op numpy restatement of the reference."""
+    from oracle import ppls_ref as R
+    W0, C0, B0, T0 = R.normalise(start["W"], start["C"], start["B"], start["sigT"])
+    t0 = time.perf_counter()
+    out = R.ppls_simult_loop(X, Y, W0, C0, B0, start["sigE"], start["sigF"], start["sigH"], T0, EMsteps=steps, atol=-np.inf)
+    return (time.perf_counter() - t0) / steps, out
+
+
+def cpu_baseline(args, truth, start, N, p, q, r, K):
+    from oracle import cbind, ppls_fused as F
+    L = cbind.load()
+    ns = min(N, args.cpu_rows)
+    X, Y = cbind.gen_data(L, SEED, 0, ns, truth)
+    steps = 2 if ns * (p + q) > 2e7 else 5
+    per_iter, _ = cpu_reference_time(X, Y, start, steps)
+    t0 = time.perf_counter()
+    F.fused_loop(L, X, Y, start["W"], start["C"], start["B"], start["sigE"], start["sigF"], start["sigH"], start["sigT"],
+                 EMsteps=steps, atol=-np.inf, want_mu=False)
+    fused_iter = (time.perf_counter() - t0) / (steps + 1)
+    scale = N / ns
+    return {"value": 1.0 / (per_iter * scale), "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+            "sample": f"oracle/ppls_ref.py (op-for-op numpy restatement of Expect_M/Maximiz_M/logl_W, BLAS threads = all cores) "
+                      f"on the first {ns} rows of the same generator, {steps} EM steps, time scaled x{scale:.0f} to N={N}",
+            "fused_cpu_value": 1.0 / (fused_iter * scale),
+            "fused_cpu_note": "oracle/ppls_fused.py: single-pass OpenMP restatement (best-effort CPU), same sample and scaling"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path on the host cores.  R is not
+    installed, so this is the oracle port (oracle/ppls_ref.py), on a bounded row sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import cbind
+    from ppls_b200 import synth
+    N, p, q, r = WORKLOADS[args.workload]
+    if args.rows:
+        N = args.rows
+    truth = synth.truth_params(p, q, r)
+    start = synth.start_params(truth, seed=1)
+    L = cbind.load()
+    ns = min(N, args.cpu_rows)
+    X, Y = cbind.gen_data(L, SEED, 0, ns, truth)
+    K, W = args.steps, max(args.warmup, 0)
+    K_eff = min(K, 3) if ns * (p + q) > 2e7 else K
+    if W:
+        cpu_reference_time(X, Y, start, 1)
+    per_iter, _ = cpu_reference_time(X, Y, start, K_eff)
+    scale = N / ns
+    value = 1.0 / (per_iter * scale)
+    sample = (f"oracle/ppls_ref.py on the first {ns} rows of the same generator, {K_eff} timed EM steps "
+              f"(bounded from --steps {K}), time scaled x{scale:.0f} to N={N}")
+    out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": K,
+           "warmup": W, "ms_per_step": per_iter * scale * 1e3, "higher_is_better": True, "scaling": "strong",
+           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": f"{args.workload}: N={N} p={p} q={q} r={r}"},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": sample},
+           "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override N (debugging)")
+    ap.add_argument("--e2e-rows", type=int, default=1_000_000)
+    ap.add_argument("--cpu-rows", type=int, default=100_000)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -19,6 +19,7 @@
 //   phase B: acc[j][k] += x[i,j] mu[i,k] re-reading the tile from shared memory.
 #include "common.cuh"
 #include <cstdlib>
+#include <cstdio>
 
 namespace ppls {
 
@@ -50,7 +51,7 @@ __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
-constexpr int RPITCH = 33;  // pitch (doubles) of the per-warp transpose buffer: conflict-free
+constexpr int RPITCH = 34;  // pitch (doubles) of the per-warp transpose buffer: 16B rows, conflict-free
 
 struct StreamArgs {
   const double* D;        // [n][ld]
@@ -63,52 +64,54 @@ struct StreamArgs {
   int32_t ld, p2, q2, nwX, nwY, nstage, write_mu;
 };
 
-// Upper bound on threads per CTA (register budget: 255 regs at 256 threads, 128 at 512).
+// Upper bound on threads per CTA incl. the reducer warp (register budget: 255 regs at 256
+// threads, 168 at 384, 128 at 512).
 __host__ __device__ constexpr int max_threads_for(int M, int R) {
-  return (M >= 4 || (M >= 2 && R >= 4) || R >= 7) ? 256 : 512;
+  return M >= 4 ? 256 : (M == 2 ? (R <= 3 ? 384 : 256) : (R <= 3 ? 512 : 384));
 }
 
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void named_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void named_arrive(int id, int nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+// named barriers: 1,2 = "projection partials of tile t ready" (t even/odd), 3,4 = "mu of tile t ready"
+constexpr int BAR_P = 1, BAR_M = 3;
+
+// Warp roles.  Warps 0..nwc-1 (nwc = nwX + nwY) are COMPUTE warps: each owns M chunks of 64
+// columns of X (or of Y) and keeps the loadings and the G accumulators of its columns in
+// registers.  Warp nwc is the REDUCER/PRODUCER: it sums the warps' projection partials, forms
+// mu_T/mu_U and the Gram terms, and keeps the shared-memory ring fed with cp.async.bulk.
+// Compute warps are software-pipelined -- A(t) then B(t-1) -- so the reducer's work on tile t
+// overlaps phase B of tile t-1 and never sits on the critical path.
 template <int R, int M, int T>
 __global__ void __launch_bounds__(max_threads_for(M, R), 1) em_stream_kernel(const StreamArgs a) {
-  constexpr int V = T * R;  // partial projections per thread and tile
+  constexpr int V = T * R;                       // projection values per tile
   static_assert(V <= 32, "T*R must fit one warp");
-  if (a.st->done && !a.write_mu) return;   // the posterior-means pass runs after the end
+  constexpr int H = (V <= 8) ? 4 : (V <= 16 ? 2 : 1);   // lane groups summing one value
+  constexpr int SEG = 32 / H;                    // staged lane-partials each group adds up
+  if (a.st->done && !a.write_mu) return;         // the posterior-means pass runs after the end
 
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nwarps = a.nwX + a.nwY;
+  const int nwc = a.nwX + a.nwY;
+  const int nbar = (nwc + 1) * 32;               // participants of the named barriers
   const int ld = a.ld;
   const size_t stage_doubles = (size_t)T * ld;
 
   double* stages = reinterpret_cast<double*>(smem_raw);
-  double* red = stages + stage_doubles * a.nstage;          // [nwarps][V][RPITCH]
-  double* wsum = red + (size_t)nwarps * V * RPITCH;          // [nwarps][V]
-  double* mu_s = wsum + (size_t)nwarps * V;                  // [2][V]
-  double* coef = mu_s + 2 * V;                               // aT,bT,aU,bU [4][R]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(coef + 4 * R);  // [nstage]
+  double* red = stages + stage_doubles * a.nstage;            // [nwc][V][RPITCH]
+  double* wsum = red + (size_t)nwc * V * RPITCH;               // [2][nwc][V]
+  double* mu_s = wsum + (size_t)2 * nwc * V;                   // [2][2][V]  (buf, T/U)
+  double* xy_s = mu_s + 4 * V;                                 // [2][V]     (reducer scratch: Xw, Yc)
+  double* coef = xy_s + 2 * V;                                 // aT,bT,aU,bU [4][R]
+  uint64_t* full = reinterpret_cast<uint64_t*>(coef + 4 * R);  // [nstage]
+  uint64_t* empty = full + a.nstage;                           // [nstage]
 
-  // ---- column ownership -------------------------------------------------------------
-  const bool isY = warp >= a.nwX;
-  const int wg = isY ? warp - a.nwX : warp;
-  const int nwg = isY ? a.nwY : a.nwX;
-  const int npairs = (isY ? a.q2 : a.p2) >> 1;
-  const int colbase = isY ? a.p2 : 0;
-  int col[M];
-  bool valid[M];
-  double w[M][2][R], acc[M][2][R];
-#pragma unroll
-  for (int m = 0; m < M; ++m) {
-    int u = (m * nwg + wg) * 32 + lane;
-    valid[m] = u < npairs;
-    col[m] = colbase + 2 * (valid[m] ? u : (npairs - 1));
-#pragma unroll
-    for (int c = 0; c < 2; ++c)
-#pragma unroll
-      for (int k = 0; k < R; ++k) {
-        w[m][c][k] = valid[m] ? a.L[(size_t)(col[m] + c) * R + k] : 0.0;
-        acc[m][c][k] = 0.0;
-      }
-  }
   if (tid < R) {
     coef[0 * R + tid] = a.st->aT[tid];
     coef[1 * R + tid] = a.st->bT[tid];
@@ -118,7 +121,7 @@ __global__ void __launch_bounds__(max_threads_for(M, R), 1) em_stream_kernel(con
   // zero the ring once: rows of a short last tile that are never loaded must stay finite
   for (size_t e = tid; e < stage_doubles * a.nstage; e += blockDim.x) stages[e] = 0.0;
   if (tid == 0) {
-    for (int s = 0; s < a.nstage; ++s) mbar_init(smem_u32(&bars[s]), 1);
+    for (int s = 0; s < a.nstage; ++s) { mbar_init(smem_u32(&full[s]), 1); mbar_init(smem_u32(&empty[s]), nwc); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   fence_proxy_async();
@@ -126,140 +129,207 @@ __global__ void __launch_bounds__(max_threads_for(M, R), 1) em_stream_kernel(con
 
   const int64_t my_tiles = (a.ntiles > (int64_t)blockIdx.x)
                                ? (a.ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  auto issue = [&](int64_t it) {  // one elected thread: bulk copy of this CTA's it-th tile
-    const int64_t tile = (int64_t)blockIdx.x + it * gridDim.x;
-    const int s = (int)(it % a.nstage);
-    const int64_t row0 = tile * T;
-    const int rows = (int)((a.n - row0 < T) ? (a.n - row0) : T);
-    const uint32_t bytes = (uint32_t)((size_t)rows * ld * sizeof(double));
-    const uint32_t bar = smem_u32(&bars[s]);
-    mbar_expect_tx(bar, bytes);
-    bulk_g2s(smem_u32(stages + stage_doubles * s), a.D + (size_t)row0 * ld, bytes, bar);
-  };
-  if (tid == 0)
-    for (int64_t it = 0; it < a.nstage && it < my_tiles; ++it) issue(it);
+  double* out = a.partials + (size_t)blockIdx.x * momvec_len(ld, R);
 
-  // Gram accumulators of warp 0: lane (i,k) keeps sums over this CTA's tiles
-  double gxx[R], gxy[R], gyy[R];
-#pragma unroll
-  for (int l = 0; l < R; ++l) gxx[l] = gxy[l] = gyy[l] = 0.0;
+  if (warp == nwc) {
+    // =============================== reducer / producer warp ===============================
+    auto issue = [&](int64_t it) {  // lane 0: bulk copy of this CTA's it-th tile
+      const int64_t tile = (int64_t)blockIdx.x + it * gridDim.x;
+      const int s = (int)(it % a.nstage);
+      const int64_t row0 = tile * T;
+      const int rows = (int)((a.n - row0 < T) ? (a.n - row0) : T);
+      const uint32_t bytes = (uint32_t)((size_t)rows * ld * sizeof(double));
+      const uint32_t bar = smem_u32(&full[s]);
+      mbar_expect_tx(bar, bytes);
+      bulk_g2s(smem_u32(stages + stage_doubles * s), a.D + (size_t)row0 * ld, bytes, bar);
+    };
+    if (lane == 0)
+      for (int64_t it = 0; it < a.nstage && it < my_tiles; ++it) issue(it);
 
-  double* red_w = red + (size_t)warp * V * RPITCH;
+    const int i = lane / R, k = lane - i * R;     // lane (i,k) owns Xw[i,k], Yc[i,k] of the tile
+    const bool act = lane < V;
+    double cT0 = 0, cT1 = 0, cU0 = 0, cU1 = 0;
+    if (act) { cT0 = coef[k]; cT1 = coef[R + k]; cU0 = coef[2 * R + k]; cU1 = coef[3 * R + k]; }
+    double gxx[R], gxy[R], gyy[R];
+#pragma unroll
+    for (int l = 0; l < R; ++l) gxx[l] = gxy[l] = gyy[l] = 0.0;
 
-  for (int64_t it = 0; it < my_tiles; ++it) {
-    const int s = (int)(it % a.nstage);
-    const uint32_t parity = (uint32_t)((it / a.nstage) & 1);
-    const int64_t row0 = ((int64_t)blockIdx.x + it * gridDim.x) * T;
-    const int rows = (int)((a.n - row0 < T) ? (a.n - row0) : T);
-    const double* tile = stages + stage_doubles * s;
-    mbar_wait(smem_u32(&bars[s]), parity);
-
-    // ---- phase A: partial projections over this thread's columns ----------------------
-    double part[T][R];
-#pragma unroll
-    for (int i = 0; i < T; ++i)
-#pragma unroll
-      for (int k = 0; k < R; ++k) part[i][k] = 0.0;
-#pragma unroll
-    for (int i = 0; i < T; ++i) {
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        const double2 x = *reinterpret_cast<const double2*>(tile + (size_t)i * ld + col[m]);
-#pragma unroll
-        for (int k = 0; k < R; ++k) {
-          part[i][k] = fma(x.x, w[m][0][k], part[i][k]);
-          part[i][k] = fma(x.y, w[m][1][k], part[i][k]);
-        }
-      }
-    }
-    // transpose-reduce inside the warp: lane v (< V) ends with the warp total of value v
-#pragma unroll
-    for (int i = 0; i < T; ++i)
-#pragma unroll
-      for (int k = 0; k < R; ++k) red_w[(i * R + k) * RPITCH + lane] = part[i][k];
-    __syncwarp();
-    if (lane < V) {
-      const double* rv = red_w + lane * RPITCH;
-      double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        s0 += rv[j]; s1 += rv[j + 1]; s2 += rv[j + 2]; s3 += rv[j + 3];
-      }
-      wsum[warp * V + lane] = (s0 + s1) + (s2 + s3);
-    }
-    __syncthreads();  // S1: warp totals visible; every warp has left phase B of tile it-1
-
-    if (tid == 0 && it >= 1 && it - 1 + a.nstage < my_tiles) issue(it - 1 + a.nstage);
-
-    if (warp == 0) {
-      const int i = lane / R, k = lane - i * R;
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      const int buf = (int)(it & 1);
+      const int64_t row0 = ((int64_t)blockIdx.x + it * gridDim.x) * T;
+      const int rows = (int)((a.n - row0 < T) ? (a.n - row0) : T);
+      named_sync(BAR_P + buf, nbar);              // all compute warps delivered tile `it`
       double xw = 0.0, yc = 0.0;
-      if (lane < V && i < rows) {
-        for (int ww = 0; ww < a.nwX; ++ww) xw += wsum[ww * V + lane];
-        for (int ww = a.nwX; ww < nwarps; ++ww) yc += wsum[ww * V + lane];
+      if (act && i < rows) {
+        const double* ws = wsum + (size_t)buf * nwc * V + lane;
+        double x1 = 0.0, y1 = 0.0;
+        int ww = 0;
+        for (; ww + 1 < a.nwX; ww += 2) { xw += ws[ww * V]; x1 += ws[(ww + 1) * V]; }
+        if (ww < a.nwX) xw += ws[ww * V];
+        for (ww = a.nwX; ww + 1 < nwc; ww += 2) { yc += ws[ww * V]; y1 += ws[(ww + 1) * V]; }
+        if (ww < nwc) yc += ws[ww * V];
+        xw += x1; yc += y1;
       }
-      if (lane < V) {
-        const double mt = coef[0 * R + k] * xw + coef[1 * R + k] * yc;
-        const double mu = coef[2 * R + k] * xw + coef[3 * R + k] * yc;
-        mu_s[lane] = mt;
-        mu_s[V + lane] = mu;
+      if (act) {
+        const double mt = cT0 * xw + cT1 * yc;
+        const double mu = cU0 * xw + cU1 * yc;
+        mu_s[(buf * 2 + 0) * V + lane] = mt;
+        mu_s[(buf * 2 + 1) * V + lane] = mu;
+        xy_s[lane] = xw;
+        xy_s[V + lane] = yc;
         if (a.write_mu && i < rows) {
           a.muT[(size_t)k * a.n + row0 + i] = mt;
           a.muU[(size_t)k * a.n + row0 + i] = mu;
         }
       }
+      __syncwarp();
+      named_arrive(BAR_M + buf, nbar);            // mu of tile `it` is ready
+      if (act) {
 #pragma unroll
-      for (int l = 0; l < R; ++l) {
-        const int src = (lane < V) ? i * R + l : lane;
-        const double xl = __shfl_sync(0xffffffffu, xw, src);
-        const double yl = __shfl_sync(0xffffffffu, yc, src);
-        gxx[l] = fma(xw, xl, gxx[l]);
-        gxy[l] = fma(xw, yl, gxy[l]);
-        gyy[l] = fma(yc, yl, gyy[l]);
-      }
-    }
-    __syncthreads();  // S2: mu visible
-
-    // ---- phase B: G += x (outer) mu over this thread's columns --------------------------
-    const double* mu_g = mu_s + (isY ? V : 0);
-#pragma unroll
-    for (int i = 0; i < T; ++i) {
-      double mk[R];
-#pragma unroll
-      for (int k = 0; k < R; ++k) mk[k] = mu_g[i * R + k];
-#pragma unroll
-      for (int m = 0; m < M; ++m) {
-        const double2 x = *reinterpret_cast<const double2*>(tile + (size_t)i * ld + col[m]);
-#pragma unroll
-        for (int k = 0; k < R; ++k) {
-          acc[m][0][k] = fma(x.x, mk[k], acc[m][0][k]);
-          acc[m][1][k] = fma(x.y, mk[k], acc[m][1][k]);
+        for (int l = 0; l < R; ++l) {
+          const double xl = xy_s[i * R + l], yl = xy_s[V + i * R + l];
+          gxx[l] = fma(xw, xl, gxx[l]);
+          gxy[l] = fma(xw, yl, gxy[l]);
+          gyy[l] = fma(yc, yl, gyy[l]);
         }
       }
+      __syncwarp();
+      // producer: refill the stage of tile it-1 as soon as every compute warp finished B(it-1)
+      if (lane == 0 && it >= 1 && it - 1 + a.nstage < my_tiles) {
+        const int64_t prev = it - 1;
+        mbar_wait(smem_u32(&empty[prev % a.nstage]), (uint32_t)((prev / a.nstage) & 1));
+        issue(prev + a.nstage);
+      }
+      __syncwarp();
     }
-  }
-
-  // ---- epilogue: this CTA's partial moment vector ----------------------------------------
-  double* out = a.partials + (size_t)blockIdx.x * momvec_len(ld, R);
+    // Gram partials of this CTA: entry (which, k, l) = sum over tile rows i of lane (i,k)'s slot l.
+    // red is free once every compute warp is past its last transpose; the final __syncthreads
+    // pair below orders that.
+    __syncthreads();
+    if (act) {
 #pragma unroll
-  for (int m = 0; m < M; ++m)
-    if (valid[m]) {
+      for (int l = 0; l < R; ++l) {
+        red[(0 * R + l) * 32 + lane] = gxx[l];
+        red[(1 * R + l) * 32 + lane] = gxy[l];
+        red[(2 * R + l) * 32 + lane] = gyy[l];
+      }
+    }
+    __syncthreads();
+  } else {
+    // ===================================== compute warps =====================================
+    const bool isY = warp >= a.nwX;
+    const int wg = isY ? warp - a.nwX : warp;
+    const int nwg = isY ? a.nwY : a.nwX;
+    const int npairs = (isY ? a.q2 : a.p2) >> 1;
+    const int colbase = isY ? a.p2 : 0;
+    int col[M];
+    bool valid[M];
+    double w[M][2][R], acc[M][2][R];
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      int u = (m * nwg + wg) * 32 + lane;
+      valid[m] = u < npairs;
+      col[m] = colbase + 2 * (valid[m] ? u : (npairs - 1));
 #pragma unroll
       for (int c = 0; c < 2; ++c)
 #pragma unroll
-        for (int k = 0; k < R; ++k) out[(size_t)(col[m] + c) * R + k] = acc[m][c][k];
+        for (int k = 0; k < R; ++k) {
+          w[m][c][k] = valid[m] ? a.L[(size_t)(col[m] + c) * R + k] : 0.0;
+          acc[m][c][k] = 0.0;
+        }
     }
-  __syncthreads();  // ring and red buffers are dead now; reuse `red` for the Gram reduction
-  if (warp == 0 && lane < V) {
+    double* red_w = red + (size_t)warp * V * RPITCH;
+    const int rg = lane / V, rv = lane - rg * V;      // transpose-reduce: lane sums segment rg of value rv
+    const bool ract = lane < H * V;
+    const double* rsrc = red_w + rv * RPITCH + (ract ? rg : 0) * SEG;
+
+    auto phaseB = [&](int64_t it) {                   // G += x (outer) mu over this thread's columns
+      const int s = (int)(it % a.nstage);
+      const int buf = (int)(it & 1);
+      const double* tile = stages + stage_doubles * s;
+      const double* mu_g = mu_s + (buf * 2 + (isY ? 1 : 0)) * V;
+      named_sync(BAR_M + buf, nbar);
 #pragma unroll
-    for (int l = 0; l < R; ++l) {
-      red[(0 * R + l) * 32 + lane] = gxx[l];
-      red[(1 * R + l) * 32 + lane] = gxy[l];
-      red[(2 * R + l) * 32 + lane] = gyy[l];
+      for (int i = 0; i < T; ++i) {
+        double mk[R];
+#pragma unroll
+        for (int k = 0; k < R; ++k) mk[k] = mu_g[i * R + k];
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+          const double2 x = *reinterpret_cast<const double2*>(tile + (size_t)i * ld + col[m]);
+#pragma unroll
+          for (int k = 0; k < R; ++k) {
+            acc[m][0][k] = fma(x.x, mk[k], acc[m][0][k]);
+            acc[m][1][k] = fma(x.y, mk[k], acc[m][1][k]);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&empty[s]));   // this warp is done with the stage
+    };
+
+    for (int64_t it = 0; it < my_tiles; ++it) {
+      const int s = (int)(it % a.nstage);
+      const int buf = (int)(it & 1);
+      const double* tile = stages + stage_doubles * s;
+      mbar_wait(smem_u32(&full[s]), (uint32_t)((it / a.nstage) & 1));
+
+      // ---- phase A: partial projections over this thread's columns ----------------------
+      double part[T][R];
+#pragma unroll
+      for (int i = 0; i < T; ++i)
+#pragma unroll
+        for (int k = 0; k < R; ++k) part[i][k] = 0.0;
+#pragma unroll
+      for (int i = 0; i < T; ++i) {
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+          const double2 x = *reinterpret_cast<const double2*>(tile + (size_t)i * ld + col[m]);
+#pragma unroll
+          for (int k = 0; k < R; ++k) {
+            part[i][k] = fma(x.x, w[m][0][k], part[i][k]);
+            part[i][k] = fma(x.y, w[m][1][k], part[i][k]);
+          }
+        }
+      }
+      // transpose-reduce inside the warp through shared memory
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < T; ++i)
+#pragma unroll
+        for (int k = 0; k < R; ++k) red_w[(i * R + k) * RPITCH + lane] = part[i][k];
+      __syncwarp();
+      double s0 = 0.0, s1 = 0.0;
+      if (ract) {
+#pragma unroll
+        for (int j = 0; j < SEG; j += 2) {
+          const double2 v2 = *reinterpret_cast<const double2*>(rsrc + j);
+          s0 += v2.x; s1 += v2.y;
+        }
+      }
+      double tot = s0 + s1;
+      if (H >= 4) tot += __shfl_down_sync(0xffffffffu, tot, 2 * V);
+      if (H >= 2) tot += __shfl_down_sync(0xffffffffu, tot, V);
+      if (lane < V) wsum[((size_t)buf * nwc + warp) * V + lane] = tot;
+      __syncwarp();
+      named_arrive(BAR_P + buf, nbar);
+
+      if (it >= 1) phaseB(it - 1);
     }
+    if (my_tiles >= 1) phaseB(my_tiles - 1);
+
+    // ---- epilogue: this CTA's partial G ----------------------------------------------------
+#pragma unroll
+    for (int m = 0; m < M; ++m)
+      if (valid[m]) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+          for (int k = 0; k < R; ++k) out[(size_t)(col[m] + c) * R + k] = acc[m][c][k];
+      }
+    __syncthreads();
+    __syncthreads();
   }
-  __syncthreads();
-  // entry (which, k, l) = sum over tile rows i of lane (i,k)'s slot l
   for (int e = tid; e < 3 * R * R; e += blockDim.x) {
     const int which = e / (R * R), kl = e - which * R * R, k = kl / R, l = kl - k * R;
     double sum = 0.0;
@@ -273,9 +343,10 @@ __global__ void __launch_bounds__(max_threads_for(M, R), 1) em_stream_kernel(con
 // ---------------------------------------------------------------------------------------
 static size_t stream_smem_bytes(int R, int T, int nstage, int nwarps, int ld) {
   const size_t V = (size_t)T * R;
-  size_t doubles = (size_t)T * ld * nstage + (size_t)nwarps * V * RPITCH + (size_t)nwarps * V +
-                   2 * V + 4 * (size_t)R;
-  return doubles * sizeof(double) + (size_t)nstage * sizeof(uint64_t);
+  // nwarps = compute warps; see the carve-up at the top of the kernel
+  size_t doubles = (size_t)T * ld * nstage + (size_t)nwarps * V * RPITCH + 2 * (size_t)nwarps * V +
+                   4 * V + 2 * V + 4 * (size_t)R;
+  return doubles * sizeof(double) + 2 * (size_t)nstage * sizeof(uint64_t);
 }
 
 static int env_int(const char* name, int dflt) {
@@ -306,48 +377,46 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
   *why = "";
   if (R < 1 || R > MAXR) { *why = "nr_comp outside 1..8"; return cudaErrorInvalidValue; }
   const int chX = (s.p2 / 2 + 31) / 32, chY = (s.q2 / 2 + 31) / 32;
-  int T = env_int("PPLS_K1_T", (R <= 4) ? 8 : 4);
-  int M = env_int("PPLS_K1_M", 0);
-  if (M == 0) {
-    M = (chX >= 8 && R <= 5) ? 4 : (chX >= 3 ? 2 : 1);
-    // widen M until the warps fit the launch bound
-    for (;;) {
-      int nw = (chX + M - 1) / M + (chY + M - 1) / M;
-      if (nw * 32 <= max_threads_for(M, R)) break;
-      if (M == 1) M = 2; else if (M == 2 && R <= 5) M = 4; else break;
+  const size_t smem_max = 227 * 1024;  // usable dynamic shared memory per CTA (1 CTA per SM)
+  const int envT = env_int("PPLS_K1_T", 0), envM = env_int("PPLS_K1_M", 0), envS = env_int("PPLS_K1_STAGES", 0);
+  // M: columns per thread = 2M.  More warps (small M) hide latency, fewer (large M) amortise the
+  // per-warp projection reduce; the launch bound caps the warps.
+  int Ms[3], nM = 0;
+  if (envM) Ms[nM++] = envM;
+  else if (chX + chY <= 4) { Ms[0] = 1; Ms[1] = 2; Ms[2] = 4; nM = 3; }
+  else { Ms[0] = 4; Ms[1] = 2; Ms[2] = 1; nM = 3; }
+  int Ts[2], nT = 0;
+  if (envT) Ts[nT++] = envT; else { Ts[nT++] = 8; Ts[nT++] = 4; }
+  int bestM = 0, bestT = 0, bestS = 0, best_score = -1;
+  for (int im = 0; im < nM; ++im) {
+    const int M = Ms[im];
+    const int nw = (chX + M - 1) / M + (chY + M - 1) / M;
+    if ((nw + 1) * 32 > max_threads_for(M, R)) continue;
+    for (int it = 0; it < nT; ++it) {
+      const int T = Ts[it];
+      if (T * R > 32 || !lookup_kernel(R, M, T)) continue;
+      int ns = 0;
+      for (int c = envS ? envS : 8; c >= (envS ? envS : 2); --c)
+        if (stream_smem_bytes(R, T, c, nw, s.ld) <= smem_max) { ns = c; break; }
+      if (!ns) continue;
+      // prefer >= 4 stages (>= 2 tiles in flight), then the earlier M in the list, then larger T
+      const int score = (ns >= 4 ? 1000 : ns * 100) + (nM - im) * 10 + (T == 8 ? 1 : 0);
+      if (score > best_score) { best_score = score; bestM = M; bestT = T; bestS = ns; }
     }
   }
-  stream_kernel_t k = lookup_kernel(R, M, T);
-  if (!k) { *why = "no streaming-kernel instantiation for (R,M,T)"; return cudaErrorInvalidValue; }
-  const int nwX = (chX + M - 1) / M, nwY = (chY + M - 1) / M;
-  const int nwarps = nwX + nwY;
-  if (nwarps * 32 > max_threads_for(M, R)) {
-    *why = "row too wide for the row-streaming kernel (use the column-sharded path)";
+  if (best_score < 0) {
+    *why = "row tile does not fit shared memory / launch bound (use the column-sharded path)";
     return cudaErrorInvalidValue;
   }
-  const size_t smem_sm = 227 * 1024;  // usable per SM; each CTA also reserves 1 KB
-  int ctas = env_int("PPLS_K1_CTAS", 0), nstage = env_int("PPLS_K1_STAGES", 0);
+  const int M = bestM, T = bestT, nstage = bestS;
+  stream_kernel_t k = lookup_kernel(R, M, T);
+  const int nwX = (chX + M - 1) / M, nwY = (chY + M - 1) / M;
+  const int nwarps = nwX + nwY;
   const int64_t ntiles = (s.n + T - 1) / T;
-  auto fits = [&](int c, int ns) {
-    return (stream_smem_bytes(R, T, ns, nwarps, s.ld) + 1024) * (size_t)c <= smem_sm + 1024 &&
-           stream_smem_bytes(R, T, ns, nwarps, s.ld) <= smem_sm;
-  };
-  if (ctas == 0 || nstage == 0) {
-    int best_c = 0, best_ns = 0;
-    for (int c = (ctas ? ctas : 2); c >= (ctas ? ctas : 1) && !best_c; --c) {
-      int lo = nstage ? nstage : 2, hi = nstage ? nstage : (c == 2 ? 4 : 6);
-      for (int ns = hi; ns >= lo; --ns)
-        if (fits(c, ns)) { best_c = c; best_ns = ns; break; }
-    }
-    if (!best_c) { *why = "row tile does not fit shared memory (use the column-sharded path)"; return cudaErrorInvalidValue; }
-    ctas = best_c; nstage = best_ns;
-  } else if (!fits(ctas, nstage)) {
-    *why = "requested PPLS_K1_CTAS/PPLS_K1_STAGES do not fit shared memory"; return cudaErrorInvalidValue;
-  }
   plan->R = R; plan->M = M; plan->T = T; plan->nstage = nstage;
-  plan->nwX = nwX; plan->nwY = nwY; plan->threads = nwarps * 32;
-  plan->ctas_per_sm = ctas;
-  int64_t grid = (int64_t)sm_count * ctas;
+  plan->nwX = nwX; plan->nwY = nwY; plan->threads = (nwarps + 1) * 32;
+  plan->ctas_per_sm = 1;
+  int64_t grid = (int64_t)sm_count;
   if (grid > ntiles) grid = ntiles;
   if (grid < 1) grid = 1;
   plan->grid = (int)grid;
@@ -356,6 +425,9 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
   cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)plan->smem_bytes);
   if (e != cudaSuccess) { *why = "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed"; return e; }
+  if (env_int("PPLS_K1_VERBOSE", 0))
+    fprintf(stderr, "[ppls] K1 plan: R=%d M=%d T=%d stages=%d warps=%d+%d+1 grid=%d smem=%zu\n", R, M, T, nstage, nwX,
+            nwY, plan->grid, plan->smem_bytes);
   return cudaSuccess;
 }
 

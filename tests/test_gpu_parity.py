@@ -123,8 +123,9 @@ def test_error_behaviour(ctx):
     from ppls_b200 import Data, Fit, PPLSError, default_init
     rng = np.random.default_rng(1)
     d = Data.from_host(ctx, rng.standard_normal((50, 6)), rng.standard_normal((50, 4)))
+    bad = dict(W=np.zeros((6, 5)), C=np.zeros((4, 5)), B=np.ones(5), sigT=np.ones(5), sigE=1.0, sigF=1.0, sigH=1.0)
     with pytest.raises(PPLSError):
-        Fit(d, default_init(6, 4, 5), 5)              # nr_comp > ncol(Y)
+        Fit(d, bad, 5)                                # nr_comp > ncol(Y): stopifnot(ncol(Y) >= nr_comp)
     with pytest.raises(ValueError):
         Fit(d, default_init(6, 4, 2), 2, type="PCA")
     with pytest.raises(ValueError):
