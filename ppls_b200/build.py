@@ -14,6 +14,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 # translation unit -> extra flags.  -fmad=false where bit-exact / reference-order arithmetic matters.
 UNITS = {
     "em_stream.cu": [],
+    **{f"em_stream_inst.cu@r{r}": [f"-DPPLS_INST_R={r}"] for r in range(1, 9)},
     "em_update.cu": ["-fmad=false"],
     "data.cu": ["-fmad=false"],
     "capi.cu": [],
@@ -38,12 +39,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
-    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(HERE, "..", "include", "ppls_b200.h")]
+    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "em_stream_kernel.cuh"),
+               os.path.join(HERE, "..", "include", "ppls_b200.h")]
     objs = []
     procs = []
-    for src, extra in UNITS.items():
+    for unit, extra in UNITS.items():
+        src, _, tag = unit.partition("@")
         s = os.path.join(CSRC, src)
-        o = os.path.join(objdir, src.replace(".cu", ".o"))
+        o = os.path.join(objdir, src.replace(".cu", (("_" + tag) if tag else "") + ".o"))
         objs.append(o)
         if force or _stale(o, [s] + headers):
             cmd = [nvcc, *ARCH, *COMMON, *extra, "-c", s, "-o", o]

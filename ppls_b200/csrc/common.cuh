@@ -57,6 +57,7 @@ struct FitState {
 struct StreamPlan {          // how K1 is launched for one shape
   int R, M, T, nstage;
   int nwX, nwY;              // warps owning X column chunks / Y column chunks
+  int cX, bigX, cY, bigY;    // chunks per warp: the first bigX X-warps own cX+1, the rest cX (Y alike)
   int threads, grid, ctas_per_sm;
   size_t smem_bytes;
   int64_t ntiles;
