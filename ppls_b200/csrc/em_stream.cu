@@ -60,20 +60,25 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
     const int T = Ts[it];
     if (envT && T != envT) continue;
     if (T * R > 32 || (T * R) % 2) continue;
-    const int nw0 = envW ? envW : 8;
+    // ~3 chunks per warp, warps in multiples of the 4 SM sub-partitions (measured: tools/tune_k1.py)
+    const int nw0 = envW ? envW : 4 * ((chX + chY + 11) / 12);
     for (int nw = nw0; nw <= 30; ++nw) {
       StreamPlan p{};
       split_chunks(chX, chY, nw, &p);
       const int nwc = p.nwX + p.nwY;
-      if (p.M > 4 || !lookup_kernel(R, p.M, T) || (nwc + 2) * 32 > max_threads_rt(R, p.M, T)) {
+      if (p.M > 6 || !lookup_kernel(R, p.M, T) || (nwc + 2) * 32 > max_threads_rt(R, p.M, T)) {
         if (envW || nwc < nw) break;           // fixed by the caller / no more chunks to spread
         continue;
       }
+      // stages: the fewest that keep >= 72 KB in flight while one stage is in phase A and one waits
+      // for phase B (more in flight measured slower), else as many as fit
       int ns = 0;
-      for (int c = envS ? envS : 8; c >= (envS ? envS : 3); --c)
-        if (stream_smem_layout(R, T, c, nwc, s.ld).total <= smem_max) { ns = c; break; }
+      for (int c = envS ? envS : 3; c <= (envS ? envS : 8); ++c) {
+        if (stream_smem_layout(R, T, c, nwc, s.ld).total > smem_max) break;
+        ns = c;
+        if ((double)(c - 2) * T * rowbytes >= 72.0 * 1024) break;
+      }
       if (!ns) break;
-      // bytes in flight while one stage is in phase A and one waits for phase B
       const double inflight = (double)(ns - 2) * T * rowbytes;
       const double score = (inflight >= 72.0 * 1024 ? 1e9 : inflight) + T * 1e3 - nwc;
       if (score > best_score) {

@@ -20,9 +20,9 @@ static stream_kernel_t kernel_if() {
 stream_kernel_t PPLS_CAT(lookup_kernel_r, PPLS_INST_R)(int M, int T) {
   constexpr int R = PPLS_INST_R;
 #define PPLS_K(m, t) if (M == m && T == t) return kernel_if<R, m, t>();
-  PPLS_K(1, 2) PPLS_K(2, 2) PPLS_K(3, 2) PPLS_K(4, 2)
-  PPLS_K(1, 4) PPLS_K(2, 4) PPLS_K(3, 4) PPLS_K(4, 4)
-  PPLS_K(1, 8) PPLS_K(2, 8) PPLS_K(3, 8) PPLS_K(4, 8)
+  PPLS_K(1, 2) PPLS_K(2, 2) PPLS_K(3, 2) PPLS_K(4, 2) PPLS_K(5, 2) PPLS_K(6, 2)
+  PPLS_K(1, 4) PPLS_K(2, 4) PPLS_K(3, 4) PPLS_K(4, 4) PPLS_K(5, 4) PPLS_K(6, 4)
+  PPLS_K(1, 8) PPLS_K(2, 8) PPLS_K(3, 8) PPLS_K(4, 8) PPLS_K(5, 8) PPLS_K(6, 8)
 #undef PPLS_K
   return nullptr;
 }

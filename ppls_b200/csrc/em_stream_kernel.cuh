@@ -80,10 +80,10 @@ __host__ __device__ constexpr int regs_estimate(int R, int M, int T) { return 8 
 __host__ __device__ constexpr int max_threads_for(int R, int M, int T) {
   int r = regs_estimate(R, M, T);
   if (r > 255) r = 255;
-  int by_regs = (65536 / r) / 32 * 32;
-  int by_m = ((M >= 3 ? 8 : (M == 2 ? 10 : 20)) + 2) * 32;
+  int by_regs = (65536 / r) / 128 * 128;         // ptxas budgets registers for the CTA size rounded up to 128
+  int by_m = ((M >= 4 ? 6 : (M == 3 ? 8 : (M == 2 ? 10 : 20))) + 2) * 32;
   int t = by_regs < by_m ? by_regs : by_m;
-  return t < 96 ? 96 : t;
+  return t < 128 ? 128 : t;
 }
 
 template <int V>
@@ -181,10 +181,14 @@ __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char*
 #pragma unroll
       for (int m = 0; m < CNT; ++m) {
         double x0, x1;
-        if (m == 0) lds128<0>(x0, x1, ra);
-        else if (m == 1) lds128<512>(x0, x1, ra);
-        else if (m == 2) lds128<1024>(x0, x1, ra);
-        else lds128<1536>(x0, x1, ra);
+        switch (m) {
+          case 0: lds128<0>(x0, x1, ra); break;
+          case 1: lds128<512>(x0, x1, ra); break;
+          case 2: lds128<1024>(x0, x1, ra); break;
+          case 3: lds128<1536>(x0, x1, ra); break;
+          case 4: lds128<2048>(x0, x1, ra); break;
+          default: lds128<2560>(x0, x1, ra); break;
+        }
 #pragma unroll
         for (int k = 0; k < R; ++k) {
           acc[m][0][k] = fma(x0, mus[i * R + k], acc[m][0][k]);
@@ -212,10 +216,14 @@ __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char*
 #pragma unroll
       for (int m = 0; m < CNT; ++m) {
         double x0, x1;
-        if (m == 0) lds128<0>(x0, x1, ra);
-        else if (m == 1) lds128<512>(x0, x1, ra);
-        else if (m == 2) lds128<1024>(x0, x1, ra);
-        else lds128<1536>(x0, x1, ra);
+        switch (m) {
+          case 0: lds128<0>(x0, x1, ra); break;
+          case 1: lds128<512>(x0, x1, ra); break;
+          case 2: lds128<1024>(x0, x1, ra); break;
+          case 3: lds128<1536>(x0, x1, ra); break;
+          case 4: lds128<2048>(x0, x1, ra); break;
+          default: lds128<2560>(x0, x1, ra); break;
+        }
 #pragma unroll
         for (int k = 0; k < R; ++k) {
           pf[i * R + k] = fma(x0, w[m][0][k], pf[i * R + k]);
@@ -320,10 +328,14 @@ __global__ void __launch_bounds__(max_threads_for(R, M, T), 1) em_stream_kernel(
     const int cb = isY ? a.cY : a.cX, big = isY ? a.bigY : a.bigX;
     const int cnt = cb + (wg < big ? 1 : 0);
     const int c0 = wg * cb + (wg < big ? wg : big);
-    if (M >= 4 && cnt == 4) compute_warp<R, T, (M >= 4 ? 4 : 1)>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out);
-    else if (M >= 3 && cnt == 3) compute_warp<R, T, (M >= 3 ? 3 : 1)>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out);
-    else if (M >= 2 && cnt == 2) compute_warp<R, T, (M >= 2 ? 2 : 1)>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out);
-    else compute_warp<R, T, 1>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out);
+#define PPLS_CW(c) compute_warp<R, T, (M >= c ? c : 1)>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out)
+    if (M >= 6 && cnt == 6) PPLS_CW(6);
+    else if (M >= 5 && cnt == 5) PPLS_CW(5);
+    else if (M >= 4 && cnt == 4) PPLS_CW(4);
+    else if (M >= 3 && cnt == 3) PPLS_CW(3);
+    else if (M >= 2 && cnt == 2) PPLS_CW(2);
+    else PPLS_CW(1);
+#undef PPLS_CW
   } else if (warp == nwc) {
     // ==================================== reducer warp =======================================
     const int i = lane / R, k = lane - i * R;     // lane (i,k) owns Xw[i,k], Yc[i,k] of the tile

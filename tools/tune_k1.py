@@ -14,13 +14,13 @@ ctx = Context(0)
 truth = synth.truth_params(p, q, r); start = synth.start_params(truth, 1)
 t0 = time.time(); data = Data.synthetic(ctx, N, p, q, truth, seed=1); print("generate", round(time.time() - t0, 2), "s", flush=True)
 grid = []
-for M in (2, 4):
+for Wn in (3, 4, 5, 6, 8):
     for T in (4, 8):
-        for st in (2, 3, 4, 5, 6, 8):
-            grid.append((M, T, 1, st))
+        for st in (3, 4, 5):
+            grid.append((Wn, T, st))
 res = []
-for M, T, ctas, st in grid:
-    os.environ.update(PPLS_K1_M=str(M), PPLS_K1_T=str(T), PPLS_K1_STAGES=str(st))
+for Wn, T, st in grid:
+    os.environ.update(PPLS_K1_WARPS=str(Wn), PPLS_K1_T=str(T), PPLS_K1_STAGES=str(st))
     try:
         f = Fit(data, start, r, EMsteps=40, atol=-np.inf, timing=True, check_every=100)
     except PPLSError as e:
@@ -29,7 +29,7 @@ for M, T, ctas, st in grid:
     ms = (b["stream_ms"] - a["stream_ms"]) / (b["stream_launches"] - a["stream_launches"])
     loop = (b["loop_ms"] - a["loop_ms"]) / 6
     gbs = 8 * N * (p + q) / ms / 1e6
-    res.append((gbs, M, T, ctas, st, ms, loop))
-    print(f"M={M} T={T} ctas={ctas} stages={st}: k1 {ms:.3f} ms  loop/iter {loop:.3f} ms  {gbs:.0f} GB/s", flush=True)
+    res.append((gbs, Wn, T, st, ms, loop))
+    print(f"warps={Wn} T={T} stages={st}: k1 {ms:.3f} ms  loop/iter {loop:.3f} ms  {gbs:.0f} GB/s", flush=True)
 res.sort(reverse=True)
 print("best:", res[:5])
