@@ -60,8 +60,9 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
     const int T = Ts[it];
     if (envT && T != envT) continue;
     if (T * R > 32 || (T * R) % 2) continue;
-    // ~3 chunks per warp, warps in multiples of the 4 SM sub-partitions (measured: tools/tune_k1.py)
-    const int nw0 = envW ? envW : 4 * ((chX + chY + 11) / 12);
+    // up to 6 chunks per warp (fewer, fatter warps = less projection-reduce traffic through shared
+    // memory), warps in multiples of the 4 SM sub-partitions (measured: tools/tune_k1.py)
+    const int nw0 = envW ? envW : 4 * ((chX + chY + 23) / 24);
     for (int nw = nw0; nw <= 30; ++nw) {
       StreamPlan p{};
       split_chunks(chX, chY, nw, &p);

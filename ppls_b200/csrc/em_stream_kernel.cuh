@@ -47,16 +47,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   do {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        : "=r"(ok) : "r"(bar), "r"(parity), "r"(0x989680u) /* suspend-time hint (ns): sleep, don't spin */ : "memory");
   } while (!ok);
 }
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
-constexpr int RP2 = 33;          // pitch (double2 units) of one value-pair row of the transpose buffer
 constexpr int RING_PAD = 512;    // zeroed bytes after the ring: lanes of a partial last chunk over-read it
 
 struct StreamArgs {
@@ -91,6 +90,10 @@ struct RedShape {
   static constexpr int NP = V / 2;                                   // value pairs
   static constexpr int H = (NP * 16 <= 32) ? 16 : (NP * 8 <= 32) ? 8 : (NP * 4 <= 32) ? 4 : (NP * 2 <= 32) ? 2 : 1;
   static constexpr int SEG = 32 / H;                                 // lanes each reader adds up
+  // pitch (double2 units) of one value-pair row of the transpose buffer.  LDS.128 is served in
+  // groups of 8 lanes; a group holds 8/H value pairs x H lane groups, so pitch = H (mod 8) makes
+  // its 8 addresses hit 8 different 16-byte bank groups.
+  static constexpr int RP2 = 32 + (H < 8 ? H : 1);
 };
 
 // 16-byte shared-memory load at [addr + IMM] (32-bit shared address, immediate offset).
@@ -98,6 +101,12 @@ struct RedShape {
 template <int IMM>
 __device__ __forceinline__ void lds128(double& a, double& b, uint32_t addr) {
   asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(a), "=d"(b) : "r"(addr), "n"(IMM));
+}
+
+__host__ __device__ constexpr int red_pitch(int V) {
+  const int NP = V / 2;
+  const int H = (NP * 16 <= 32) ? 16 : (NP * 8 <= 32) ? 8 : (NP * 4 <= 32) ? 4 : (NP * 2 <= 32) ? 2 : 1;
+  return 32 + (H < 8 ? H : 1);
 }
 
 struct StreamSmem {            // byte offsets of the dynamic shared-memory carve-up
@@ -108,7 +117,7 @@ __host__ __device__ inline StreamSmem stream_smem_layout(int R, int T, int nstag
   StreamSmem s;
   uint32_t o = 0;
   s.ring = o; o += (uint32_t)T * ld * 8u * nstage + RING_PAD;
-  s.red = o;  o += (uint32_t)nwc * NP * RP2 * 16u;
+  s.red = o;  o += (uint32_t)nwc * NP * red_pitch(V) * 16u;
   s.wsum = o; o += 2u * nwc * V * 8u;
   s.mu = o;   o += 4u * V * 8u;           // [buf][T/U][V]
   s.xy = o;   o += 2u * V * 8u;           // reducer scratch: Xw, Yc of the tile
@@ -128,7 +137,8 @@ __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char*
                                              double* out) {
   constexpr int V = T * R;
   using RS = RedShape<V>;
-  constexpr int NP = RS::NP, H = RS::H, SEG = RS::SEG;
+  constexpr int NP = RS::NP, H = RS::H, SEG = RS::SEG, RP2 = RS::RP2;
+  static_assert(RP2 == red_pitch(V), "pitch");
   const uint32_t rowbytes = (uint32_t)a.ld * 8u;
   const uint32_t stage_bytes = rowbytes * T;
   const uint32_t ring_bytes = stage_bytes * (uint32_t)a.nstage;
