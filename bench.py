@@ -198,9 +198,19 @@ def run_ours(args):
                "seconds_sample": e_s, "loglik_last": float(res["loglik"][-1])}
         del Xp, Yp
     data.close()
+    # orderly teardown on EVERY rank (communicators are collective objects), then leave without
+    # running interpreter-exit destructors: a rank that lingers in them hangs torchrun
+    def leave():
+        barrier()
+        ctx.close()
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
 
     if rank != 0:
-        return
+        leave()
     peak, peak_src = measured_peak()
     bytes_pass = 8 * n_local * (p + q)                    # algorithmic bytes one launch reads (this rank)
     achieved = bytes_pass / (k1_ms * 1e-3) / 1e9
@@ -231,8 +241,7 @@ def run_ours(args):
     if not args.no_cpu and world == 1:
         out["cpu_baseline"] = cpu_baseline(args, truth, start, N, p, q, r, K)
     print(json.dumps(out), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    leave()
 
 
 def cpu_reference_time(X, Y, start, steps):
