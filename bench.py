@@ -27,6 +27,7 @@ WORKLOADS = {
     # name: (N, p, q, r)   -- BASELINE.json configs
     "c1": (500, 20, 10, 2),
     "c2": (1_000_000, 500, 100, 3),
+    "c4": (2000, 50000, 1000, 5),
     "c3": (10_000_000, 1000, 200, 3),
     "c5shape": (100_000, 200, 50, 2),
 }

@@ -15,6 +15,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler",
 UNITS = {
     "em_stream.cu": [],
     **{f"em_stream_inst.cu@r{r}": [f"-DPPLS_INST_R={r}"] for r in range(1, 9)},
+    "em_wide.cu": [],
     "em_update.cu": ["-fmad=false"],
     "data.cu": ["-fmad=false"],
     "capi.cu": [],

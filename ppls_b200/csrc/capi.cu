@@ -372,6 +372,10 @@ struct ppls_fit {
   const ppls_data* data = nullptr;
   ppls_opts opts{};
   StreamPlan plan{};
+  bool wide = false;             // two-pass wide-row path (em_wide.cu) instead of the fused kernel
+  WidePlan wplan{};
+  WideOffsets woff{};
+  double* wide_ws = nullptr;
   int R = 0;
   int64_t veclen = 0;
   double *L = nullptr, *Lscratch = nullptr, *partials = nullptr, *momvec = nullptr, *trace = nullptr;
@@ -390,7 +394,7 @@ static void fit_free(ppls_fit* f) {
   if (f->ctx) cudaSetDevice(f->ctx->device);
   for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto e : f->ev_free) cudaEventDestroy(e);
-  cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
+  cudaFree(f->wide_ws); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
   cudaFree(f->st);
   if (f->st_host) cudaFreeHost(f->st_host);
   delete f;
@@ -415,13 +419,22 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   if (!f) return fail(PPLS_E_OOM, "host allocation failed");
   f->ctx = ctx; f->data = d; f->opts = *opts; f->R = R;
   const char* why = "";
-  cudaError_t e = plan_stream(d->s, R, ctx->sm_count, &f->plan, &why);
-  if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_UNSUPPORTED, std::string("streaming-kernel plan: ") + why); }
+  const char* force_wide = getenv("PPLS_FORCE_WIDE");
+  cudaError_t e = (force_wide && atoi(force_wide)) ? cudaErrorInvalidValue : plan_stream(d->s, R, ctx->sm_count, &f->plan, &why);
+  if (e != cudaSuccess) {
+    // the row does not fit the fused kernel's shared-memory tile: two-pass wide-row path
+    const std::string why1 = why;
+    e = plan_wide(d->s, R, ctx->sm_count, &f->wplan, &why);
+    if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_UNSUPPORTED, "streaming-kernel plan: " + why1 + "; " + why); }
+    f->wide = true;
+  }
   f->veclen = momvec_len(d->s.ld, R);
   const size_t Lbytes = (size_t)d->s.ld * R * sizeof(double);
   e = cudaMalloc(&f->L, Lbytes);
   if (e == cudaSuccess) e = cudaMalloc(&f->Lscratch, Lbytes);
-  if (e == cudaSuccess) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
+  if (e == cudaSuccess && !f->wide) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
+  if (e == cudaSuccess && f->wide)
+    e = cudaMalloc(&f->wide_ws, wide_workspace_doubles(d->s, f->wplan, &f->woff) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->momvec, (size_t)f->veclen * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->trace, (size_t)(opts->max_steps + 1) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->st, sizeof(FitState));
@@ -442,7 +455,7 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // L (host vector) must outlive the copy
   if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_CUDA, std::string("fit setup: ") + cudaGetErrorString(e)); }
   f->tm.kernel_launches = 1;
-  f->tm.bytes_per_pass = (int64_t)8 * d->s.n * ((int64_t)d->s.p + d->s.q);
+  f->tm.bytes_per_pass = (int64_t)(f->wide ? 16 : 8) * d->s.n * ((int64_t)d->s.p + d->s.q);
   *out = f;
   return PPLS_OK;
 }
@@ -487,9 +500,17 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
     if (f->passes > f->opts.max_steps) break;
     cudaEvent_t a = nullptr, b = nullptr;
     if (timing) { a = fit_event(f); b = fit_event(f); cudaEventRecord(a, ctx->stream); }
-    cudaError_t e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream);
-    if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
-    if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
+    cudaError_t e;
+    if (f->wide) {
+      e = launch_wide_project(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, ctx->stream);
+      if (e == cudaSuccess) e = launch_wide_accum(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, f->momvec, ctx->stream);
+      if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+      f->tm.kernel_launches += 3;      // 5 launches in this branch, 2 in the other; +3 more below
+    } else {
+      e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream);
+      if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+      if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
+    }
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
     rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
     if (rc) return rc;
@@ -558,7 +579,18 @@ extern "C" int ppls_fit_result(ppls_fit* f, ppls_params* est, double* loglik, in
     m[3 * R] = h->Cee; m[3 * R + 1] = h->Cff;
     for (int e = 0; e < R * R; ++e) m[3 * R + 2 + e] = h->Chh[e];
   }
-  if (mu_T) {
+  if (mu_T && f->wide) {
+    // the last pass left mu_T, mu_U of the final parameters in the workspace ([2][n][R], row-major)
+    const int64_t npad = wide_npad(s.n);
+    std::vector<double> mu((size_t)2 * npad * R);
+    CU(cudaMemcpyAsync(mu.data(), f->wide_ws + f->woff.mu, mu.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int64_t i = 0; i < s.n; ++i)
+      for (int k = 0; k < R; ++k) {
+        mu_T[i + (size_t)k * s.n] = mu[(size_t)i * R + k];
+        mu_U[i + (size_t)k * s.n] = mu[(size_t)(npad + i) * R + k];
+      }
+  } else if (mu_T) {
     // One more pass with the final parameters writes the posterior means (EM_W_multi.R:802).
     double* dmu = nullptr;
     CU(cudaMalloc(&dmu, (size_t)2 * s.n * R * sizeof(double)));

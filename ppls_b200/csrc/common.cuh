@@ -63,6 +63,21 @@ struct StreamPlan {          // how K1 is launched for one shape
   int64_t ntiles;
 };
 
+struct WidePlan {            // two-pass wide-row path (em_wide.cu)
+  int R, NCH, nstage;
+  int scX, scY, nslabX, nslabY;      // slab widths (columns) and counts
+  int nrg, rows_per_rg, nblk_mu;
+};
+struct WideOffsets { size_t ppart, proj, mu, gpart, gram; };   // offsets (doubles) into the wide workspace
+cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, const char** why);
+int64_t wide_npad(int64_t n);
+size_t wide_workspace_doubles(const DataShape& s, const WidePlan& w, WideOffsets* o);
+cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const double* D, const double* L,
+                                const FitState* st, double* ws, const WideOffsets& o, cudaStream_t stream);
+cudaError_t launch_wide_accum(const WidePlan& w, const DataShape& s, const double* D, const double* L,
+                              const FitState* st, double* ws, const WideOffsets& o, double* momvec,
+                              cudaStream_t stream);
+
 cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* plan, const char** why);
 // One data pass: per-CTA partials -> `partials` [grid][momvec_len].
 cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const double* D,

@@ -131,3 +131,34 @@ def test_error_behaviour(ctx):
     with pytest.raises(ValueError):
         Data.from_host(ctx, np.zeros((5, 3)), np.zeros((6, 2)))
     d.close()
+
+
+@pytest.mark.parametrize("name", ["c1_wellcond_1000", "r5_odd_shapes", "r3_qr", "r8_max", "r1_p_lt_q", "r3_wide_row"])
+def test_golden_through_the_wide_path(ctx, name, monkeypatch):
+    """The two-pass wide-row path (em_wide.cu) forced on the golden cases: same bar as the fused kernel."""
+    monkeypatch.setenv("PPLS_FORCE_WIDE", "1")
+    g = load_golden(name)
+    res = _run(ctx, g["X"], g["Y"], init_of(g), int(g["r"]), int(g["EMsteps"]), float(g["atol"]), str(g["type"]))
+    _compare(res, g, name)
+
+
+@pytest.mark.parametrize("shape,steps", [((300, 6000, 500, 5), 6), ((1037, 9001, 33, 3), 4), ((2000, 50000, 1000, 5), 3)])
+def test_wide_shapes_vs_fused_oracle(ctx, oracle_lib, shape, steps):
+    """Rows too wide for the fused kernel's tile (incl. BASELINE config 4 at full size: N=2000, p=50000,
+    q=1000, r=5) take the wide path by themselves; compared with the CPU restatement on the exported data."""
+    from oracle import ppls_fused as F
+    from ppls_b200 import Data, Fit, synth
+    N, p, q, r = shape
+    truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
+    d = Data.synthetic(ctx, N, p, q, truth, seed=777)
+    st = synth.start_params(truth, 3)
+    f = Fit(d, st, r, steps, -np.inf, "SVD")
+    f.run()
+    res = f.result()
+    X, Y = d.export()
+    o = F.fused_loop(oracle_lib, X, Y, st["W"], st["C"], st["B"], st["sigE"], st["sigF"], st["sigH"], st["sigT"],
+                     EMsteps=steps, atol=-np.inf)
+    assert relmax(res["loglik"], o["loglik"]) < 1e-10
+    for k in ("W", "C", "B", "sigT", "Ctt", "Cuu", "Cut", "Chh", "mu_T", "mu_U"):
+        assert relmax(res[k], o[k]) < TOL_PARAM, k
+    f.close(); d.close()
