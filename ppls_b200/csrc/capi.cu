@@ -376,6 +376,7 @@ struct ppls_fit {
   WidePlan wplan{};
   WideOffsets woff{};
   double* wide_ws = nullptr;
+  double* upd_scratch = nullptr; // Gram partials of the grid update kernel
   int R = 0;
   int64_t veclen = 0;
   double *L = nullptr, *Lscratch = nullptr, *partials = nullptr, *momvec = nullptr, *trace = nullptr;
@@ -394,7 +395,7 @@ static void fit_free(ppls_fit* f) {
   if (f->ctx) cudaSetDevice(f->ctx->device);
   for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto e : f->ev_free) cudaEventDestroy(e);
-  cudaFree(f->wide_ws); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
+  cudaFree(f->wide_ws); cudaFree(f->upd_scratch); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
   cudaFree(f->st);
   if (f->st_host) cudaFreeHost(f->st_host);
   delete f;
@@ -436,6 +437,8 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   if (e == cudaSuccess && f->wide)
     e = cudaMalloc(&f->wide_ws, wide_workspace_doubles(d->s, f->wplan, &f->woff) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->momvec, (size_t)f->veclen * sizeof(double));
+  if (e == cudaSuccess && !(getenv("PPLS_K2_SINGLE") && atoi(getenv("PPLS_K2_SINGLE"))))
+    e = cudaMalloc(&f->upd_scratch, update_grid_scratch_doubles(d->s.ld, R) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->trace, (size_t)(opts->max_steps + 1) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->st, sizeof(FitState));
   if (e == cudaSuccess) e = cudaMallocHost(&f->st_host, sizeof(FitState));
@@ -514,7 +517,7 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
     rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
     if (rc) return rc;
-    e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, ctx->stream);
+    e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
     f->tm.kernel_launches += 3;
     f->passes += 1;

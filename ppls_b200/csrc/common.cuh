@@ -87,8 +87,11 @@ cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const d
 cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t len, double* momvec,
                                    const FitState* st, cudaStream_t stream);
 // K2: loglik, E-step moments, break rule, M-step, next coefficients.
+// orth_type SVD + gscratch != null: the grid (cooperative) kernel; else the single-CTA kernel.
 cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
-                             FitState* st, double* trace, cudaStream_t stream);
+                             FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream);
+int update_grid_blocks(int ld);
+size_t update_grid_scratch_doubles(int ld, int R);
 // Prepare coefficients + Gram matrices for the start state (pass 0).
 cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream);
 

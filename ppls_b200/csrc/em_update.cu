@@ -12,17 +12,41 @@
 //   coefficients of mu_T, mu_U for the next pass (:691-694 with the diagonal algebra collapsed)
 #include "common.cuh"
 #include <math.h>
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 namespace ppls {
 
 constexpr int UPD_THREADS = 512;
 constexpr int UPD_WARPS = UPD_THREADS / 32;
 
-// Closed-form inverse coefficients.  squared_g = false: as Expect_M evaluates them (:672-680);
-// squared_g = true: as logl_W does (:312-320; g is stored as a square root and re-squared).
+// Integer powers with one rounding (error-free products + a correction term): what a correctly
+// rounded pow(x, n) -- R's and numpy's `^` / `**` go through libm pow -- returns in all but
+// near-tie cases, at a few flops instead of a few hundred.
+__device__ __forceinline__ double pow2_err(double x, double* lo) { const double h = x * x; *lo = fma(x, x, -h); return h; }
+__device__ __forceinline__ double pow4(double x) {
+  double ae; const double a = pow2_err(x, &ae);
+  const double b = a * a, be = fma(a, a, -b) + 2.0 * a * ae;
+  return b + be;
+}
+__device__ __forceinline__ double pow6(double x) {
+  double ae; const double a = pow2_err(x, &ae);
+  const double b = a * a, be = fma(a, a, -b) + 2.0 * a * ae;
+  const double c = b * a, ce = fma(b, a, -c) + b * ae + be * a;
+  return c + ce;
+}
+__device__ __forceinline__ double powm2(double x) {      // x^-2
+  double e; const double s2 = pow2_err(x, &e);
+  const double r = 1.0 / s2;
+  const double res = fma(-r, s2, 1.0) - r * e;
+  return fma(r, res, r);
+}
+
+// Closed-form inverse coefficients.  sqrt_g = false: as Expect_M evaluates them (:672-680);
+// sqrt_g = true: as logl_W does (:312-320; g is stored as a square root and re-squared).
 __device__ void closed_form_coef(bool sqrt_g, double b, double t, double sE, double sF, double sH,
                                  double* c1, double* c2, double* c3, double* Kc_out) {
-  const double t2 = t * t, t4 = pow(t, 4.0), t6 = pow(t, 6.0), b2 = b * b;
+  const double t2 = t * t, t4 = pow4(t), t6 = pow6(t), b2 = b * b;
   const double sE2 = sE * sE, sF2 = sF * sF, sH2 = sH * sH;
   double g = t2 * b2 + sH2;
   if (sqrt_g) { g = sqrt(g); g = g * g; }
@@ -37,21 +61,22 @@ __device__ void closed_form_coef(bool sqrt_g, double b, double t, double sE, dou
   *Kc_out = Kc;
 }
 
-// Coefficients of the posterior means for the streaming kernel (EM_W_multi.R:691-694):
+// Coefficients of the posterior means for the streaming kernel (EM_W_multi.R:691-694), component k:
 //   mu_T[:,k] = aT Xw[:,k] + bT Yc[:,k],  mu_U[:,k] = aU Xw[:,k] + bU Yc[:,k]
-__device__ void posterior_coef(FitState* st, int R) {
+__device__ void posterior_coef_k(FitState* st, int k) {
   const double sE = st->sigE, sF = st->sigF, sH = st->sigH;
-  const double isE2 = pow(sE, -2.0), isF2 = pow(sF, -2.0);
-  for (int k = 0; k < R; ++k) {
-    const double b = st->b[k], t = st->t[k];
-    double c1, c2, c3, Kc;
-    closed_form_coef(false, b, t, sE, sF, sH, &c1, &c2, &c3, &Kc);
-    const double t2 = t * t, varU = t2 * (b * b) + sH * sH;
-    st->aT[k] = isE2 * t2 - c1 * t2 - c2 * t2 * b;
-    st->bT[k] = isF2 * (t2 * b) - c2 * t2 - c3 * b * t2;
-    st->aU[k] = isE2 * (t2 * b) - c1 * t2 * b - c2 * varU;
-    st->bU[k] = isF2 * varU - c2 * t2 * b - c3 * varU;
-  }
+  const double isE2 = powm2(sE), isF2 = powm2(sF);
+  const double b = st->b[k], t = st->t[k];
+  double c1, c2, c3, Kc;
+  closed_form_coef(false, b, t, sE, sF, sH, &c1, &c2, &c3, &Kc);
+  const double t2 = t * t, varU = t2 * (b * b) + sH * sH;
+  st->aT[k] = isE2 * t2 - c1 * t2 - c2 * t2 * b;
+  st->bT[k] = isF2 * (t2 * b) - c2 * t2 - c3 * b * t2;
+  st->aU[k] = isE2 * (t2 * b) - c1 * t2 * b - c2 * varU;
+  st->bU[k] = isF2 * varU - c2 * t2 * b - c3 * varU;
+}
+__device__ void posterior_coef(FitState* st, int R) {
+  for (int k = 0; k < R; ++k) posterior_coef_k(st, k);
 }
 
 // ---- deterministic block reductions (fixed thread partition, fixed tree) -------------------
@@ -254,16 +279,21 @@ struct UpdateArgs {
   double* Lscratch;       // [ld][R] work space (QR)
   FitState* st;
   double* trace;          // [max_steps]
+  double* gscratch;       // grid kernel: [3 phases][row blocks][2 matrices][R*R] Gram partials
   int32_t p, q, p2, q2, ld;
 };
 
 __device__ inline bool finite_d(double x) { return isfinite(x); }
 
-// Scalar part (one thread): loglik(theta_k), E-step moments, break rule, M-step scalars.
-// Returns 1 when the run ends with this pass.
+// Scalar part, executed by ONE FULL WARP (lane k < R owns component k; every sum over components is
+// added by lane 0 in component order, as the sequential reference does): loglik(theta_k), E-step
+// moments, break rule, M-step scalars.  Returns 1 (on all lanes) when the run ends with this pass.
+struct ScalarShared { double c1[MAXR], c2[MAXR], c3[MAXR], tl[MAXR], lt[MAXR], lk[MAXR]; int done; };
+
 template <int R>
-__device__ int update_scalars(const UpdateArgs& a) {
+__device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
   FitState* st = a.st;
+  const int lane = threadIdx.x & 31;
   const double* Gxx = a.momvec + (size_t)a.ld * R;
   const double* Gxy = Gxx + R * R;
   const double* Gyy = Gxy + R * R;
@@ -271,38 +301,36 @@ __device__ int update_scalars(const UpdateArgs& a) {
   const double sE = st->sigE, sF = st->sigF, sH = st->sigH;
   const double sE2 = sE * sE, sF2 = sF * sF, sH2 = sH * sH;
   const int k_pass = st->pass;
+  const int k = lane;
 
   // ---- log-likelihood at theta_k: logl_W :312-320 + loglC_fast loglC.cpp:331-336 ----------
-  {
-    double Logdiag = 0.0, sumT = 0.0, sumK = 0.0;
+  if (k < R) {
+    double c1, c2, c3, Kc;
+    closed_form_coef(true, st->b[k], st->t[k], sE, sF, sH, &c1, &c2, &c3, &Kc);
+    sh->lt[k] = log(sE2 + st->t[k] * st->t[k]);
+    sh->lk[k] = log(sF2 + Kc);
+    sh->tl[k] = -c1 * Gxx[k * R + k] - 2.0 * c2 * Gxy[k * R + k] - c3 * Gyy[k * R + k];
+  }
+  __syncwarp();
+  if (lane == 0) {
+    double sumT = 0.0, sumK = 0.0;
     double traceL = 1.0 / sE2 * st->ssqX + 1.0 / sF2 * st->ssqY;
-    for (int k = 0; k < R; ++k) {
-      double c1, c2, c3, Kc;
-      closed_form_coef(true, st->b[k], st->t[k], sE, sF, sH, &c1, &c2, &c3, &Kc);
-      sumT += log(sE2 + st->t[k] * st->t[k]);
-      sumK += log(sF2 + Kc);
-      traceL += -c1 * Gxx[k * R + k] - 2.0 * c2 * Gxy[k * R + k] - c3 * Gyy[k * R + k];
-    }
-    Logdiag = sumT + (p - R) * log(sE2) + sumK + (q - R) * log(sF2);
+    for (int j = 0; j < R; ++j) { sumT += sh->lt[j]; sumK += sh->lk[j]; traceL += sh->tl[j]; }
+    const double Logdiag = sumT + (p - R) * log(sE2) + sumK + (q - R) * log(sF2);
     const double ll = -0.5 * N * (p + q) * log(2.0 * 3.14159265358979323846) - 0.5 * N * Logdiag - 0.5 * traceL;
     st->loglik_last = ll;
     if (k_pass >= 1) a.trace[k_pass - 1] = ll;
   }
 
   // ---- E-step second moments at theta_k: Expect_M :672-712 ----------------------------------
-  const double isE2 = pow(sE, -2.0), isF2 = pow(sF, -2.0);
-  const double sE4 = pow(sE, 4.0), sF4 = pow(sF, 4.0), sH4 = pow(sH, 4.0);
-  double c1v[R], c2v[R], c3v[R];
-  double sumc1 = 0.0, sumc3 = 0.0;
-  for (int k = 0; k < R; ++k) {
-    double Kc;
-    closed_form_coef(false, st->b[k], st->t[k], sE, sF, sH, &c1v[k], &c2v[k], &c3v[k], &Kc);
-    sumc1 += c1v[k]; sumc3 += c3v[k];
-  }
-  for (int k = 0; k < R; ++k) {
-    const double b = st->b[k], t = st->t[k], t2 = t * t, t4 = pow(t, 4.0), b2 = b * b;
+  const double isE2 = powm2(sE), isF2 = powm2(sF);
+  const double sE4 = pow4(sE), sF4 = pow4(sF), sH4 = pow4(sH);
+  if (k < R) {
+    double c1, c2, c3, Kc;
+    closed_form_coef(false, st->b[k], st->t[k], sE, sF, sH, &c1, &c2, &c3, &Kc);
+    sh->c1[k] = c1; sh->c2[k] = c2; sh->c3[k] = c3;
+    const double b = st->b[k], t = st->t[k], t2 = t * t, t4 = pow4(t), b2 = b * b;
     const double varU = t2 * b2 + sH2;
-    const double c1 = c1v[k], c2 = c2v[k], c3 = c3v[k];
     const double aT = st->aT[k], bT = st->bT[k], aU = st->aU[k], bU = st->bU[k];
     const double xx = Gxx[k * R + k], xy = Gxy[k * R + k], yy = Gyy[k * R + k];
     const double mTT = aT * aT * xx + 2.0 * aT * bT * xy + bT * bT * yy;     // crossprod(mu_T)[k,k]
@@ -317,73 +345,90 @@ __device__ int update_scalars(const UpdateArgs& a) {
     st->Cuu[k] = fabs(Cuu);
     st->Cut[k] = Cut;
   }
-  // residual sums of squares, algebraically from the Gram matrices (exact for any W, C):
-  //   mu_E = X - M W',  M = Xw diag(sE2 c1) + Yc diag(sE2 c2)                      (:703)
-  //   ||mu_E||^2 = ||X||^2 - 2 tr(M'Xw) + tr(M'M W'W)
-  double ssqE = st->ssqX, ssqF = st->ssqY;
-  for (int k = 0; k < R; ++k) {
-    const double Ak = sE2 * c1v[k], Bk = sE2 * c2v[k];       // on Xw, on Yc
-    const double Fk = sF2 * c3v[k], Hk = sF2 * c2v[k];       // mu_F: on Yc, on Xw     (:708)
-    ssqE -= 2.0 * (Ak * Gxx[k * R + k] + Bk * Gxy[k * R + k]);
-    ssqF -= 2.0 * (Fk * Gyy[k * R + k] + Hk * Gxy[k * R + k]);
-    for (int l = 0; l < R; ++l) {
-      const double Al = sE2 * c1v[l], Bl = sE2 * c2v[l];
-      const double Fl = sF2 * c3v[l], Hl = sF2 * c2v[l];
-      const double MtM = Ak * Al * Gxx[k * R + l] + Ak * Bl * Gxy[k * R + l] + Bk * Al * Gxy[l * R + k] +
-                         Bk * Bl * Gyy[k * R + l];
-      const double MtMf = Fk * Fl * Gyy[k * R + l] + Fk * Hl * Gxy[l * R + k] + Hk * Fl * Gxy[k * R + l] +
-                          Hk * Hl * Gxx[k * R + l];
-      ssqE += MtM * st->WtW[l * R + k];
-      ssqF += MtMf * st->CtC[l * R + k];
-    }
-  }
-  const double Cee = (p * sE2 - p * sE2 + sE4 * sumc1 + ssqE / N) / p;     // :706
-  const double Cff = (q * sF2 - q * sF2 + sF4 * sumc3 + ssqF / N) / q;     // :709
-  st->Cee = Cee; st->Cff = Cff;
+  __syncwarp();
+  const double* c1v = sh->c1; const double* c2v = sh->c2; const double* c3v = sh->c3;
   // Chh (:711-712): mu_H[:,k] = hX_k Xw[:,k] + hY_k Yc[:,k]; full r x r, abs, not masked
-  double trChh = 0.0;
-  for (int k = 0; k < R; ++k)
-    for (int l = 0; l < R; ++l) {
-      const double hXk = -sH2 * c2v[k], hYk = isF2 * sH2 - sH2 * c3v[k];
-      const double hXl = -sH2 * c2v[l], hYl = isF2 * sH2 - sH2 * c3v[l];
-      double v = (hXk * hXl * Gxx[k * R + l] + hXk * hYl * Gxy[k * R + l] + hYk * hXl * Gxy[l * R + k] +
-                  hYk * hYl * Gyy[k * R + l]) / N;
-      if (k == l) v += (sH2 - sH4 / sF2) + sH4 * c3v[k];
-      v = fabs(v);
-      st->Chh[k + l * R] = v;
-      if (k == l) trChh += v;
+  for (int e = lane; e < R * R; e += 32) {
+    const int kk = e / R, l = e - kk * R;
+    const double hXk = -sH2 * c2v[kk], hYk = isF2 * sH2 - sH2 * c3v[kk];
+    const double hXl = -sH2 * c2v[l], hYl = isF2 * sH2 - sH2 * c3v[l];
+    double v = (hXk * hXl * Gxx[kk * R + l] + hXk * hYl * Gxy[kk * R + l] + hYk * hXl * Gxy[l * R + kk] +
+                hYk * hYl * Gyy[kk * R + l]) / N;
+    if (kk == l) v += (sH2 - sH4 / sF2) + sH4 * c3v[kk];
+    st->Chh[kk + l * R] = fabs(v);
+  }
+  __syncwarp();
+  if (lane == 0) {
+    // residual sums of squares, algebraically from the Gram matrices (exact for any W, C):
+    //   mu_E = X - M W',  M = Xw diag(sE2 c1) + Yc diag(sE2 c2)                      (:703)
+    //   ||mu_E||^2 = ||X||^2 - 2 tr(M'Xw) + tr(M'M W'W)
+    double sumc1 = 0.0, sumc3 = 0.0;
+    for (int j = 0; j < R; ++j) { sumc1 += c1v[j]; sumc3 += c3v[j]; }
+    double ssqE = st->ssqX, ssqF = st->ssqY;
+    for (int kk = 0; kk < R; ++kk) {
+      const double Ak = sE2 * c1v[kk], Bk = sE2 * c2v[kk];       // on Xw, on Yc
+      const double Fk = sF2 * c3v[kk], Hk = sF2 * c2v[kk];       // mu_F: on Yc, on Xw     (:708)
+      ssqE -= 2.0 * (Ak * Gxx[kk * R + kk] + Bk * Gxy[kk * R + kk]);
+      ssqF -= 2.0 * (Fk * Gyy[kk * R + kk] + Hk * Gxy[kk * R + kk]);
+      for (int l = 0; l < R; ++l) {
+        const double Al = sE2 * c1v[l], Bl = sE2 * c2v[l];
+        const double Fl = sF2 * c3v[l], Hl = sF2 * c2v[l];
+        const double MtM = Ak * Al * Gxx[kk * R + l] + Ak * Bl * Gxy[kk * R + l] + Bk * Al * Gxy[l * R + kk] +
+                           Bk * Bl * Gyy[kk * R + l];
+        const double MtMf = Fk * Fl * Gyy[kk * R + l] + Fk * Hl * Gxy[l * R + kk] + Hk * Fl * Gxy[kk * R + l] +
+                            Hk * Hl * Gxx[kk * R + l];
+        ssqE += MtM * st->WtW[l * R + kk];
+        ssqF += MtMf * st->CtC[l * R + kk];
+      }
     }
-
-  // ---- break rule (:792) / EMsteps exhausted -------------------------------------------------
-  bool done = (k_pass >= st->max_steps);
-  if (k_pass >= 2 && (a.trace[k_pass - 1] - a.trace[k_pass - 2]) < st->atol) done = true;
-  if (!finite_d(st->loglik_last)) { st->status = PPLS_E_NONFINITE; done = true; }
-  if (done) { st->done = 1; st->steps_done = k_pass; return 1; }
+    const double Cee = (p * sE2 - p * sE2 + sE4 * sumc1 + ssqE / N) / p;     // :706
+    const double Cff = (q * sF2 - q * sF2 + sF4 * sumc3 + ssqF / N) / q;     // :709
+    st->Cee = Cee; st->Cff = Cff;
+    // ---- break rule (:792) / EMsteps exhausted -------------------------------------------------
+    bool done = (k_pass >= st->max_steps);
+    if (k_pass >= 2 && (a.trace[k_pass - 1] - a.trace[k_pass - 2]) < st->atol) done = true;
+    if (!finite_d(st->loglik_last)) { st->status = PPLS_E_NONFINITE; done = true; }
+    if (done) st->steps_done = k_pass;                   // the CALLER raises st->done (see the grid kernel)
+    sh->done = done ? 1 : 0;
+  }
+  __syncwarp();
+  if (sh->done) return 1;
 
   // ---- M-step scalars (:734-738) -> theta_{k+1} -----------------------------------------------
   bool ok = true;
-  for (int k = 0; k < R; ++k) {
+  if (k < R) {
     const double bn = st->Cut[k] * (1.0 / st->Ctt[k]);       // Cut %*% solve(Ctt) * I
     const double tn = sqrt(st->Ctt[k]);
     st->b[k] = bn; st->t[k] = tn;
-    ok = ok && finite_d(bn) && finite_d(tn);
+    ok = finite_d(bn) && finite_d(tn);
   }
-  st->sigE = sqrt(Cee); st->sigF = sqrt(Cff); st->sigH = sqrt(trChh / R);
-  ok = ok && finite_d(st->sigE) && finite_d(st->sigF) && finite_d(st->sigH);
-  posterior_coef(st, R);
-  for (int k = 0; k < R; ++k) ok = ok && finite_d(st->aT[k]) && finite_d(st->bT[k]) && finite_d(st->aU[k]) && finite_d(st->bU[k]);
-  st->pass = k_pass + 1;
-  if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = k_pass; return 1; }
-  return 0;
+  if (lane == 0) {
+    double trChh = 0.0;
+    for (int j = 0; j < R; ++j) trChh += st->Chh[j + j * R];
+    st->sigE = sqrt(st->Cee); st->sigF = sqrt(st->Cff); st->sigH = sqrt(trChh / R);
+    ok = ok && finite_d(st->sigE) && finite_d(st->sigF) && finite_d(st->sigH);
+  }
+  __syncwarp();
+  if (k < R) {
+    posterior_coef_k(st, k);
+    ok = ok && finite_d(st->aT[k]) && finite_d(st->bT[k]) && finite_d(st->aU[k]) && finite_d(st->bU[k]);
+  }
+  ok = __all_sync(0xffffffffu, ok);
+  if (lane == 0) {
+    st->pass = k_pass + 1;
+    if (!ok) { st->status = PPLS_E_NONFINITE; st->steps_done = k_pass; }
+  }
+  return ok ? 0 : 1;
 }
 
 template <int R>
 __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateArgs a) {
   __shared__ double scratch[UPD_WARPS * 36], S[R * R], Mat[R * R];
   __shared__ int s_done;
+  __shared__ ScalarShared ssh;
   FitState* st = a.st;
   if (st->done) return;
-  if (threadIdx.x == 0) s_done = update_scalars<R>(a);
+  if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) { s_done = d; if (d) st->done = 1; } }
   __syncthreads();
   if (s_done) return;
   // ---- loadings: W = orth(t(X) mu_T), C = orth(t(Y) mu_U)  (:732-733) ----------------------------
@@ -412,6 +457,177 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateA
   }
 }
 
+
+// ---- grid version of K2 (type = "SVD"): the O((p+q) r^2) work spread over row blocks ---------------
+// Block 0 does the scalar part; blocks 1..nb own rows j = (b-1)*GT + tid (+ nb*GT ...) of [G1; G2].
+// Three grid-wide syncs separate: Gram of G | G (G'G)^{-1/2} and its Gram | Newton-Schulz polish and
+// the Gram of the new loadings.  Partial Grams are added in block order: run-to-run deterministic.
+constexpr int GT = 256, GW = GT / 32;
+
+template <int R>
+__device__ void grid_partial_gram(const double* A, int row_lo, int row_hi, int rb, int nb, double* dst /*[R*R]*/,
+                                  double* scratch /*[GW*36]*/) {
+  constexpr int NV = R * (R + 1) / 2;
+  double v[NV];
+#pragma unroll
+  for (int e = 0; e < NV; ++e) v[e] = 0.0;
+  for (int j = row_lo + rb * GT + threadIdx.x; j < row_hi; j += nb * GT) {
+    double row[R];
+#pragma unroll
+    for (int k = 0; k < R; ++k) row[k] = A[(size_t)j * R + k];
+    int e = 0;
+#pragma unroll
+    for (int k = 0; k < R; ++k)
+#pragma unroll
+      for (int l = k; l < R; ++l) v[e++] += row[k] * row[l];
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int e = 0; e < NV; ++e) {
+    double x = v[e];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) scratch[warp * 36 + e] = x;
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < NV) {
+    double sacc = 0.0;
+    for (int w = 0; w < GW; ++w) sacc += scratch[w * 36 + threadIdx.x];
+    dst[threadIdx.x] = sacc;              // packed upper triangle
+  }
+  __syncthreads();
+}
+
+// S (full symmetric R x R, shared) = sum over row blocks of the packed partials
+template <int R>
+__device__ void grid_sum_gram(const double* parts /*[nb][2][R*R]*/, int nb, int which, double* S) {
+  constexpr int NV = R * (R + 1) / 2;
+  if ((int)threadIdx.x < NV) {
+    double sacc = 0.0;
+    for (int b = 0; b < nb; ++b) sacc += parts[((size_t)b * 2 + which) * R * R + threadIdx.x];
+    int e = threadIdx.x, k = 0;
+    while (e >= R - k) { e -= R - k; ++k; }
+    const int l = k + e;
+    S[k * R + l] = sacc; S[l * R + k] = sacc;
+  }
+}
+
+template <int R>
+__global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double scratch[GW * 36], S[2][R * R], Mat[2][R * R];
+  FitState* st = a.st;
+  if (st->done) return;                                   // same on every block: no sync is skipped
+  const int nb = gridDim.x - 1, rb = (int)blockIdx.x - 1;
+  double* ph0 = a.gscratch;
+  double* ph1 = ph0 + (size_t)nb * 2 * R * R;
+  double* ph2 = ph1 + (size_t)nb * 2 * R * R;
+  const double* G = a.momvec;
+  // ---- phase 1: scalars | Gram of G1, G2 ---------------------------------------------------------
+  // st->done is read by every block at entry, so it may only be raised after the first grid-wide
+  // sync; until then the decision travels in a scratch flag.
+  int* done_now = reinterpret_cast<int*>(a.gscratch + (size_t)3 * nb * 2 * R * R);
+  if (rb < 0) {
+    __shared__ ScalarShared ssh;
+    if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) *done_now = d; }
+  } else {
+    grid_partial_gram<R>(G, 0, a.p2, rb, nb, ph0 + ((size_t)rb * 2 + 0) * R * R, scratch);
+    grid_partial_gram<R>(G, a.p2, a.ld, rb, nb, ph0 + ((size_t)rb * 2 + 1) * R * R, scratch);
+  }
+  grid.sync();
+  if (*done_now) {                                        // the run ended with this pass: keep theta_k
+    if (rb < 0 && threadIdx.x == 0) st->done = 1;
+    return;
+  }
+  // ---- phase 2: L = G (G'G)^{-1/2}, Gram of it ------------------------------------------------------
+  if (rb >= 0) {
+    grid_sum_gram<R>(ph0, nb, 0, S[0]);
+    grid_sum_gram<R>(ph0, nb, 1, S[1]);
+    __syncthreads();
+    if (threadIdx.x == 0 || threadIdx.x == 32) {
+      const int w = threadIdx.x >> 5;
+      double A[R * R], V[R * R];
+      for (int e = 0; e < R * R; ++e) A[e] = S[w][e];
+      jacobi_eig<R>(A, V);
+      for (int i = 0; i < R; ++i)
+        for (int j = 0; j < R; ++j) {
+          double sacc = 0.0;
+          for (int k = 0; k < R; ++k) sacc += V[i * R + k] * (1.0 / sqrt(A[k * R + k])) * V[j * R + k];
+          Mat[w][i * R + j] = sacc;
+        }
+    }
+    __syncthreads();
+    for (int j = rb * GT + threadIdx.x; j < a.ld; j += nb * GT) {
+      const double* M = Mat[j >= a.p2 ? 1 : 0];
+      double row[R];
+#pragma unroll
+      for (int k = 0; k < R; ++k) row[k] = G[(size_t)j * R + k];
+#pragma unroll
+      for (int l = 0; l < R; ++l) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int k = 0; k < R; ++k) sacc += row[k] * M[k * R + l];
+        a.L[(size_t)j * R + l] = sacc;
+      }
+    }
+    __syncthreads();
+    grid_partial_gram<R>(a.L, 0, a.p2, rb, nb, ph1 + ((size_t)rb * 2 + 0) * R * R, scratch);
+    grid_partial_gram<R>(a.L, a.p2, a.ld, rb, nb, ph1 + ((size_t)rb * 2 + 1) * R * R, scratch);
+  }
+  grid.sync();
+  // ---- phase 3: one Newton-Schulz step L <- L (3I - L'L)/2, Gram of the result ----------------------
+  if (rb >= 0) {
+    grid_sum_gram<R>(ph1, nb, 0, S[0]);
+    grid_sum_gram<R>(ph1, nb, 1, S[1]);
+    __syncthreads();
+    if (threadIdx.x < 2 * R * R) {
+      const int w = threadIdx.x / (R * R), e = threadIdx.x - w * R * R;
+      Mat[w][e] = ((e / R) == (e % R) ? 1.5 : 0.0) - 0.5 * S[w][e];
+    }
+    __syncthreads();
+    for (int j = rb * GT + threadIdx.x; j < a.ld; j += nb * GT) {
+      const double* M = Mat[j >= a.p2 ? 1 : 0];
+      double row[R], res[R];
+#pragma unroll
+      for (int k = 0; k < R; ++k) row[k] = a.L[(size_t)j * R + k];
+#pragma unroll
+      for (int l = 0; l < R; ++l) {
+        double sacc = 0.0;
+#pragma unroll
+        for (int k = 0; k < R; ++k) sacc += row[k] * M[k * R + l];
+        res[l] = sacc;
+      }
+#pragma unroll
+      for (int l = 0; l < R; ++l) a.L[(size_t)j * R + l] = res[l];
+    }
+    __syncthreads();
+    grid_partial_gram<R>(a.L, 0, a.p2, rb, nb, ph2 + ((size_t)rb * 2 + 0) * R * R, scratch);
+    grid_partial_gram<R>(a.L, a.p2, a.ld, rb, nb, ph2 + ((size_t)rb * 2 + 1) * R * R, scratch);
+  }
+  grid.sync();
+  // ---- phase 4: W'W, C'C of the new loadings -----------------------------------------------------------
+  if (rb < 0) {
+    grid_sum_gram<R>(ph2, nb, 0, S[0]);
+    grid_sum_gram<R>(ph2, nb, 1, S[1]);
+    __syncthreads();
+    if (threadIdx.x < R * R) { st->WtW[threadIdx.x] = S[0][threadIdx.x]; st->CtC[threadIdx.x] = S[1][threadIdx.x]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      bool ok = true;
+      for (int e = 0; e < R * R; ++e) ok = ok && finite_d(S[0][e]) && finite_d(S[1][e]);
+      if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = st->pass - 1; }
+    }
+  }
+}
+
+int update_grid_blocks(int ld) {
+  int nb = (ld + GT - 1) / GT;
+  if (nb > 96) nb = 96;
+  if (nb < 1) nb = 1;
+  return nb + 1;
+}
+size_t update_grid_scratch_doubles(int ld, int R) { return (size_t)3 * (update_grid_blocks(ld) - 1) * 2 * R * R + 2; }
+
 // Start state: coefficients and Gram matrices for theta_0.
 template <int R>
 __global__ void __launch_bounds__(UPD_THREADS, 1) em_prepare_kernel(const UpdateArgs a) {
@@ -431,63 +647,71 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_prepare_kernel(const Update
   }
 }
 
-// out[e] = sum over CTAs (in CTA order) of partials[c][e]
-__global__ void reduce_partials_kernel(const double* __restrict__ partials, int nparts, int64_t len,
-                                       double* __restrict__ out, const FitState* st) {
+// out[e] = sum over CTAs of partials[c][e], in a fixed order: slice y of 8 adds parts y, y+8, ...,
+// then the 8 slices are added in order (run-to-run deterministic, 8x the parallelism of one thread
+// per element).
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ partials, int nparts, int64_t len,
+                                                              double* __restrict__ out, const FitState* st) {
   if (st->done) return;
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= len) return;
-  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-  int c = 0;
-  for (; c + 3 < nparts; c += 4) {
-    s0 += partials[(size_t)c * len + e];
-    s1 += partials[(size_t)(c + 1) * len + e];
-    s2 += partials[(size_t)(c + 2) * len + e];
-    s3 += partials[(size_t)(c + 3) * len + e];
+  __shared__ double sh[8][33];
+  const int64_t e = (int64_t)blockIdx.x * 32 + threadIdx.x;
+  double s0 = 0.0, s1 = 0.0;
+  if (e < len) {
+    int c = threadIdx.y;
+    for (; c + 8 < nparts; c += 16) { s0 += partials[(size_t)c * len + e]; s1 += partials[(size_t)(c + 8) * len + e]; }
+    if (c < nparts) s0 += partials[(size_t)c * len + e];
   }
-  for (; c < nparts; ++c) s0 += partials[(size_t)c * len + e];
-  out[e] = (s0 + s1) + (s2 + s3);
+  sh[threadIdx.y][threadIdx.x] = s0 + s1;
+  __syncthreads();
+  if (threadIdx.y == 0 && e < len) {
+    double t = 0.0;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += sh[y][threadIdx.x];
+    out[e] = t;
+  }
 }
 
 cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t len, double* momvec,
                                    const FitState* st, cudaStream_t stream) {
-  const int threads = 128;
-  reduce_partials_kernel<<<(unsigned)((len + threads - 1) / threads), threads, 0, stream>>>(partials, nparts, len, momvec, st);
+  reduce_partials_kernel<<<(unsigned)((len + 31) / 32), dim3(32, 8), 0, stream>>>(partials, nparts, len, momvec, st);
   return cudaGetLastError();
 }
 
 template <int R>
-static void launch_update_R(const UpdateArgs& a, bool prepare, cudaStream_t stream) {
+static void launch_update_R(const UpdateArgs& a, bool prepare, int orth_type, cudaStream_t stream) {
   if (prepare) em_prepare_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
-  else em_update_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
+  else if (orth_type == PPLS_ORTH_SVD && a.gscratch) {
+    void* args[] = {(void*)&a};
+    cudaLaunchCooperativeKernel((const void*)em_update_grid_kernel<R>, dim3(update_grid_blocks(a.ld)), dim3(GT), args, 0, stream);
+  } else em_update_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
 }
 
 static cudaError_t dispatch_update(const DataShape& s, int R, const double* momvec, double* L,
                                    double* Lscratch, FitState* st, double* trace, bool prepare,
-                                   cudaStream_t stream) {
+                                   int orth_type, double* gscratch, cudaStream_t stream) {
   UpdateArgs a;
-  a.momvec = momvec; a.L = L; a.Lscratch = Lscratch; a.st = st; a.trace = trace;
+  a.momvec = momvec; a.L = L; a.Lscratch = Lscratch; a.st = st; a.trace = trace; a.gscratch = gscratch;
   a.p = s.p; a.q = s.q; a.p2 = s.p2; a.q2 = s.q2; a.ld = s.ld;
   switch (R) {
-    case 1: launch_update_R<1>(a, prepare, stream); break;
-    case 2: launch_update_R<2>(a, prepare, stream); break;
-    case 3: launch_update_R<3>(a, prepare, stream); break;
-    case 4: launch_update_R<4>(a, prepare, stream); break;
-    case 5: launch_update_R<5>(a, prepare, stream); break;
-    case 6: launch_update_R<6>(a, prepare, stream); break;
-    case 7: launch_update_R<7>(a, prepare, stream); break;
-    case 8: launch_update_R<8>(a, prepare, stream); break;
+    case 1: launch_update_R<1>(a, prepare, orth_type, stream); break;
+    case 2: launch_update_R<2>(a, prepare, orth_type, stream); break;
+    case 3: launch_update_R<3>(a, prepare, orth_type, stream); break;
+    case 4: launch_update_R<4>(a, prepare, orth_type, stream); break;
+    case 5: launch_update_R<5>(a, prepare, orth_type, stream); break;
+    case 6: launch_update_R<6>(a, prepare, orth_type, stream); break;
+    case 7: launch_update_R<7>(a, prepare, orth_type, stream); break;
+    case 8: launch_update_R<8>(a, prepare, orth_type, stream); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
 }
 
 cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
-                             FitState* st, double* trace, cudaStream_t stream) {
-  return dispatch_update(s, R, momvec, L, Lscratch, st, trace, false, stream);
+                             FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream) {
+  return dispatch_update(s, R, momvec, L, Lscratch, st, trace, false, orth_type, gscratch, stream);
 }
 cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream) {
-  return dispatch_update(s, R, nullptr, const_cast<double*>(L), nullptr, st, nullptr, true, stream);
+  return dispatch_update(s, R, nullptr, const_cast<double*>(L), nullptr, st, nullptr, true, 0, nullptr, stream);
 }
 
 }  // namespace ppls

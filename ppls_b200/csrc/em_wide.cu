@@ -198,24 +198,28 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
   }
 }
 
-// proj[i][0..R) = sum over X slabs of the partial projections, proj[i][R..2R) = sum over Y slabs
-// (slab order: fixed).  One thread per (row, component).
-__global__ void wide_proj_sum_kernel(const double* __restrict__ ppart, int64_t n, int R, int nslabX, int nslabY,
-                                     double* __restrict__ proj, const FitState* st) {
+// proj[i][0..R) = sum over X slabs of the partial projections, proj[i][R..2R) = sum over Y slabs.
+// Fixed order: slice y of 8 adds slabs y, y+8, ...; the 8 slices are then added in order.
+__global__ void __launch_bounds__(256) wide_proj_sum_kernel(const double* __restrict__ ppart, int64_t n, int R, int nslabX,
+                                                            int nslabY, double* __restrict__ proj, const FitState* st) {
   if (st->done) return;
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n * R) return;
-  const int64_t i = e / R; const int k = (int)(e - i * R);
+  __shared__ double sh[2][8][33];
+  const int64_t e = (int64_t)blockIdx.x * 32 + threadIdx.x;
   const size_t slab_stride = (size_t)n * R;
-  double s0 = 0.0, s1 = 0.0;
-  int s = 0;
-  for (; s + 1 < nslabX; s += 2) { s0 += ppart[(size_t)s * slab_stride + e]; s1 += ppart[(size_t)(s + 1) * slab_stride + e]; }
-  if (s < nslabX) s0 += ppart[(size_t)s * slab_stride + e];
-  proj[i * 2 * R + k] = s0 + s1;
-  s0 = 0.0; s1 = 0.0;
-  for (s = nslabX; s + 1 < nslabX + nslabY; s += 2) { s0 += ppart[(size_t)s * slab_stride + e]; s1 += ppart[(size_t)(s + 1) * slab_stride + e]; }
-  if (s < nslabX + nslabY) s0 += ppart[(size_t)s * slab_stride + e];
-  proj[i * 2 * R + R + k] = s0 + s1;
+  double sx = 0.0, sy = 0.0;
+  if (e < n * R) {
+    for (int s = threadIdx.y; s < nslabX; s += 8) sx += ppart[(size_t)s * slab_stride + e];
+    for (int s = nslabX + threadIdx.y; s < nslabX + nslabY; s += 8) sy += ppart[(size_t)s * slab_stride + e];
+  }
+  sh[0][threadIdx.y][threadIdx.x] = sx; sh[1][threadIdx.y][threadIdx.x] = sy;
+  __syncthreads();
+  if (threadIdx.y < 2 && e < n * R) {
+    double t = 0.0;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += sh[threadIdx.y][y][threadIdx.x];
+    const int64_t i = e / R; const int k = (int)(e - i * R);
+    proj[i * 2 * R + threadIdx.y * R + k] = t;
+  }
 }
 
 // mu_T, mu_U of every row (EM_W_multi.R:691-694) and per-block partial Gram sums of [Xw Yc].
@@ -370,7 +374,7 @@ cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const dou
   dim3 grid(w.nslabX + w.nslabY, w.nrg);
   wide_lookup(w.R, w.NCH, MODE_PROJECT)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_PROJECT), stream>>>(a);
   const int64_t ne = s.n * w.R;
-  wide_proj_sum_kernel<<<(unsigned)((ne + 255) / 256), 256, 0, stream>>>(ws + o.ppart, s.n, w.R, w.nslabX, w.nslabY, ws + o.proj, st);
+  wide_proj_sum_kernel<<<(unsigned)((ne + 31) / 32), dim3(32, 8), 0, stream>>>(ws + o.ppart, s.n, w.R, w.nslabX, w.nslabY, ws + o.proj, st);
   return cudaGetLastError();
 }
 
