@@ -145,6 +145,16 @@ int ppls_simult_run(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts,
                     const ppls_params* init, ppls_params* est, double* loglik,
                     int32_t* steps_done, double* moments, double* mu_T, double* mu_U);
 
+/* ---- batched multi-start: n_starts start states over one resident dataset ----------------- */
+/* Every start is an independent run of EM_W_multi.R:780-793 (its own break rule and trace); the
+ * starts share each pass over the data (floor(8/r) starts per streaming-kernel launch).
+ * inits / ests: arrays of n_starts structs (ests in LOOP order, caller-allocated W, C, B, sigT);
+ * loglik: n_starts x max_steps, row s holds loglik[0 .. steps_done[s]-1] of start s (may be NULL);
+ * timing: loop time / launches / passes of the whole batch (may be NULL). */
+int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, int32_t n_starts,
+                            const ppls_params* inits, ppls_params* ests, double* loglik,
+                            int32_t* steps_done, ppls_timing* timing);
+
 #ifdef __cplusplus
 }
 #endif

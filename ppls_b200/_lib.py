@@ -63,6 +63,7 @@ SIGNATURES = {
     "ppls_fit_result": (C.c_int, [_vp, C.POINTER(Params), _vp, _i32p, _vp, _vp, _vp]),
     "ppls_fit_timing": (C.c_int, [_vp, C.POINTER(Timing)]),
     "ppls_fit_destroy": (C.c_int, [_vp]),
+    "ppls_simult_run_batched": (C.c_int, [_vp, _vp, C.POINTER(Opts), C.c_int32, _vp, _vp, _vp, _i32p, C.POINTER(Timing)]),
     "ppls_simult_run": (C.c_int, [_vp, _vp, C.POINTER(Opts), C.POINTER(Params), C.POINTER(Params), _vp, _i32p,
                                   _vp, _vp, _vp]),
 }

@@ -282,3 +282,51 @@ def PPLS_simult(X, Y, a, EMsteps=10, atol=1e-4, type="SVD", init: Optional[dict]
                 loop_state=dict(W=res["W"], C=res["C"], B=np.diag(res["B"]), sigT=np.diag(res["sigT"]),
                                 sigE=res["sigE"], sigF=res["sigF"], sigH=res["sigH"]),
                 **{"class": "PPLS_simult"})
+
+
+def PPLS_simult_batched(X, Y, a, inits, EMsteps=10, atol=1e-4, type="SVD", ctx: Optional[Context] = None,
+                        data: Optional[Data] = None, timing: bool = False):
+    """Multi-start PPLS_simult: every element of `inits` is a start state (as `init=` of PPLS_simult);
+    all starts run the loop of EM_W_multi.R:780-793 concurrently over ONE resident copy of X and Y
+    (ppls_simult_run_batched).  Returns a list of {'loglik', 'estimates', 'loop_state', 'steps'} in the
+    order of `inits` (estimates normalised as at :794-799); with timing=True also the batch timing dict.
+    The reference has no such entry point: it would call PPLS_simult once per start."""
+    if isinstance(type, (tuple, list)):
+        type = type[0]
+    if type not in ("SVD", "QR"):
+        raise ValueError("'arg' should be one of 'SVD', 'QR'")
+    a = int(a)
+    ctx = ctx or (data.ctx if data is not None else default_context())
+    own = data is None
+    if data is None:
+        data = Data.from_host(ctx, X, Y)
+    try:
+        S = len(inits)
+        starts, outs = [], []
+        for init in inits:
+            W0, C0, B0, T0 = normalise(init["W"], init["C"], init["B"], init["sigT"])          # :773-778
+            starts.append(_ParamsBuf(data.p, data.q, a, W0, C0, B0, T0, init["sigE"], init["sigF"], init["sigH"]))
+            outs.append(_ParamsBuf(data.p, data.q, a))
+        ini_arr = (L.Params * S)(*[s.struct for s in starts])
+        est_arr = (L.Params * S)(*[o.struct for o in outs])
+        opts = L.Opts(a, int(EMsteps), L.PPLS_ORTH_SVD if type == "SVD" else L.PPLS_ORTH_QR, 0, float(atol), 0, 0)
+        loglik = np.zeros((S, max(int(EMsteps), 1)))
+        steps = (C.c_int32 * S)()
+        tm = L.Timing()
+        L.check(L.lib().ppls_simult_run_batched(ctx._h, data._h, C.byref(opts), S, ini_arr, est_arr,
+                                                loglik.ctypes.data, steps, C.byref(tm)))
+    finally:
+        if own:
+            data.close()
+    res = []
+    for s in range(S):
+        o = outs[s]
+        Wn, Cn, Bn, Tn = normalise(o.W, o.C, o.B, o.sigT)                                       # :794-799
+        e = est_arr[s]
+        res.append(dict(loglik=loglik[s, :steps[s]].copy(), steps=int(steps[s]),
+                        estimates=dict(W=Wn, C=Cn, B=Bn, sigE=e.sigE, sigF=e.sigF, sigH=e.sigH, sigT=Tn),
+                        loop_state=dict(W=o.W, C=o.C, B=np.diag(o.B), sigT=np.diag(o.sigT), sigE=e.sigE, sigF=e.sigF,
+                                        sigH=e.sigH)))
+    if timing:
+        return res, {k: getattr(tm, k) for k, _ in L.Timing._fields_}
+    return res

@@ -635,3 +635,115 @@ extern "C" int ppls_simult_run(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   fit_free(f);
   return rc;
 }
+
+// ---- batched multi-start (BASELINE config 5) ------------------------------------------------------------
+// S start states over ONE resident dataset.  Starts are packed g = floor(8 / r) at a time into the
+// streaming kernel's component dimension (the E-step is diagonal in the components, so a pack of starts
+// is a wider W): each data pass serves g starts, the update runs one block per start.
+extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, int32_t n_starts,
+                                       const ppls_params* inits, ppls_params* ests, double* loglik,
+                                       int32_t* steps_done, ppls_timing* timing) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!d || !opts || !inits || !ests || !steps_done) return fail(PPLS_E_INVALID, "null argument");
+  if (d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
+  const int R = opts->r, S = n_starts;
+  if (R < 1 || R > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
+  if (S < 1) return fail(PPLS_E_INVALID, "need at least one start");
+  if (R > d->s.p || R > d->s.q) return fail(PPLS_E_INVALID, "nr_comp exceeds ncol(X) or ncol(Y)");
+  if (opts->max_steps < 0) return fail(PPLS_E_INVALID, "EMsteps must be >= 0");
+  for (int s = 0; s < S; ++s) { rc = check_params(&inits[s], "init"); if (rc) return rc; rc = check_params(&ests[s], "est"); if (rc) return rc; }
+  const DataShape& sh = d->s;
+  const int g = (MAXR / R) < S ? (MAXR / R) : S, RP = g * R, groups = (S + g - 1) / g;
+  StreamPlan plan{};
+  const char* why = "";
+  if (plan_stream(sh, RP, ctx->sm_count, &plan, &why) != cudaSuccess)
+    return fail(PPLS_E_UNSUPPORTED, std::string("batched run: streaming-kernel plan: ") + why);
+  const size_t veclen = (size_t)momvec_len(sh.ld, R), veclenP = (size_t)momvec_len(sh.ld, RP);
+  const int tracelen = opts->max_steps + 1;
+  struct Bufs {
+    double *Lp = nullptr, *Ls = nullptr, *Lsc = nullptr, *mp = nullptr, *ms = nullptr, *tr = nullptr, *part = nullptr;
+    FitState *pst = nullptr, *st = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    ~Bufs() { cudaFree(Lp); cudaFree(Ls); cudaFree(Lsc); cudaFree(mp); cudaFree(ms); cudaFree(tr); cudaFree(part); cudaFree(pst); cudaFree(st);
+              if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); }
+  } B;
+  CU(cudaMalloc(&B.Lp, (size_t)groups * sh.ld * RP * sizeof(double)));
+  CU(cudaMalloc(&B.Ls, (size_t)S * sh.ld * R * sizeof(double)));
+  CU(cudaMalloc(&B.Lsc, (size_t)S * sh.ld * R * sizeof(double)));
+  CU(cudaMalloc(&B.mp, (size_t)groups * veclenP * sizeof(double)));
+  CU(cudaMalloc(&B.ms, (size_t)S * veclen * sizeof(double)));
+  CU(cudaMalloc(&B.tr, (size_t)S * tracelen * sizeof(double)));
+  CU(cudaMalloc(&B.part, (size_t)plan.grid * veclenP * sizeof(double)));
+  CU(cudaMalloc(&B.pst, (size_t)groups * sizeof(FitState)));
+  CU(cudaMalloc(&B.st, (size_t)S * sizeof(FitState)));
+  CU(cudaEventCreate(&B.e0)); CU(cudaEventCreate(&B.e1));
+  std::vector<FitState> hst(S);
+  std::vector<double> Lh((size_t)S * sh.ld * R), L1;
+  for (int s = 0; s < S; ++s) {
+    FitState& h = hst[s];
+    memset(&h, 0, sizeof(FitState));
+    for (int k = 0; k < R; ++k) { h.b[k] = inits[s].B[k]; h.t[k] = inits[s].sigT[k]; }
+    h.sigE = inits[s].sigE; h.sigF = inits[s].sigF; h.sigH = inits[s].sigH;
+    h.ssqX = d->ssq[0]; h.ssqY = d->ssq[1]; h.Ntot = (double)d->n_total;
+    h.max_steps = opts->max_steps; h.orth_type = opts->orth_type; h.R = R; h.atol = opts->atol;
+    pack_loadings(sh, R, inits[s].W, inits[s].C, L1);
+    memcpy(&Lh[(size_t)s * sh.ld * R], L1.data(), L1.size() * sizeof(double));
+  }
+  cudaStream_t st = ctx->stream;
+  CU(cudaMemcpyAsync(B.st, hst.data(), (size_t)S * sizeof(FitState), cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(B.Ls, Lh.data(), Lh.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  CU(cudaMemsetAsync(B.Lp, 0, (size_t)groups * sh.ld * RP * sizeof(double), st));
+  CU(cudaMemsetAsync(B.pst, 0, (size_t)groups * sizeof(FitState), st));
+  CU(cudaMemsetAsync(B.tr, 0, (size_t)S * tracelen * sizeof(double), st));
+  CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 1, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st));
+  CU(cudaStreamSynchronize(st));            // host vectors must outlive the copies
+  const int check_every = opts->check_every > 0 ? opts->check_every : 16;
+  int64_t launches = 1, passes = 0;
+  CU(cudaEventRecord(B.e0, st));
+  for (int pass = 0; pass <= opts->max_steps; ++pass) {
+    for (int gr = 0; gr < groups; ++gr) {
+      CU(launch_em_stream(plan, sh, d->D, B.Lp + (size_t)gr * sh.ld * RP, B.pst + gr, B.part, nullptr, nullptr, 0, st));
+      CU(launch_reduce_partials(B.part, plan.grid, (int64_t)veclenP, B.mp + (size_t)gr * veclenP, B.pst + gr, st));
+    }
+    rc = allreduce_sum(ctx, B.mp, (size_t)groups * veclenP);
+    if (rc) return rc;
+    CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 0, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st));
+    launches += 2 * groups + 2; passes += 1;
+    if ((pass + 1) % check_every == 0 && pass < opts->max_steps) {
+      CU(cudaMemcpyAsync(hst.data(), B.st, (size_t)S * sizeof(FitState), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      bool all = true;
+      for (int s = 0; s < S; ++s) all = all && hst[s].done;
+      if (all) break;
+    }
+  }
+  CU(cudaEventRecord(B.e1, st));
+  CU(cudaMemcpyAsync(hst.data(), B.st, (size_t)S * sizeof(FitState), cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(Lh.data(), B.Ls, Lh.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  std::vector<double> trh((size_t)S * tracelen);
+  CU(cudaMemcpyAsync(trh.data(), B.tr, trh.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  for (int s = 0; s < S; ++s) {
+    const FitState& h = hst[s];
+    if (h.status != PPLS_OK) return fail(h.status, "a parameter became non-finite during EM (batched run)");
+    const double* L = &Lh[(size_t)s * sh.ld * R];
+    for (int k = 0; k < R; ++k) {
+      for (int j = 0; j < sh.p; ++j) ests[s].W[j + (size_t)k * sh.p] = L[(size_t)j * R + k];
+      for (int j = 0; j < sh.q; ++j) ests[s].C[j + (size_t)k * sh.q] = L[(size_t)(sh.p2 + j) * R + k];
+      ests[s].B[k] = h.b[k]; ests[s].sigT[k] = h.t[k];
+    }
+    ests[s].sigE = h.sigE; ests[s].sigF = h.sigF; ests[s].sigH = h.sigH;
+    steps_done[s] = h.steps_done;
+    if (loglik) for (int i = 0; i < h.steps_done; ++i) loglik[(size_t)s * opts->max_steps + i] = trh[(size_t)s * tracelen + i];
+  }
+  if (timing) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, B.e0, B.e1);
+    memset(timing, 0, sizeof(*timing));
+    timing->loop_ms = ms; timing->kernel_launches = launches; timing->passes = passes;
+    timing->stream_launches = passes * groups;
+    timing->bytes_per_pass = (int64_t)8 * sh.n * ((int64_t)sh.p + sh.q);
+  }
+  return PPLS_OK;
+}

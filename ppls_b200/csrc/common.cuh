@@ -90,6 +90,10 @@ cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t l
 // orth_type SVD + gscratch != null: the grid (cooperative) kernel; else the single-CTA kernel.
 cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
                              FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream);
+// batched multi-start: S starts, g per pack of RP = g*R components (em_update.cu)
+cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int S, int tracelen, int prepare,
+                                   const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,
+                                   double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream);
 int update_grid_blocks(int ld);
 size_t update_grid_scratch_doubles(int ld, int R);
 // Prepare coefficients + Gram matrices for the start state (pass 0).

@@ -422,7 +422,7 @@ __device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
 }
 
 template <int R>
-__global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateArgs a) {
+__device__ void update_body(const UpdateArgs& a) {
   __shared__ double scratch[UPD_WARPS * 36], S[R * R], Mat[R * R];
   __shared__ int s_done;
   __shared__ ScalarShared ssh;
@@ -455,6 +455,72 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateA
     for (int e = 0; e < R * R; ++e) ok = ok && finite_d(st->WtW[e]) && finite_d(S[e]);
     if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = st->pass - 1; }
   }
+}
+
+template <int R>
+__global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateArgs a) { update_body<R>(a); }
+
+// ---- batched multi-start: one block per start ------------------------------------------------------
+// The streaming kernel runs `g` starts at once as g*R "components" (the E-step is diagonal in the
+// components, so a pack of starts is just a wider W); this kernel cuts every start's slice out of the
+// pack's moment vector, runs the ordinary update on it and writes the new loadings / coefficients back
+// into the pack.  prepare = 1: start state (coefficients, W'W, C'C) instead of an update.
+struct BatchArgs {
+  const double* momvec_pack;   // [groups][ld*RP + 3*RP*RP]
+  double* L_pack;              // [groups][ld][RP]
+  FitState* pack_st;           // [groups]  what the streaming kernel reads (coefficients, done)
+  FitState* st;                // [S]
+  double* momvec_s;            // [S][ld*R + 3*R*R]
+  double* L_s;                 // [S][ld][R]
+  double* Lscratch_s;          // [S][ld][R]
+  double* trace;               // [S][tracelen]
+  int32_t RP, g, S, tracelen, prepare;
+  int32_t p, q, p2, q2, ld;
+};
+
+template <int R>
+__device__ void prepare_body(const UpdateArgs& a);
+
+template <int R>
+__global__ void __launch_bounds__(UPD_THREADS, 1) em_update_batch_kernel(const BatchArgs b) {
+  const int sidx = blockIdx.x, group = sidx / b.g, k0 = (sidx - group * b.g) * R, RP = b.RP;
+  const size_t veclen = (size_t)b.ld * R + 3 * R * R, veclenP = (size_t)b.ld * RP + 3 * RP * RP;
+  UpdateArgs a;
+  a.momvec = b.momvec_s + sidx * veclen; a.L = b.L_s + (size_t)sidx * b.ld * R;
+  a.Lscratch = b.Lscratch_s + (size_t)sidx * b.ld * R; a.st = b.st + sidx; a.trace = b.trace + (size_t)sidx * b.tracelen;
+  a.gscratch = nullptr; a.p = b.p; a.q = b.q; a.p2 = b.p2; a.q2 = b.q2; a.ld = b.ld;
+  FitState* st = a.st;
+  FitState* ps = b.pack_st + group;
+  double* Lp = b.L_pack + (size_t)group * b.ld * RP;
+  if (b.prepare) {
+    prepare_body<R>(a);
+  } else {
+    if (st->done) return;
+    const double* mp = b.momvec_pack + group * veclenP;
+    double* ms = b.momvec_s + sidx * veclen;
+    for (int e = threadIdx.x; e < b.ld * R; e += UPD_THREADS) { const int j = e / R, k = e - j * R; ms[e] = mp[(size_t)j * RP + k0 + k]; }
+    for (int e = threadIdx.x; e < 3 * R * R; e += UPD_THREADS) {
+      const int which = e / (R * R), kl = e - which * R * R, k = kl / R, l = kl - k * R;
+      ms[(size_t)b.ld * R + e] = mp[(size_t)b.ld * RP + (size_t)which * RP * RP + (size_t)(k0 + k) * RP + k0 + l];
+    }
+    __syncthreads();
+    update_body<R>(a);
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < b.ld * R; e += UPD_THREADS) { const int j = e / R, k = e - j * R; Lp[(size_t)j * RP + k0 + k] = a.L[e]; }
+  if (threadIdx.x < R) {
+    const int k = threadIdx.x;
+    ps->aT[k0 + k] = st->aT[k]; ps->bT[k0 + k] = st->bT[k]; ps->aU[k0 + k] = st->aU[k]; ps->bU[k0 + k] = st->bU[k];
+  }
+}
+
+// a pack is done when every member is
+__global__ void batch_done_kernel(FitState* pack_st, const FitState* st, int g, int S) {
+  const int group = blockIdx.x * blockDim.x + threadIdx.x;
+  if (group * g >= S) return;
+  int all = 1;
+  for (int m = group * g; m < (group + 1) * g && m < S; ++m) all = all && st[m].done;
+  pack_st[group].done = all;
 }
 
 
@@ -630,7 +696,7 @@ size_t update_grid_scratch_doubles(int ld, int R) { return (size_t)3 * (update_g
 
 // Start state: coefficients and Gram matrices for theta_0.
 template <int R>
-__global__ void __launch_bounds__(UPD_THREADS, 1) em_prepare_kernel(const UpdateArgs a) {
+__device__ void prepare_body(const UpdateArgs& a) {
   __shared__ double scratch[UPD_WARPS * 36], S[R * R];
   FitState* st = a.st;
   block_gram<R>(a.L, a.p2, S, scratch);
@@ -645,6 +711,34 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_prepare_kernel(const Update
     for (int k = 0; k < R; ++k) ok = ok && finite_d(st->aT[k]) && finite_d(st->bT[k]) && finite_d(st->aU[k]) && finite_d(st->bU[k]);
     if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; }
   }
+}
+template <int R>
+__global__ void __launch_bounds__(UPD_THREADS, 1) em_prepare_kernel(const UpdateArgs a) { prepare_body<R>(a); }
+
+template <int R>
+static void launch_batch_R(const BatchArgs& b, cudaStream_t stream) {
+  em_update_batch_kernel<R><<<b.S, UPD_THREADS, 0, stream>>>(b);
+}
+cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int S, int tracelen, int prepare,
+                                   const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,
+                                   double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream) {
+  BatchArgs b;
+  b.momvec_pack = momvec_pack; b.L_pack = L_pack; b.pack_st = pack_st; b.st = st; b.momvec_s = momvec_s; b.L_s = L_s;
+  b.Lscratch_s = Lscratch_s; b.trace = trace; b.RP = RP; b.g = g; b.S = S; b.tracelen = tracelen; b.prepare = prepare;
+  b.p = s.p; b.q = s.q; b.p2 = s.p2; b.q2 = s.q2; b.ld = s.ld;
+  switch (R) {
+    case 1: launch_batch_R<1>(b, stream); break;
+    case 2: launch_batch_R<2>(b, stream); break;
+    case 3: launch_batch_R<3>(b, stream); break;
+    case 4: launch_batch_R<4>(b, stream); break;
+    case 5: launch_batch_R<5>(b, stream); break;
+    case 6: launch_batch_R<6>(b, stream); break;
+    case 7: launch_batch_R<7>(b, stream); break;
+    case 8: launch_batch_R<8>(b, stream); break;
+    default: return cudaErrorInvalidValue;
+  }
+  if (!prepare) batch_done_kernel<<<(S / g + 64) / 64, 64, 0, stream>>>(pack_st, st, g, S);
+  return cudaGetLastError();
 }
 
 // out[e] = sum over CTAs of partials[c][e], in a fixed order: slice y of 8 adds parts y, y+8, ...,

@@ -162,3 +162,35 @@ def test_wide_shapes_vs_fused_oracle(ctx, oracle_lib, shape, steps):
     for k in ("W", "C", "B", "sigT", "Ctt", "Cuu", "Cut", "Chh", "mu_T", "mu_U"):
         assert relmax(res[k], o[k]) < TOL_PARAM, k
     f.close(); d.close()
+
+
+@pytest.mark.parametrize("shape,S,steps", [((3000, 60, 22, 2), 9, 12), ((1500, 40, 30, 3), 5, 8), ((800, 33, 17, 8), 3, 5),
+                                            ((2000, 50, 20, 1), 11, 10)])
+def test_batched_multistart_matches_single_runs(ctx, oracle_lib, shape, S, steps):
+    """ppls_simult_run_batched (starts packed into the streaming kernel's component dimension) ==
+    one ordinary run per start, and == the oracle for the first start."""
+    from oracle import ppls_fused as F
+    from ppls_b200 import Data, Fit, PPLS_simult_batched, synth, normalise
+    N, p, q, r = shape
+    truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
+    d = Data.synthetic(ctx, N, p, q, truth, seed=31)
+    inits = [synth.start_params(truth, seed=100 + s, noise=0.5 + 0.1 * s) for s in range(S)]
+    out = PPLS_simult_batched(None, None, r, inits, EMsteps=steps, atol=1e-3, data=d)
+    assert len(out) == S
+    for s in range(S):
+        W0, C0, B0, T0 = normalise(inits[s]["W"], inits[s]["C"], inits[s]["B"], inits[s]["sigT"])
+        st = dict(inits[s], W=W0, C=C0, B=B0, sigT=T0)
+        f = Fit(d, st, r, steps, 1e-3, "SVD"); f.run(); one = f.result(want_mu=False); f.close()
+        assert out[s]["steps"] == one["steps"]
+        assert relmax(out[s]["loglik"], one["loglik"]) < 1e-12
+        ls = out[s]["loop_state"]
+        for k in ("W", "C"):
+            assert relmax(ls[k], one[k]) < 1e-10, k
+        assert relmax(np.diag(ls["B"]), one["B"]) < 1e-10 and abs(ls["sigE"] / one["sigE"] - 1) < 1e-10
+    X, Y = d.export()
+    W0, C0, B0, T0 = normalise(inits[0]["W"], inits[0]["C"], inits[0]["B"], inits[0]["sigT"])
+    o = F.fused_loop(oracle_lib, X, Y, W0, C0, B0, inits[0]["sigE"], inits[0]["sigF"], inits[0]["sigH"], T0,
+                     EMsteps=steps, atol=1e-3, want_mu=False)
+    assert out[0]["steps"] == o["steps"] and relmax(out[0]["loglik"], o["loglik"]) < 1e-10
+    assert relmax(out[0]["loop_state"]["W"], o["W"]) < TOL_PARAM
+    d.close()
