@@ -218,13 +218,13 @@ def run_ours(args):
     #   8*n*(p+q) for the fused kernel, twice that for the two-pass wide-row path
     wide = bytes_pass > 8 * n_local * (p + q)
     achieved = bytes_pass / (k1_ms * 1e-3) / 1e9
-    traffic = None
+    traffic = None                                       # dram bytes per launch, from the committed ncu capture
     tpath = os.path.join(ROOT, "profiles", "k1_traffic.json")
-    if os.path.exists(tpath):
+    if os.path.exists(tpath) and not wide:
         try:
             tj = json.load(open(tpath))
-            if tj.get("workload") == args.workload and tj.get("gpus", 1) == world:
-                traffic = tj.get("dram_bytes_per_launch")
+            if tj.get("workload") == args.workload:
+                traffic = tj["dram_bytes_per_row"] * n_local
         except Exception:
             pass
     out = {
