@@ -191,6 +191,9 @@ static int shape_init(DataShape* s, int64_t n, int64_t p, int64_t q) {
   s->n = n; s->p = (int32_t)p; s->q = (int32_t)q;
   s->p2 = (int32_t)((p + 1) & ~(int64_t)1); s->q2 = (int32_t)((q + 1) & ~(int64_t)1);
   s->ld = s->p2 + s->q2;
+  const char* fp = getenv("PPLS_PANEL");
+  s->panel = (fp && *fp) ? (atoi(fp) != 0) : (s->ld > PANEL_LD_MIN);
+  s->npX = (s->p2 + PANEL_W - 1) / PANEL_W; s->npY = (s->q2 + PANEL_W - 1) / PANEL_W;
   return PPLS_OK;
 }
 
@@ -229,8 +232,9 @@ extern "C" int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, 
   d->ctx = ctx;
   rc = shape_init(&d->s, n, p, q);
   if (rc) { delete d; return rc; }
-  const size_t bytes = (size_t)n * d->s.ld * sizeof(double);
+  const size_t bytes = data_elems(d->s) * sizeof(double);
   cudaError_t e = cudaMalloc(&d->D, bytes);
+  if (e == cudaSuccess && d->s.panel) e = cudaMemsetAsync(d->D, 0, bytes, ctx->stream);
   if (e != cudaSuccess) { delete d; return fail(PPLS_E_OOM, std::string("device allocation of the data shard: ") + cudaGetErrorString(e)); }
   // staging: chunks of rows, column-major as they lie in the caller's arrays
   const size_t stage_budget = (size_t)256 << 20;
@@ -249,8 +253,8 @@ extern "C" int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, 
     if (e == cudaSuccess)
       e = cudaMemcpy2DAsync(stgY, rows * sizeof(double), Y + i0, ldY * sizeof(double), rows * sizeof(double), (size_t)q,
                             cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = launch_retile(stgX, rows, rows, (int)p, d->D, d->s.ld, 0, i0, ctx->stream);
-    if (e == cudaSuccess) e = launch_retile(stgY, rows, rows, (int)q, d->D, d->s.ld, d->s.p2, i0, ctx->stream);
+    if (e == cudaSuccess) e = launch_retile(stgX, rows, rows, (int)p, d->D, d->s, 0, i0, ctx->stream);
+    if (e == cudaSuccess) e = launch_retile(stgY, rows, rows, (int)q, d->D, d->s, d->s.p2, i0, ctx->stream);
   }
   if (e == cudaSuccess) e = launch_zero_pad(d->D, d->s, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
@@ -291,8 +295,9 @@ extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64
   d->ctx = ctx;
   rc = shape_init(&d->s, n, p, q);
   if (rc) { delete d; return rc; }
-  cudaError_t e = cudaMalloc(&d->D, (size_t)n * d->s.ld * sizeof(double));
+  cudaError_t e = cudaMalloc(&d->D, data_elems(d->s) * sizeof(double));
   if (e != cudaSuccess) { delete d; return fail(PPLS_E_OOM, std::string("device allocation of the data shard: ") + cudaGetErrorString(e)); }
+  if (d->s.panel) cudaMemsetAsync(d->D, 0, data_elems(d->s) * sizeof(double), ctx->stream);
   std::vector<double> L;
   pack_loadings(d->s, r, truth->W, truth->C, L);
   double *dL = nullptr, *dbt = nullptr;
@@ -331,8 +336,8 @@ extern "C" int ppls_data_export(ppls_ctx* ctx, const ppls_data* d, int64_t row0,
   for (int64_t i0 = 0; i0 < n && e == cudaSuccess; i0 += cr) {
     const int64_t rows = (n - i0 < cr) ? (n - i0) : cr;
     double* sX = stg; double* sY = stg + (size_t)cr * p;
-    e = launch_untile(d->D, d->s.ld, 0, row0 + i0, rows, p, sX, rows, ctx->stream);
-    if (e == cudaSuccess) e = launch_untile(d->D, d->s.ld, d->s.p2, row0 + i0, rows, q, sY, rows, ctx->stream);
+    e = launch_untile(d->D, d->s, 0, row0 + i0, rows, p, sX, rows, ctx->stream);
+    if (e == cudaSuccess) e = launch_untile(d->D, d->s, d->s.p2, row0 + i0, rows, q, sY, rows, ctx->stream);
     if (e == cudaSuccess)
       e = cudaMemcpy2DAsync(X + i0, ldX * sizeof(double), sX, rows * sizeof(double), rows * sizeof(double), (size_t)p,
                             cudaMemcpyDeviceToHost, ctx->stream);

@@ -21,7 +21,23 @@ struct DataShape {
   int32_t p, q;     // logical columns
   int32_t p2, q2;   // padded (even)
   int32_t ld;       // p2 + q2
+  // Wide shapes (ld > PANEL_LD_MIN) are stored PANEL-MAJOR instead: the padded column space is cut into
+  // panels of PANEL_W columns (X panels, then Y panels; the last panel of each is zero-padded) and
+  // D[panel][n][PANEL_W] -- a CTA of the wide-row path then streams ONE contiguous 1 KB x n block.
+  int32_t panel, npX, npY;
 };
+constexpr int PANEL_W = 128;
+constexpr int PANEL_LD_MIN = 2304;
+__host__ __device__ inline size_t data_index(const DataShape& s, int64_t i, int c) {
+  if (!s.panel) return (size_t)i * s.ld + c;
+  const int cy = c - s.p2;
+  const int P = (c < s.p2) ? c / PANEL_W : s.npX + cy / PANEL_W;
+  const int j = (c < s.p2) ? c % PANEL_W : cy % PANEL_W;
+  return ((size_t)P * s.n + i) * PANEL_W + j;
+}
+__host__ __device__ inline size_t data_elems(const DataShape& s) {
+  return s.panel ? (size_t)(s.npX + s.npY) * s.n * PANEL_W : (size_t)s.n * s.ld;
+}
 
 // Layout of the per-CTA partial vector and of the reduced vector ("moment vector"):
 //   [ G (ld x R, row-major: G1 rows then G2 rows) | Gxx (R x R) | Gxy (R x R) | Gyy (R x R) ]
@@ -101,8 +117,8 @@ cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitSta
 
 // data.cu
 cudaError_t launch_retile(const double* colmajor, int64_t ldc, int64_t nrows, int ncols,
-                          double* D, int ld, int col0, int64_t row0, cudaStream_t stream);
-cudaError_t launch_untile(const double* D, int ld, int col0, int64_t row0, int64_t nrows, int ncols,
+                          double* D, const DataShape& s, int col0, int64_t row0, cudaStream_t stream);
+cudaError_t launch_untile(const double* D, const DataShape& s, int col0, int64_t row0, int64_t nrows, int ncols,
                           double* colmajor, int64_t ldc, cudaStream_t stream);
 cudaError_t launch_zero_pad(double* D, const DataShape& s, cudaStream_t stream);
 cudaError_t launch_ssq(const double* D, const DataShape& s, double* out2, double* scratch, int nblocks,

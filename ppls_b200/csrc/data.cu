@@ -10,7 +10,7 @@ namespace ppls {
 // ---- column-major (R) -> row-major shard ---------------------------------------------------
 // src: nrows x ncols column-major with leading dimension lds; dst rows row0.., columns col0..
 __global__ void retile_kernel(const double* __restrict__ src, int64_t lds, int64_t nrows, int ncols,
-                              double* __restrict__ D, int ld, int col0, int64_t row0) {
+                              double* __restrict__ D, const DataShape s, int col0, int64_t row0) {
   __shared__ double tile[32][33];
   const int64_t rb = (int64_t)blockIdx.x * 32;
   const int cb = blockIdx.y * 32;
@@ -23,11 +23,11 @@ __global__ void retile_kernel(const double* __restrict__ src, int64_t lds, int64
   for (int r = threadIdx.y; r < 32; r += 8) {   // coalesced along columns of the row-major shard
     const int64_t i = rb + r;
     const int j = cb + threadIdx.x;
-    if (i < nrows && j < ncols) D[(size_t)(row0 + i) * ld + col0 + j] = tile[threadIdx.x][r];
+    if (i < nrows && j < ncols) D[data_index(s, row0 + i, col0 + j)] = tile[threadIdx.x][r];
   }
 }
 
-__global__ void untile_kernel(const double* __restrict__ D, int ld, int col0, int64_t row0, int64_t nrows,
+__global__ void untile_kernel(const double* __restrict__ D, const DataShape s, int col0, int64_t row0, int64_t nrows,
                               int ncols, double* __restrict__ dst, int64_t ldd) {
   __shared__ double tile[32][33];
   const int64_t rb = (int64_t)blockIdx.x * 32;
@@ -35,7 +35,7 @@ __global__ void untile_kernel(const double* __restrict__ D, int ld, int col0, in
   for (int r = threadIdx.y; r < 32; r += 8) {
     const int64_t i = rb + r;
     const int j = cb + threadIdx.x;
-    tile[r][threadIdx.x] = (i < nrows && j < ncols) ? D[(size_t)(row0 + i) * ld + col0 + j] : 0.0;
+    tile[r][threadIdx.x] = (i < nrows && j < ncols) ? D[data_index(s, row0 + i, col0 + j)] : 0.0;
   }
   __syncthreads();
   for (int c = threadIdx.y; c < 32; c += 8) {
@@ -45,23 +45,23 @@ __global__ void untile_kernel(const double* __restrict__ D, int ld, int col0, in
   }
 }
 
-cudaError_t launch_retile(const double* colmajor, int64_t ldc, int64_t nrows, int ncols, double* D, int ld,
+cudaError_t launch_retile(const double* colmajor, int64_t ldc, int64_t nrows, int ncols, double* D, const DataShape& s,
                           int col0, int64_t row0, cudaStream_t stream) {
   if (nrows <= 0 || ncols <= 0) return cudaSuccess;
   const int64_t gx = (nrows + 31) / 32, gy = (ncols + 31) / 32;
   if (gy > 65535) return cudaErrorInvalidValue;
   dim3 grid((unsigned)gx, (unsigned)gy), block(32, 8);
-  retile_kernel<<<grid, block, 0, stream>>>(colmajor, ldc, nrows, ncols, D, ld, col0, row0);
+  retile_kernel<<<grid, block, 0, stream>>>(colmajor, ldc, nrows, ncols, D, s, col0, row0);
   return cudaGetLastError();
 }
 
-cudaError_t launch_untile(const double* D, int ld, int col0, int64_t row0, int64_t nrows, int ncols,
+cudaError_t launch_untile(const double* D, const DataShape& s, int col0, int64_t row0, int64_t nrows, int ncols,
                           double* colmajor, int64_t ldc, cudaStream_t stream) {
   if (nrows <= 0 || ncols <= 0) return cudaSuccess;
   const int64_t gx = (nrows + 31) / 32, gy = (ncols + 31) / 32;
   if (gy > 65535) return cudaErrorInvalidValue;
   dim3 grid((unsigned)gx, (unsigned)gy), block(32, 8);
-  untile_kernel<<<grid, block, 0, stream>>>(D, ld, col0, row0, nrows, ncols, colmajor, ldc);
+  untile_kernel<<<grid, block, 0, stream>>>(D, s, col0, row0, nrows, ncols, colmajor, ldc);
   return cudaGetLastError();
 }
 
@@ -73,19 +73,19 @@ __global__ void zero_pad_kernel(double* D, int64_t n, int ld, int p, int p2, int
   if (q2 != q) D[(size_t)i * ld + p2 + q] = 0.0;
 }
 cudaError_t launch_zero_pad(double* D, const DataShape& s, cudaStream_t stream) {
-  if (s.p2 == s.p && s.q2 == s.q) return cudaSuccess;
+  if (s.panel || (s.p2 == s.p && s.q2 == s.q)) return cudaSuccess;   // panel-major storage is zero-filled up front
   zero_pad_kernel<<<(unsigned)((s.n + 255) / 256), 256, 0, stream>>>(D, s.n, s.ld, s.p, s.p2, s.q, s.q2);
   return cudaGetLastError();
 }
 
 // ---- ||X||_F^2, ||Y||_F^2 -------------------------------------------------------------------
-__global__ void ssq_partial_kernel(const double* __restrict__ D, int64_t n, int ld, int p2,
+__global__ void ssq_partial_kernel(const double* __restrict__ D, const DataShape s,
                                    double* __restrict__ scratch /*[grid][2]*/) {
+  const int64_t n = s.n; const int ld = s.ld, p2 = s.p2;
   double sx = 0.0, sy = 0.0;
   for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
-    const double* row = D + (size_t)i * ld;
     for (int j = threadIdx.x; j < ld; j += blockDim.x) {
-      const double v = row[j];
+      const double v = D[data_index(s, i, j)];
       if (j < p2) sx += v * v; else sy += v * v;
     }
   }
@@ -112,7 +112,7 @@ __global__ void ssq_final_kernel(const double* scratch, int nblocks, double* out
 }
 cudaError_t launch_ssq(const double* D, const DataShape& s, double* out2, double* scratch, int nblocks,
                        cudaStream_t stream) {
-  ssq_partial_kernel<<<nblocks, 256, 0, stream>>>(D, s.n, s.ld, s.p2, scratch);
+  ssq_partial_kernel<<<nblocks, 256, 0, stream>>>(D, s, scratch);
   ssq_final_kernel<<<1, 32, 0, stream>>>(scratch, nblocks, out2);
   return cudaGetLastError();
 }
@@ -205,12 +205,13 @@ __device__ __forceinline__ double gen_normal(uint64_t seed, uint32_t stream, uin
 }
 
 constexpr int SYN_ROWS = 8;
-__global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, int64_t n, int64_t row0, int ld,
-                                                    int p, int p2, int q, int R, uint64_t seed,
+__global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, const DataShape s, int64_t row0,
+                                                    int R, uint64_t seed,
                                                     const double* __restrict__ Lt, const double* __restrict__ b,
                                                     const double* __restrict__ t, double sigE, double sigF,
                                                     double sigH) {
   __shared__ double Ts[SYN_ROWS][MAXR], Us[SYN_ROWS][MAXR];
+  const int64_t n = s.n; const int ld = s.ld, p = s.p, p2 = s.p2, q = s.q;
   const int64_t ngroups = (n + SYN_ROWS - 1) / SYN_ROWS;
   for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
     const int64_t i0 = g * SYN_ROWS;
@@ -227,7 +228,6 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, int6
     __syncthreads();
     for (int i = 0; i < SYN_ROWS && i0 + i < n; ++i) {
       const uint64_t row = (uint64_t)(row0 + i0 + i);
-      double* out = D + (size_t)(i0 + i) * ld;
       for (int j = threadIdx.x; j < ld; j += blockDim.x) {
         double v = 0.0;
         if (j < p) {
@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, int6
           for (int k = 0; k < R; ++k) acc = acc + Us[i][k] * Lt[(size_t)j * R + k];
           v = acc + sigF * gen_normal(seed, 3u, row, (uint32_t)(j - p2));
         }
-        out[j] = v;
+        D[data_index(s, i0 + i, j)] = v;
       }
     }
   }
@@ -250,7 +250,7 @@ cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, int R, uin
                          cudaStream_t stream) {
   int64_t ngroups = (s.n + SYN_ROWS - 1) / SYN_ROWS;
   int grid = (int)(ngroups < 148 * 8 ? (ngroups < 1 ? 1 : ngroups) : 148 * 8);
-  synth_kernel<<<grid, 256, 0, stream>>>(D, s.n, row0, s.ld, s.p, s.p2, s.q, R, seed, Ltruth, b, t, sigE, sigF, sigH);
+  synth_kernel<<<grid, 256, 0, stream>>>(D, s, row0, R, seed, Ltruth, b, t, sigE, sigF, sigH);
   return cudaGetLastError();
 }
 

@@ -47,6 +47,7 @@ static bool split_chunks(int chX, int chY, int nw, StreamPlan* p) {
 cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* plan, const char** why) {
   *why = "";
   if (R < 1 || R > MAXR) { *why = "nr_comp outside 1..8"; return cudaErrorInvalidValue; }
+  if (s.panel) { *why = "panel-major (wide) data layout"; return cudaErrorInvalidValue; }
   const int chX = (s.p2 / 2 + 31) / 32, chY = (s.q2 / 2 + 31) / 32;
   const size_t smem_max = 227 * 1024;  // usable dynamic shared memory per CTA (1 CTA per SM)
   const int envT = env_int("PPLS_K1_T", 0), envW = env_int("PPLS_K1_WARPS", 0), envS = env_int("PPLS_K1_STAGES", 0);

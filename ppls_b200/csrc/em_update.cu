@@ -537,7 +537,9 @@ __device__ void grid_partial_gram(const double* A, int row_lo, int row_hi, int r
   double v[NV];
 #pragma unroll
   for (int e = 0; e < NV; ++e) v[e] = 0.0;
-  for (int j = row_lo + rb * GT + threadIdx.x; j < row_hi; j += nb * GT) {
+  // same thread <-> row mapping as the loops that WRITE the rows in the same phase (no grid sync between)
+  for (int j = rb * GT + threadIdx.x; j < row_hi; j += nb * GT) {
+    if (j < row_lo) continue;
     double row[R];
 #pragma unroll
     for (int k = 0; k < R; ++k) row[k] = A[(size_t)j * R + k];

@@ -26,6 +26,7 @@ struct WideArgs {
   double* gpart;            // [nrg][ld][R]    (pass 2 out)
   int64_t n, npad;          // npad: n rounded up to the tile height (stride of the mu arrays)
   int32_t ld, p2, q2, scX, scY, nslabX, nslabY, nrg, rows_per_rg, nstage;
+  int32_t panel;            // panel-major storage: slab = one panel, a tile is one contiguous block
 };
 
 // Transposing butterfly: on entry every lane holds NV values; on exit value index
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
   const int64_t rbeg = (int64_t)rg * a.rows_per_rg;
   const int64_t rend = (rbeg + a.rows_per_rg < a.n) ? rbeg + a.rows_per_rg : a.n;
   const int ntile = (int)((rend - rbeg + WIDE_TR - 1) / WIDE_TR);
-  const uint32_t segbytes = (uint32_t)width * 8u;
+  const uint32_t segbytes = a.panel ? PANEL_W * 8u : (uint32_t)width * 8u;   // a panel is stored whole (zero-padded)
   const uint32_t pitch = (uint32_t)NCH * 64u * 8u;                            // smem row pitch (bytes)
   const uint32_t mubytes = (MODE == MODE_ACCUM) ? WIDE_TR * R * 8u : 0u;
   const uint32_t stage_bytes = WIDE_TR * pitch + mubytes;
@@ -94,8 +95,12 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
         const int rows = (int)((rend - row0 < WIDE_TR) ? (rend - row0) : WIDE_TR);
         const uint32_t full = bars + 8u * s, dst = sbase + s * stage_bytes;
         mbar_expect_tx(full, (uint32_t)rows * segbytes + mubytes);
-        for (int i = 0; i < rows; ++i)
-          bulk_g2s(dst + (uint32_t)i * pitch, a.D + (size_t)(row0 + i) * a.ld + cbeg, segbytes, full);
+        if (a.panel) {
+          bulk_g2s(dst, a.D + ((size_t)slab * a.n + row0) * PANEL_W, (uint32_t)rows * segbytes, full);
+        } else {
+          for (int i = 0; i < rows; ++i)
+            bulk_g2s(dst + (uint32_t)i * pitch, a.D + (size_t)(row0 + i) * a.ld + cbeg, segbytes, full);
+        }
         if (MODE == MODE_ACCUM)
           bulk_g2s(dst + WIDE_TR * pitch, a.mu + (isY ? (size_t)a.npad * R : 0) + (size_t)row0 * R, mubytes, full);   // whole tile: the arrays are padded
         if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
@@ -307,31 +312,42 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
   *why = "";
   const int nch_cap = (24 / R) < 8 ? (24 / R) : 8;                 // register budget: NCH * R <= 24
   const int allowed[6] = {1, 2, 3, 4, 6, 8};
-  int nch_max = 1;
-  for (int c : allowed) if (c <= nch_cap) nch_max = c;
-  const int sc_max = nch_max * 64;
-  const int64_t cols = (int64_t)s.p2 + s.q2;
-  int waves = (int)((cols + (int64_t)sm_count * sc_max - 1) / ((int64_t)sm_count * sc_max));
-  if (waves < 1) waves = 1;
-  int target = sm_count * waves;
-  if (target > cols / 2) target = (int)(cols / 2);
-  int nY = (int)((double)target * s.q2 / (double)cols + 0.5);
-  if (nY < 1) nY = 1;
-  if (nY > s.q2 / 2) nY = s.q2 / 2;
-  int nX = target - nY;
-  if (nX < 1) nX = 1;
-  if (nX > s.p2 / 2) nX = s.p2 / 2;
-  w->scX = 2 * ((s.p2 / 2 + nX - 1) / nX); w->nslabX = (s.p2 + w->scX - 1) / w->scX;
-  w->scY = 2 * ((s.q2 / 2 + nY - 1) / nY); w->nslabY = (s.q2 + w->scY - 1) / w->scY;
-  const int scm = w->scX > w->scY ? w->scX : w->scY;
-  if (scm > sc_max) { *why = "wide path: column slab exceeds the register budget"; return cudaErrorInvalidValue; }
-  w->NCH = 8;
-  for (int i = 5; i >= 0; --i) if (allowed[i] * 64 >= scm) w->NCH = allowed[i];
+  int slots = sm_count;                                              // CTAs resident at once
+  if (s.panel) {
+    // panel-major storage: one slab per stored panel (PANEL_W = 128 columns, NCH = 2)
+    w->scX = w->scY = PANEL_W; w->nslabX = s.npX; w->nslabY = s.npY; w->NCH = PANEL_W / 64;
+    slots = 2 * sm_count;
+  } else {
+    int nch_max = 1;
+    for (int c : allowed) if (c <= nch_cap) nch_max = c;
+    const int sc_max = nch_max * 64;
+    const int64_t cols = (int64_t)s.p2 + s.q2;
+    int waves = (int)((cols + (int64_t)sm_count * sc_max - 1) / ((int64_t)sm_count * sc_max));
+    if (waves < 1) waves = 1;
+    int target = sm_count * waves;
+    if (target > cols / 2) target = (int)(cols / 2);
+    int nY = (int)((double)target * s.q2 / (double)cols + 0.5);
+    if (nY < 1) nY = 1;
+    if (nY > s.q2 / 2) nY = s.q2 / 2;
+    int nX = target - nY;
+    if (nX < 1) nX = 1;
+    if (nX > s.p2 / 2) nX = s.p2 / 2;
+    w->scX = 2 * ((s.p2 / 2 + nX - 1) / nX); w->nslabX = (s.p2 + w->scX - 1) / w->scX;
+    w->scY = 2 * ((s.q2 / 2 + nY - 1) / nY); w->nslabY = (s.q2 + w->scY - 1) / w->scY;
+    const int scm = w->scX > w->scY ? w->scX : w->scY;
+    if (scm > sc_max) { *why = "wide path: column slab exceeds the register budget"; return cudaErrorInvalidValue; }
+    w->NCH = 8;
+    for (int i = 5; i >= 0; --i) if (allowed[i] * 64 >= scm) w->NCH = allowed[i];
+  }
+  // row groups: fill the resident-CTA slots in whole waves (each group keeps >= 4 tiles of rows)
   const int nslab = w->nslabX + w->nslabY;
-  int nrg = (sm_count + nslab - 1) / nslab;
   const int64_t max_rg = (s.n + 4 * WIDE_TR - 1) / (4 * WIDE_TR);
-  if (nrg > max_rg) nrg = (int)max_rg;
-  if (nrg < 1) nrg = 1;
+  int nrg = 1; double best_eff = -1.0;
+  for (int c = 1; c <= 12 && c <= max_rg; ++c) {
+    const int64_t ctas = (int64_t)nslab * c;
+    const double eff = (double)ctas / (double)(((ctas + slots - 1) / slots) * slots) - 0.004 * (c - 1);
+    if (eff > best_eff) { best_eff = eff; nrg = c; }
+  }
   w->rows_per_rg = (int)(((s.n + nrg - 1) / nrg + WIDE_TR - 1) / WIDE_TR * WIDE_TR);
   w->nrg = (int)((s.n + w->rows_per_rg - 1) / w->rows_per_rg);
   w->R = R;
@@ -370,7 +386,7 @@ cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const dou
   WideArgs a{};
   a.D = D; a.L = L; a.st = st; a.ppart = ws + o.ppart; a.mu = ws + o.mu; a.gpart = ws + o.gpart;
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.q2 = s.q2; a.scX = w.scX; a.scY = w.scY; a.nslabX = w.nslabX;
-  a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage;
+  a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage; a.panel = s.panel;
   dim3 grid(w.nslabX + w.nslabY, w.nrg);
   wide_lookup(w.R, w.NCH, MODE_PROJECT)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_PROJECT), stream>>>(a);
   const int64_t ne = s.n * w.R;
@@ -386,7 +402,7 @@ cudaError_t launch_wide_accum(const WidePlan& w, const DataShape& s, const doubl
   WideArgs a{};
   a.D = D; a.L = L; a.st = st; a.ppart = ws + o.ppart; a.mu = ws + o.mu; a.gpart = ws + o.gpart;
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.q2 = s.q2; a.scX = w.scX; a.scY = w.scY; a.nslabX = w.nslabX;
-  a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage;
+  a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage; a.panel = s.panel;
   dim3 grid(w.nslabX + w.nslabY, w.nrg);
   wide_lookup(w.R, w.NCH, MODE_ACCUM)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_ACCUM), stream>>>(a);
   const int64_t glen = (int64_t)s.ld * w.R; const int glen2 = 3 * w.R * w.R;

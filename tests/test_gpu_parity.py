@@ -134,9 +134,12 @@ def test_error_behaviour(ctx):
 
 
 @pytest.mark.parametrize("name", ["c1_wellcond_1000", "r5_odd_shapes", "r3_qr", "r8_max", "r1_p_lt_q", "r3_wide_row"])
-def test_golden_through_the_wide_path(ctx, name, monkeypatch):
-    """The two-pass wide-row path (em_wide.cu) forced on the golden cases: same bar as the fused kernel."""
+@pytest.mark.parametrize("panel", ["0", "1"])
+def test_golden_through_the_wide_path(ctx, name, panel, monkeypatch):
+    """The two-pass wide-row path (em_wide.cu) forced on the golden cases, with row-major and with
+    panel-major storage: same bar as the fused kernel."""
     monkeypatch.setenv("PPLS_FORCE_WIDE", "1")
+    monkeypatch.setenv("PPLS_PANEL", panel)
     g = load_golden(name)
     res = _run(ctx, g["X"], g["Y"], init_of(g), int(g["r"]), int(g["EMsteps"]), float(g["atol"]), str(g["type"]))
     _compare(res, g, name)
