@@ -110,6 +110,16 @@ int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, const doubl
  * any sharding).  `truth` holds the generating parameters with r components. */
 int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
                         uint64_t seed, const ppls_params* truth, ppls_data** out);
+/* Column-sharded variants (wide shapes, p >> N): every rank holds ALL n rows of a block of
+ * p_local columns of X and q_local columns of Y (blocks in rank order).  Start values / estimates passed
+ * to ppls_fit_* are then the rank's ROWS of W (p_local x r) and C (q_local x r); per EM iteration the
+ * ranks exchange the n x 2r projection sums and the (p+q) x r moment rows.  colX0 / colY0: global index
+ * of the block's first column (counter of the generator); truth_local: the block's rows of W, C. */
+int ppls_data_from_host_cols(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
+                             int64_t n, int64_t p_local, int64_t q_local, ppls_data** out);
+int ppls_data_synthetic_cols(ppls_ctx* ctx, int64_t n, int64_t p_local, int64_t q_local, int64_t colX0,
+                             int64_t colY0, int32_t r, uint64_t seed, const ppls_params* truth_local,
+                             ppls_data** out);
 /* Copy rows row0 .. row0+n-1 (local numbering) back to column-major host arrays. */
 int ppls_data_export(ppls_ctx* ctx, const ppls_data* d, int64_t row0, int64_t n,
                      double* X, int64_t ldX, double* Y, int64_t ldY);

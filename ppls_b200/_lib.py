@@ -55,6 +55,9 @@ SIGNATURES = {
     "ppls_data_from_host": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _vpp]),
     "ppls_data_synthetic": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_uint64,
                                       C.POINTER(Params), _vpp]),
+    "ppls_data_from_host_cols": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _vpp]),
+    "ppls_data_synthetic_cols": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_uint64,
+                                           C.POINTER(Params), _vpp]),
     "ppls_data_export": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, _vp, C.c_int64, _vp, C.c_int64]),
     "ppls_data_info": (C.c_int, [_vp, _i64p, _i64p, _i64p, _i64p, c_double_p, c_double_p]),
     "ppls_data_destroy": (C.c_int, [_vp]),

@@ -127,6 +127,28 @@ class Data:
         L.check(L.lib().ppls_data_synthetic(ctx._h, n, row0, p, q, r, seed, C.byref(pb.struct), C.byref(h)))
         return cls(ctx, h)
 
+    @classmethod
+    def from_host_cols(cls, ctx: Context, X_block, Y_block) -> "Data":
+        """Column-sharded: this rank's column block of X and of Y (all rows); wide shapes, p >> N."""
+        Xf, Yf = _f64(np.asarray(X_block)), _f64(np.asarray(Y_block))
+        if Xf.ndim != 2 or Yf.ndim != 2 or Xf.shape[0] != Yf.shape[0]:
+            raise ValueError("X and Y blocks must be matrices with the same number of rows")
+        n, p = Xf.shape; q = Yf.shape[1]
+        h = C.c_void_p()
+        L.check(L.lib().ppls_data_from_host_cols(ctx._h, Xf.ctypes.data, max(n, 1), Yf.ctypes.data, max(n, 1), n, p, q, C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def synthetic_cols(cls, ctx: Context, n: int, truth: dict, seed: int, colsX: slice, colsY: slice) -> "Data":
+        """Column block [colsX] of X and [colsY] of Y of the synthetic sample (same bits as the row generator)."""
+        W = np.asarray(truth["W"])[colsX]; Cm = np.asarray(truth["C"])[colsY]
+        r = W.shape[1]
+        pb = _ParamsBuf(W.shape[0], Cm.shape[0], r, W, Cm, truth["B"], truth["sigT"], truth["sigE"], truth["sigF"], truth["sigH"])
+        h = C.c_void_p()
+        L.check(L.lib().ppls_data_synthetic_cols(ctx._h, n, W.shape[0], Cm.shape[0], colsX.start, colsY.start, r, seed,
+                                                 C.byref(pb.struct), C.byref(h)))
+        return cls(ctx, h)
+
     def export(self, row0: int = 0, n: Optional[int] = None):
         n = self.n - row0 if n is None else n
         X = np.empty((n, self.p), order="F"); Y = np.empty((n, self.q), order="F")

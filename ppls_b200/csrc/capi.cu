@@ -80,6 +80,10 @@ struct ppls_data {
   double* D = nullptr;
   double ssq[2] = {0, 0};      // global
   int64_t n_total = 0;         // global
+  // column-sharded mode (wide shapes): this rank holds ALL rows of a column block of X and of Y
+  int colshard = 0;
+  int64_t p_glob = 0, q_glob = 0;          // global logical column counts
+  std::vector<int32_t> xoff, yoff;         // [world+1] cumulative padded (p2 / q2) widths of the ranks' blocks
 };
 
 static int ctx_activate(const ppls_ctx* ctx) {
@@ -216,11 +220,47 @@ static int data_finalize(ppls_ctx* ctx, ppls_data* d) {
   cudaFree(scratch);
   if (rc) return rc;
   d->ssq[0] = h[0]; d->ssq[1] = h[1]; d->n_total = (int64_t)llround(h[2]);
+  d->p_glob = d->s.p; d->q_glob = d->s.q;
+  if (d->colshard) {
+    // every rank holds all rows: N is not summed; the ranks' block widths are exchanged once
+    d->n_total = d->s.n;
+    const int W = ctx->world;
+    std::vector<double> hw((size_t)4 * W, 0.0);
+    hw[4 * ctx->rank + 0] = d->s.p; hw[4 * ctx->rank + 1] = d->s.q; hw[4 * ctx->rank + 2] = d->s.p2; hw[4 * ctx->rank + 3] = d->s.q2;
+    double* dw = nullptr;
+    CU(cudaMalloc(&dw, hw.size() * sizeof(double)));
+    e = cudaMemcpyAsync(dw, hw.data(), hw.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+    rc = (e == cudaSuccess) ? allreduce_sum(ctx, dw, hw.size()) : fail(PPLS_E_CUDA, cudaGetErrorString(e));
+    if (!rc) {
+      e = cudaMemcpyAsync(hw.data(), dw, hw.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      if (e != cudaSuccess) rc = fail(PPLS_E_CUDA, std::string("block-width exchange: ") + cudaGetErrorString(e));
+    }
+    cudaFree(dw);
+    if (rc) return rc;
+    d->xoff.assign(W + 1, 0); d->yoff.assign(W + 1, 0);
+    d->p_glob = 0; d->q_glob = 0;
+    for (int g = 0; g < W; ++g) {
+      d->p_glob += (int64_t)llround(hw[4 * g + 0]); d->q_glob += (int64_t)llround(hw[4 * g + 1]);
+      d->xoff[g + 1] = d->xoff[g] + (int32_t)llround(hw[4 * g + 2]);
+      d->yoff[g + 1] = d->yoff[g] + (int32_t)llround(hw[4 * g + 3]);
+    }
+  }
   return PPLS_OK;
 }
 
+static int data_from_host_impl(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
+                               int64_t n, int64_t p, int64_t q, int colshard, ppls_data** out);
 extern "C" int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
                                    int64_t n, int64_t p, int64_t q, ppls_data** out) {
+  return data_from_host_impl(ctx, X, ldX, Y, ldY, n, p, q, 0, out);
+}
+extern "C" int ppls_data_from_host_cols(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
+                                        int64_t n, int64_t p_local, int64_t q_local, ppls_data** out) {
+  return data_from_host_impl(ctx, X, ldX, Y, ldY, n, p_local, q_local, 1, out);
+}
+static int data_from_host_impl(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
+                               int64_t n, int64_t p, int64_t q, int colshard, ppls_data** out) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   *out = nullptr;
   int rc = ctx_activate(ctx);
@@ -229,7 +269,7 @@ extern "C" int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, 
   if (ldX < n || ldY < n) return fail(PPLS_E_INVALID, "leading dimension smaller than the row count");
   ppls_data* d = new (std::nothrow) ppls_data();
   if (!d) return fail(PPLS_E_OOM, "host allocation failed");
-  d->ctx = ctx;
+  d->ctx = ctx; d->colshard = colshard;
   rc = shape_init(&d->s, n, p, q);
   if (rc) { delete d; return rc; }
   const size_t bytes = data_elems(d->s) * sizeof(double);
@@ -280,8 +320,19 @@ static int check_params(const ppls_params* P, const char* what) {
   return PPLS_OK;
 }
 
+static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int64_t colX0, int64_t colY0,
+                               int colshard, int32_t r, uint64_t seed, const ppls_params* truth, ppls_data** out);
 extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
                                    uint64_t seed, const ppls_params* truth, ppls_data** out) {
+  return data_synthetic_impl(ctx, n, row0, p, q, 0, 0, 0, r, seed, truth, out);
+}
+extern "C" int ppls_data_synthetic_cols(ppls_ctx* ctx, int64_t n, int64_t p_local, int64_t q_local, int64_t colX0,
+                                        int64_t colY0, int32_t r, uint64_t seed, const ppls_params* truth_local,
+                                        ppls_data** out) {
+  return data_synthetic_impl(ctx, n, 0, p_local, q_local, colX0, colY0, 1, r, seed, truth_local, out);
+}
+static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int64_t colX0, int64_t colY0,
+                               int colshard, int32_t r, uint64_t seed, const ppls_params* truth, ppls_data** out) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   *out = nullptr;
   int rc = ctx_activate(ctx);
@@ -289,10 +340,10 @@ extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64
   rc = check_params(truth, "truth");
   if (rc) return rc;
   if (r < 1 || r > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
-  if (row0 < 0) return fail(PPLS_E_INVALID, "negative row offset");
+  if (row0 < 0 || colX0 < 0 || colY0 < 0) return fail(PPLS_E_INVALID, "negative row / column offset");
   ppls_data* d = new (std::nothrow) ppls_data();
   if (!d) return fail(PPLS_E_OOM, "host allocation failed");
-  d->ctx = ctx;
+  d->ctx = ctx; d->colshard = colshard;
   rc = shape_init(&d->s, n, p, q);
   if (rc) { delete d; return rc; }
   cudaError_t e = cudaMalloc(&d->D, data_elems(d->s) * sizeof(double));
@@ -308,7 +359,7 @@ extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64
   if (e == cudaSuccess) e = cudaMemcpyAsync(dL, L.data(), L.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(dbt, bt, sizeof(bt), cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess)
-    e = launch_synth(d->D, d->s, row0, r, seed, dL, dbt, dbt + MAXR, truth->sigE, truth->sigF, truth->sigH, ctx->stream);
+    e = launch_synth(d->D, d->s, row0, (uint32_t)colX0, (uint32_t)colY0, r, seed, dL, dbt, dbt + MAXR, truth->sigE, truth->sigF, truth->sigH, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (dL) cudaFree(dL);
   if (dbt) cudaFree(dbt);
@@ -371,6 +422,25 @@ extern "C" int ppls_data_destroy(ppls_data* d) {
   return PPLS_OK;
 }
 
+// ---- column-sharded mode: local <-> global rows of the (p+q) x r objects -------------------------------
+// Global layout: [X rows of rank 0 .. rank W-1 | Y rows of rank 0 .. rank W-1] (padded widths).
+__global__ void rows_local_to_global(const double* __restrict__ loc, double* __restrict__ glob, int p2l, int q2l,
+                                     int xoff, int yoff_abs, int R) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (p2l + q2l) * R) return;
+  const int j = e / R, k = e - j * R;
+  const int gj = (j < p2l) ? xoff + j : yoff_abs + (j - p2l);
+  glob[(size_t)gj * R + k] = loc[e];
+}
+__global__ void rows_global_to_local(const double* __restrict__ glob, double* __restrict__ loc, int p2l, int q2l,
+                                     int xoff, int yoff_abs, int R) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= (p2l + q2l) * R) return;
+  const int j = e / R, k = e - j * R;
+  const int gj = (j < p2l) ? xoff + j : yoff_abs + (j - p2l);
+  loc[e] = glob[(size_t)gj * R + k];
+}
+
 // ---- one EM run -----------------------------------------------------------------------------------
 struct ppls_fit {
   ppls_ctx* ctx = nullptr;
@@ -382,6 +452,10 @@ struct ppls_fit {
   WideOffsets woff{};
   double* wide_ws = nullptr;
   double* upd_scratch = nullptr; // Gram partials of the grid update kernel
+  bool cols = false;             // column-sharded: the update runs replicated on the GLOBAL (p+q) x r objects
+  DataShape sg{};                // global shape (all ranks' column blocks)
+  double *Gglob = nullptr, *Lglob = nullptr, *Lscratch_g = nullptr;
+  int xoff = 0, yoff_abs = 0;    // first global row of this rank's X / Y block
   int R = 0;
   int64_t veclen = 0;
   double *L = nullptr, *Lscratch = nullptr, *partials = nullptr, *momvec = nullptr, *trace = nullptr;
@@ -400,7 +474,7 @@ static void fit_free(ppls_fit* f) {
   if (f->ctx) cudaSetDevice(f->ctx->device);
   for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto e : f->ev_free) cudaEventDestroy(e);
-  cudaFree(f->wide_ws); cudaFree(f->upd_scratch); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
+  cudaFree(f->wide_ws); cudaFree(f->upd_scratch); cudaFree(f->Gglob); cudaFree(f->Lglob); cudaFree(f->Lscratch_g); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
   cudaFree(f->st);
   if (f->st_host) cudaFreeHost(f->st_host);
   delete f;
@@ -418,15 +492,23 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   if (rc) return rc;
   const int R = opts->r;
   if (R < 1 || R > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
-  if (R > d->s.p || R > d->s.q) return fail(PPLS_E_INVALID, "nr_comp exceeds ncol(X) or ncol(Y)");
+  if (!d->colshard && (R > d->s.p || R > d->s.q)) return fail(PPLS_E_INVALID, "nr_comp exceeds ncol(X) or ncol(Y)");
   if (opts->max_steps < 0) return fail(PPLS_E_INVALID, "EMsteps must be >= 0");
   if (opts->orth_type != PPLS_ORTH_SVD && opts->orth_type != PPLS_ORTH_QR) return fail(PPLS_E_INVALID, "type must be SVD or QR");
   ppls_fit* f = new (std::nothrow) ppls_fit();
   if (!f) return fail(PPLS_E_OOM, "host allocation failed");
   f->ctx = ctx; f->data = d; f->opts = *opts; f->R = R;
   const char* why = "";
+  f->cols = d->colshard != 0;
+  if (f->cols) {
+    f->sg = d->s;
+    f->sg.p = (int32_t)d->p_glob; f->sg.q = (int32_t)d->q_glob;
+    f->sg.p2 = d->xoff[ctx->world]; f->sg.q2 = d->yoff[ctx->world]; f->sg.ld = f->sg.p2 + f->sg.q2;
+    f->xoff = d->xoff[ctx->rank]; f->yoff_abs = f->sg.p2 + d->yoff[ctx->rank];
+    if (R > d->p_glob || R > d->q_glob) { fit_free(f); return fail(PPLS_E_INVALID, "nr_comp exceeds ncol(X) or ncol(Y)"); }
+  }
   const char* force_wide = getenv("PPLS_FORCE_WIDE");
-  cudaError_t e = (force_wide && atoi(force_wide)) ? cudaErrorInvalidValue : plan_stream(d->s, R, ctx->sm_count, &f->plan, &why);
+  cudaError_t e = ((force_wide && atoi(force_wide)) || f->cols) ? cudaErrorInvalidValue : plan_stream(d->s, R, ctx->sm_count, &f->plan, &why);
   if (e != cudaSuccess) {
     // the row does not fit the fused kernel's shared-memory tile: two-pass wide-row path
     const std::string why1 = why;
@@ -443,7 +525,10 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
     e = cudaMalloc(&f->wide_ws, wide_workspace_doubles(d->s, f->wplan, &f->woff) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->momvec, (size_t)f->veclen * sizeof(double));
   if (e == cudaSuccess && !(getenv("PPLS_K2_SINGLE") && atoi(getenv("PPLS_K2_SINGLE"))))
-    e = cudaMalloc(&f->upd_scratch, update_grid_scratch_doubles(d->s.ld, R) * sizeof(double));
+    e = cudaMalloc(&f->upd_scratch, update_grid_scratch_doubles(f->cols ? f->sg.ld : d->s.ld, R) * sizeof(double));
+  if (e == cudaSuccess && f->cols) e = cudaMalloc(&f->Gglob, (size_t)momvec_len(f->sg.ld, R) * sizeof(double));
+  if (e == cudaSuccess && f->cols) e = cudaMalloc(&f->Lglob, (size_t)f->sg.ld * R * sizeof(double));
+  if (e == cudaSuccess && f->cols) e = cudaMalloc(&f->Lscratch_g, (size_t)f->sg.ld * R * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->trace, (size_t)(opts->max_steps + 1) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->st, sizeof(FitState));
   if (e == cudaSuccess) e = cudaMallocHost(&f->st_host, sizeof(FitState));
@@ -459,7 +544,14 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   e = cudaMemcpyAsync(f->L, L.data(), Lbytes, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(f->st, h, sizeof(FitState), cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(f->trace, 0, (size_t)(opts->max_steps + 1) * sizeof(double), ctx->stream);
-  if (e == cudaSuccess) e = launch_em_prepare(d->s, R, f->L, f->st, ctx->stream);
+  if (e == cudaSuccess && f->cols) {
+    // assemble the global start loadings (each rank contributes its rows; the rest are zeros)
+    e = cudaMemsetAsync(f->Lglob, 0, (size_t)f->sg.ld * R * sizeof(double), ctx->stream);
+    const int ne = d->s.ld * R;
+    if (e == cudaSuccess) rows_local_to_global<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->L, f->Lglob, d->s.p2, d->s.q2, f->xoff, f->yoff_abs, R);
+    if (e == cudaSuccess && allreduce_sum(ctx, f->Lglob, (size_t)f->sg.ld * R)) e = cudaErrorUnknown;
+    if (e == cudaSuccess) e = launch_em_prepare(f->sg, R, f->Lglob, f->st, ctx->stream);
+  } else if (e == cudaSuccess) e = launch_em_prepare(d->s, R, f->L, f->st, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // L (host vector) must outlive the copy
   if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_CUDA, std::string("fit setup: ") + cudaGetErrorString(e)); }
   f->tm.kernel_launches = 1;
@@ -511,6 +603,10 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
     cudaError_t e;
     if (f->wide) {
       e = launch_wide_project(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, ctx->stream);
+      if (e == cudaSuccess && f->cols) {      // column-sharded: the N x 2r projection sums are what ranks exchange
+        rc = allreduce_sum(ctx, f->wide_ws + f->woff.proj, (size_t)s.n * 2 * f->R);
+        if (rc) return rc;
+      }
       if (e == cudaSuccess) e = launch_wide_accum(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, f->momvec, ctx->stream);
       if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
       f->tm.kernel_launches += 3;      // 5 launches in this branch, 2 in the other; +3 more below
@@ -520,9 +616,27 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
       if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
     }
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
-    rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
-    if (rc) return rc;
-    e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
+    if (f->cols) {
+      // global G = every rank's rows (zeros elsewhere) summed; the Gram tail is identical on all ranks
+      // (it comes from the exchanged projections), so rank 0 alone contributes it
+      const int R_ = f->R, ne = s.ld * R_;
+      const size_t glen = (size_t)f->sg.ld * R_, tail = (size_t)3 * R_ * R_;
+      e = cudaMemsetAsync(f->Gglob, 0, (glen + tail) * sizeof(double), ctx->stream);
+      if (e == cudaSuccess) rows_local_to_global<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->momvec, f->Gglob, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
+      if (e == cudaSuccess && ctx->rank == 0)
+        e = cudaMemcpyAsync(f->Gglob + glen, f->momvec + (size_t)s.ld * R_, tail * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+      if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("column-sharded gather: ") + cudaGetErrorString(e));
+      rc = allreduce_sum(ctx, f->Gglob, glen + tail);
+      if (rc) return rc;
+      e = launch_em_update(f->sg, R_, f->Gglob, f->Lglob, f->Lscratch_g, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
+      if (e == cudaSuccess) rows_global_to_local<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->Lglob, f->L, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
+      if (e == cudaSuccess) e = cudaGetLastError();
+      f->tm.kernel_launches += 2;
+    } else {
+      rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
+      if (rc) return rc;
+      e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
+    }
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
     f->tm.kernel_launches += 3;
     f->passes += 1;

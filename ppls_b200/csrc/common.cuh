@@ -123,7 +123,7 @@ cudaError_t launch_untile(const double* D, const DataShape& s, int col0, int64_t
 cudaError_t launch_zero_pad(double* D, const DataShape& s, cudaStream_t stream);
 cudaError_t launch_ssq(const double* D, const DataShape& s, double* out2, double* scratch, int nblocks,
                        cudaStream_t stream);
-cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, int R, uint64_t seed,
+cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t colX0, uint32_t colY0, int R, uint64_t seed,
                          const double* Ltruth /*[ld][R]*/, const double* b, const double* t,
                          double sigE, double sigF, double sigH, cudaStream_t stream);
 

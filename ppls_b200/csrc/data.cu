@@ -206,7 +206,7 @@ __device__ __forceinline__ double gen_normal(uint64_t seed, uint32_t stream, uin
 
 constexpr int SYN_ROWS = 8;
 __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, const DataShape s, int64_t row0,
-                                                    int R, uint64_t seed,
+                                                    uint32_t cx0, uint32_t cy0, int R, uint64_t seed,
                                                     const double* __restrict__ Lt, const double* __restrict__ b,
                                                     const double* __restrict__ t, double sigE, double sigF,
                                                     double sigH) {
@@ -233,11 +233,11 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, cons
         if (j < p) {
           double acc = 0.0;
           for (int k = 0; k < R; ++k) acc = acc + Ts[i][k] * Lt[(size_t)j * R + k];
-          v = acc + sigE * gen_normal(seed, 2u, row, (uint32_t)j);
+          v = acc + sigE * gen_normal(seed, 2u, row, cx0 + (uint32_t)j);
         } else if (j >= p2 && j - p2 < q) {
           double acc = 0.0;
           for (int k = 0; k < R; ++k) acc = acc + Us[i][k] * Lt[(size_t)j * R + k];
-          v = acc + sigF * gen_normal(seed, 3u, row, (uint32_t)(j - p2));
+          v = acc + sigF * gen_normal(seed, 3u, row, cy0 + (uint32_t)(j - p2));
         }
         D[data_index(s, i0 + i, j)] = v;
       }
@@ -245,12 +245,12 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, cons
   }
 }
 
-cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, int R, uint64_t seed, const double* Ltruth,
+cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t colX0, uint32_t colY0, int R, uint64_t seed, const double* Ltruth,
                          const double* b, const double* t, double sigE, double sigF, double sigH,
                          cudaStream_t stream) {
   int64_t ngroups = (s.n + SYN_ROWS - 1) / SYN_ROWS;
   int grid = (int)(ngroups < 148 * 8 ? (ngroups < 1 ? 1 : ngroups) : 148 * 8);
-  synth_kernel<<<grid, 256, 0, stream>>>(D, s, row0, R, seed, Ltruth, b, t, sigE, sigF, sigH);
+  synth_kernel<<<grid, 256, 0, stream>>>(D, s, row0, colX0, colY0, R, seed, Ltruth, b, t, sigE, sigF, sigH);
   return cudaGetLastError();
 }
 

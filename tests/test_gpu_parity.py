@@ -197,3 +197,16 @@ def test_batched_multistart_matches_single_runs(ctx, oracle_lib, shape, S, steps
     assert out[0]["steps"] == o["steps"] and relmax(out[0]["loglik"], o["loglik"]) < 1e-10
     assert relmax(out[0]["loop_state"]["W"], o["W"]) < TOL_PARAM
     d.close()
+
+
+def test_column_sharded_two_gpus():
+    """Column-sharded wide path over 2 ranks (one process per GPU, NCCL inside the library) vs the oracle;
+    skipped on a 1-GPU box (tests/mgpu_colshard.py is the torchrun entry)."""
+    import os, subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29541", os.path.join(root, "tests", "mgpu_colshard.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "COLSHARD OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
