@@ -38,6 +38,7 @@ extern "C" {
 #define PPLS_E_OOM          -4   /* device or host allocation failed          */
 #define PPLS_E_NONFINITE    -5   /* a parameter became NaN/Inf during EM      */
 #define PPLS_E_UNSUPPORTED  -6   /* shape outside what the kernels cover      */
+#define PPLS_E_DEGENERATE   -7   /* a noise s.d. fell below 100*eps (EM_W_multi.R:153) */
 
 #define PPLS_MAX_R           8   /* nr_comp supported by the streaming kernel */
 #define PPLS_NCCL_ID_BYTES 128
@@ -154,6 +155,23 @@ int ppls_fit_destroy(ppls_fit* fit);
 int ppls_simult_run(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts,
                     const ppls_params* init, ppls_params* est, double* loglik,
                     int32_t* steps_done, double* moments, double* mu_T, double* mu_U);
+
+/* ---- sequential fit: the start-value path of PPLS_simult (EM_W_multi.R:762) ------------------------ */
+/* PPLS(X, Y, nr_comp, EMsteps, atol, initialGuess, customGuess) of EM_W_multi.R:229-279: components one at
+ * a time (PPLSi :116-180, EMstep_W :51-74, EMstepC_fast loglC.cpp:341-397), each on the data deflated by the
+ * earlier ones (:270-271, applied implicitly on the device).  critfunc = identity, no constraints.
+ * guesses: nr_comp start states with ONE component each (W p x 1, C q x 1, B[1], sigT[1], sigE, sigF, sigH);
+ * est: W p x nr_comp, C q x nr_comp, B[nr_comp], sigT[nr_comp] (+ sigE, sigF, sigH of the last component);
+ * sig: nr_comp x 4 column-major (sigX, sigY, sigH, sigT per component, the reference's `sig` matrix);
+ * logvalues: nr_comp x (EMsteps+1), row i = logvalue[0 .. steps[i]] (may be NULL); last_incr may be NULL;
+ * comps_done < nr_comp when a noise s.d. vanished (:153-155, :257-262: the earlier components are kept). */
+int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int32_t EMsteps, double atol,
+                        const ppls_params* guesses, ppls_params* est, double* sig, double* logvalues,
+                        int32_t* steps, double* last_incr, int32_t* comps_done);
+
+/* logl_W(X, Y, W, C, B, sigE, sigF, sigH, sigT) of EM_W_multi.R:296-326 (-> loglC_fast, loglC.cpp:318-338)
+ * for r components: one streaming pass over the resident data. */
+int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out);
 
 /* ---- batched multi-start: n_starts start states over one resident dataset ----------------- */
 /* Every start is an independent run of EM_W_multi.R:780-793 (its own break rule and trace); the

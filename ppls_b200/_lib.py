@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libppls_b200.so")
 
 PPLS_OK = 0
-PPLS_E_INVALID, PPLS_E_CUDA, PPLS_E_NCCL, PPLS_E_OOM, PPLS_E_NONFINITE, PPLS_E_UNSUPPORTED = -1, -2, -3, -4, -5, -6
+PPLS_E_INVALID, PPLS_E_CUDA, PPLS_E_NCCL, PPLS_E_OOM, PPLS_E_NONFINITE, PPLS_E_UNSUPPORTED, PPLS_E_DEGENERATE = -1, -2, -3, -4, -5, -6, -7
 PPLS_MAX_R = 8
 PPLS_NCCL_ID_BYTES = 128
 PPLS_ORTH_SVD, PPLS_ORTH_QR = 0, 1
@@ -66,6 +66,8 @@ SIGNATURES = {
     "ppls_fit_result": (C.c_int, [_vp, C.POINTER(Params), _vp, _i32p, _vp, _vp, _vp]),
     "ppls_fit_timing": (C.c_int, [_vp, C.POINTER(Timing)]),
     "ppls_fit_destroy": (C.c_int, [_vp]),
+    "ppls_sequential_run": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_double, _vp, C.POINTER(Params), _vp, _vp, _i32p, _vp, _i32p]),
+    "ppls_loglik": (C.c_int, [_vp, _vp, C.c_int32, C.POINTER(Params), _vp]),
     "ppls_simult_run_batched": (C.c_int, [_vp, _vp, C.POINTER(Opts), C.c_int32, _vp, _vp, _vp, _i32p, C.POINTER(Timing)]),
     "ppls_simult_run": (C.c_int, [_vp, _vp, C.POINTER(Opts), C.POINTER(Params), C.POINTER(Params), _vp, _i32p,
                                   _vp, _vp, _vp]),

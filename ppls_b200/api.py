@@ -17,7 +17,8 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["Context", "Data", "Fit", "PPLS_simult", "normalise", "default_init", "default_context"]
+__all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "normalise", "default_init",
+           "default_context"]
 
 
 def _f64(a, order="F"):
@@ -352,3 +353,88 @@ def PPLS_simult_batched(X, Y, a, inits, EMsteps=10, atol=1e-4, type="SVD", ctx: 
     if timing:
         return res, {k: getattr(tm, k) for k, _ in L.Timing._fields_}
     return res
+
+
+def _guess(p, q, kind, custom):
+    """Start state of one component (EM_W_multi.R:126-141): 'equal' or 'custom'."""
+    if kind == "custom" or custom is not None:
+        if custom is None:
+            raise ValueError("initialGuess='custom' needs customGuess")
+        g = custom
+        return _ParamsBuf(p, q, 1, np.reshape(g["W"], (p, 1)), np.reshape(g["C"], (q, 1)), np.ravel(g["B"])[:1],
+                          np.ravel(g["sigT"])[:1], g["sigE"], g["sigF"], g["sigH"])
+    if kind != "equal":
+        raise ValueError("initialGuess must be 'equal' or 'custom' here: 'random' needs R's RNG stream and 'o2m' "
+                         "needs OmicsPLS::o2m (pass their result as customGuess)")
+    return _ParamsBuf(p, q, 1, np.full((p, 1), 1.0 / np.sqrt(p)), np.full((q, 1), 1.0 / np.sqrt(q)), [1.0], [1.0],
+                      1.0 / p, 1.0 / q, 1.0)
+
+
+def PPLS(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None,
+         ctx: Optional[Context] = None, data: Optional[Data] = None, loglikelihoods: bool = True):
+    """Sequential PPLS fit -- mirror of PPLS (Package/PPLS/R/EM_W_multi.R:229-279) on the GPU: the fit
+    PPLS_simult runs for its start values (:762).  critfunc = identity, no constraints.
+
+    Returns {'W' p x a, 'C' q x a, 'B' [a], 'sig' a x 4 (sigX, sigY, sigH, sigT), 'Other_output':
+    {'Last_increment', 'Number_steps', 'Loglikelihoods', 'logvalues'}}.  customGuess: one dict (used for
+    every component, as the reference does) or a list with one dict per component.  If a noise s.d.
+    vanishes at component i the earlier components are returned with a warning (:257-262)."""
+    if isinstance(initialGuess, (tuple, list)):
+        initialGuess = initialGuess[0]
+    a = int(nr_comp)
+    if a <= 0:
+        raise ValueError("#components must be >0")
+    ctx = ctx or (data.ctx if data is not None else default_context())
+    own = data is None
+    if data is None:
+        data = Data.from_host(ctx, X, Y)
+    try:
+        p, q = data.p, data.q
+        if p < a or q < a:
+            raise ValueError("ncol(X) >= nr_comp and ncol(Y) >= nr_comp are required")
+        gs = [_guess(p, q, initialGuess, customGuess[i] if isinstance(customGuess, (list, tuple)) else customGuess)
+              for i in range(a)]
+        garr = (L.Params * a)(*[g.struct for g in gs])
+        out = _ParamsBuf(p, q, a)
+        sig = np.zeros((a, 4), order="F")
+        logv = np.zeros((a, int(EMsteps) + 1))
+        steps = (C.c_int32 * a)()
+        last = np.zeros(a)
+        ndone = C.c_int32(0)
+        L.check(L.lib().ppls_sequential_run(ctx._h, data._h, a, int(EMsteps), float(atol), garr, C.byref(out.struct),
+                                            sig.ctypes.data, logv.ctypes.data, steps, last.ctypes.data,
+                                            C.byref(ndone)))
+        k = int(ndone.value)
+        if k < a:
+            warnings.warn(f"From component {k + 1} on the residuals are of rank < 1e-14 and calculations are stopped.")
+        W, Cm, B, sg = out.W[:, :k].copy(), out.C[:, :k].copy(), out.B[:k].copy(), np.ascontiguousarray(sig[:k])
+        other = dict(Last_increment=last[:k].copy(), Number_steps=np.array(steps[:k], dtype=int),
+                     logvalues=[logv[i, :steps[i] + 1].copy() for i in range(k)])
+        if loglikelihoods:                                                                       # :275
+            other["Loglikelihoods"] = np.array([
+                logl_W(None, None, W[:, :i + 1], Cm[:, :i + 1], B[:i + 1], sg[i, 0], sg[i, 1], sg[i, 2], sg[:i + 1, 3],
+                       data=data) for i in range(k)])
+    finally:
+        if own:
+            data.close()
+    return dict(W=W, C=Cm, B=B, sig=sg, Other_output=other, **{"class": "PPLS"})
+
+
+def logl_W(X, Y, W, C_, B_T, sigX, sigY, sigH, sigT, ctx: Optional[Context] = None, data: Optional[Data] = None):
+    """Log-likelihood of a parameter set: logl_W (EM_W_multi.R:296-326) -> loglC_fast (loglC.cpp:318-338),
+    one streaming pass on the GPU.  B_T and sigT: r x r diagonal matrices or length-r vectors."""
+    W = _f64(W); W = W.reshape(W.shape[0], -1)
+    r = W.shape[1]
+    ctx = ctx or (data.ctx if data is not None else default_context())
+    own = data is None
+    if data is None:
+        data = Data.from_host(ctx, X, Y)
+    try:
+        th = _ParamsBuf(data.p, data.q, r, W, np.reshape(_f64(C_), (data.q, r), order="F"), B_T, sigT,
+                        float(np.ravel(sigX)[0]), float(np.ravel(sigY)[0]), float(np.ravel(sigH)[0]))
+        out = C.c_double(0.0)
+        L.check(L.lib().ppls_loglik(ctx._h, data._h, r, C.byref(th.struct), C.byref(out)))
+    finally:
+        if own:
+            data.close()
+    return float(out.value)

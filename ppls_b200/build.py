@@ -17,6 +17,7 @@ UNITS = {
     **{f"em_stream_inst.cu@r{r}": [f"-DPPLS_INST_R={r}"] for r in range(1, 9)},
     "em_wide.cu": [],
     "em_update.cu": ["-fmad=false"],
+    "em_seq.cu": ["-fmad=false"],
     "data.cu": ["-fmad=false"],
     "capi.cu": [],
 }

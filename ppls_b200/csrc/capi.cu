@@ -452,6 +452,9 @@ struct ppls_fit {
   WideOffsets woff{};
   double* wide_ws = nullptr;
   double* upd_scratch = nullptr; // Gram partials of the grid update kernel
+  bool seq = false;              // sequential one-component fit (em_seq.cu) instead of the simultaneous update
+  const double* prev = nullptr;  // [nprev][ld] loadings of the earlier components (device, owned by the caller)
+  int nprev = 0;
   bool cols = false;             // column-sharded: the update runs replicated on the GLOBAL (p+q) x r objects
   DataShape sg{};                // global shape (all ranks' column blocks)
   double *Gglob = nullptr, *Lglob = nullptr, *Lscratch_g = nullptr;
@@ -480,8 +483,14 @@ static void fit_free(ppls_fit* f) {
   delete f;
 }
 
+static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
+                           bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out);
 extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
                                ppls_fit** out) {
+  return fit_create_impl(ctx, d, opts, init, false, nullptr, 0, nullptr, out);
+}
+static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
+                           bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   *out = nullptr;
   int rc = ctx_activate(ctx);
@@ -498,6 +507,8 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   ppls_fit* f = new (std::nothrow) ppls_fit();
   if (!f) return fail(PPLS_E_OOM, "host allocation failed");
   f->ctx = ctx; f->data = d; f->opts = *opts; f->R = R;
+  f->seq = seq; f->prev = prev; f->nprev = nprev;
+  if (seq && (R != 1 || d->colshard)) { fit_free(f); return fail(PPLS_E_UNSUPPORTED, "sequential fit: one component at a time, row-sharded data"); }
   const char* why = "";
   f->cols = d->colshard != 0;
   if (f->cols) {
@@ -539,7 +550,8 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   memset(h, 0, sizeof(FitState));
   for (int k = 0; k < R; ++k) { h->b[k] = init->B[k]; h->t[k] = init->sigT[k]; }
   h->sigE = init->sigE; h->sigF = init->sigF; h->sigH = init->sigH;
-  h->ssqX = d->ssq[0]; h->ssqY = d->ssq[1]; h->Ntot = (double)d->n_total;
+  h->ssqX = ssq_deflated ? ssq_deflated[0] : d->ssq[0]; h->ssqY = ssq_deflated ? ssq_deflated[1] : d->ssq[1];
+  h->Ntot = (double)d->n_total;
   h->max_steps = opts->max_steps; h->orth_type = opts->orth_type; h->R = R; h->atol = opts->atol;
   e = cudaMemcpyAsync(f->L, L.data(), Lbytes, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(f->st, h, sizeof(FitState), cudaMemcpyHostToDevice, ctx->stream);
@@ -551,7 +563,8 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
     if (e == cudaSuccess) rows_local_to_global<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->L, f->Lglob, d->s.p2, d->s.q2, f->xoff, f->yoff_abs, R);
     if (e == cudaSuccess && allreduce_sum(ctx, f->Lglob, (size_t)f->sg.ld * R)) e = cudaErrorUnknown;
     if (e == cudaSuccess) e = launch_em_prepare(f->sg, R, f->Lglob, f->st, ctx->stream);
-  } else if (e == cudaSuccess) e = launch_em_prepare(d->s, R, f->L, f->st, ctx->stream);
+  } else if (e == cudaSuccess && seq) e = launch_seq_update(d->s, nullptr, f->L, f->st, f->trace, prev, nprev, 1, ctx->stream);
+  else if (e == cudaSuccess) e = launch_em_prepare(d->s, R, f->L, f->st, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // L (host vector) must outlive the copy
   if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_CUDA, std::string("fit setup: ") + cudaGetErrorString(e)); }
   f->tm.kernel_launches = 1;
@@ -579,7 +592,7 @@ static int fit_poll(ppls_fit* f) {
   }
   f->ev_k1.clear();
   f->finished = f->st_host->done != 0;
-  if (f->st_host->status != PPLS_OK)
+  if (f->st_host->status != PPLS_OK && !(f->seq && f->st_host->status == PPLS_E_DEGENERATE))
     return fail(f->st_host->status, "a parameter became non-finite during EM (degenerate data or start values)");
   return PPLS_OK;
 }
@@ -635,7 +648,8 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
     } else {
       rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
       if (rc) return rc;
-      e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
+      if (f->seq) e = launch_seq_update(s, f->momvec, f->L, f->st, f->trace, f->prev, f->nprev, 0, ctx->stream);
+      else e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
     }
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
     f->tm.kernel_launches += 3;
@@ -865,4 +879,86 @@ extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const 
     timing->bytes_per_pass = (int64_t)8 * sh.n * ((int64_t)sh.p + sh.q);
   }
   return PPLS_OK;
+}
+
+
+// ---- sequential fit: PPLS(X, Y, nr_comp, EMsteps, atol, ...), the start-value path of PPLS_simult ------------
+// Package/PPLS/R/EM_W_multi.R:229-279 (PPLS) / :116-180 (PPLSi) / :51-74 (EMstep_W) /
+// Package/PPLS/src/loglC.cpp:341-397 (EMstepC_fast).  Components one at a time; the deflation of :270-271 is
+// implicit (no deflated copy of X or Y): see csrc/em_seq.cu.  critfunc = identity, no constraints.
+extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int32_t EMsteps, double atol,
+                                   const ppls_params* guesses, ppls_params* est, double* sig, double* logvalues,
+                                   int32_t* steps, double* last_incr, int32_t* comps_done) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!d || !guesses || !est || !sig || !steps || !comps_done) return fail(PPLS_E_INVALID, "null argument");
+  if (d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
+  if (nr_comp <= 0) return fail(PPLS_E_INVALID, "#components must be >0");
+  if (nr_comp > d->s.p || nr_comp > d->s.q) return fail(PPLS_E_INVALID, "nr_comp exceeds ncol(X) or ncol(Y)");
+  if (EMsteps < 1) return fail(PPLS_E_INVALID, "EMsteps must be a strictly positive integer");
+  rc = check_params(est, "est");
+  if (rc) return rc;
+  const DataShape& sh = d->s;
+  const int a = nr_comp;
+  double* dprev = nullptr;
+  CU(cudaMalloc(&dprev, (size_t)a * sh.ld * sizeof(double)));
+  struct Guard { double* p; ~Guard() { cudaFree(p); } } guard{dprev};
+  double ssq[2] = {d->ssq[0], d->ssq[1]};
+  ppls_opts opts{};
+  opts.r = 1; opts.max_steps = EMsteps; opts.atol = atol; opts.orth_type = PPLS_ORTH_SVD; opts.check_every = 8;
+  *comps_done = 0;
+  for (int i = 0; i < a; ++i) {
+    rc = check_params(&guesses[i], "guess");
+    if (rc) return rc;
+    ppls_fit* f = nullptr;
+    rc = fit_create_impl(ctx, d, &opts, &guesses[i], true, dprev, i, ssq, &f);
+    if (rc) return rc;
+    int32_t done = 0, fin = 0;
+    while (!fin) {
+      rc = ppls_fit_iterate(f, 8, &done, &fin);
+      if (rc) { fit_free(f); return rc; }
+      if (!fin && done > EMsteps + 1) { fit_free(f); return fail(PPLS_E_CUDA, "sequential EM loop did not terminate"); }
+    }
+    const FitState hs = *f->st_host;      // by value: the pinned copy goes away with the fit
+    const FitState* h = &hs;
+    if (h->status == PPLS_E_DEGENERATE) { fit_free(f); break; }     // :257-262: stop at this component, keep the earlier ones
+    const int k = h->steps_done;
+    std::vector<double> L(sh.ld), tr((size_t)k + 1);
+    double gram[3];
+    cudaError_t e = cudaMemcpyAsync(L.data(), f->L, sh.ld * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(tr.data(), f->trace, tr.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(gram, f->momvec + sh.ld, sizeof(gram), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dprev + (size_t)i * sh.ld, f->L, sh.ld * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    fit_free(f);
+    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("sequential fit readback: ") + cudaGetErrorString(e));
+    for (int j = 0; j < sh.p; ++j) est->W[j + (size_t)i * sh.p] = L[j];
+    for (int j = 0; j < sh.q; ++j) est->C[j + (size_t)i * sh.q] = L[sh.p2 + j];
+    est->B[i] = h->b[0]; est->sigT[i] = h->t[0];
+    sig[i + 0 * a] = h->sigE; sig[i + 1 * a] = h->sigF; sig[i + 2 * a] = h->sigH; sig[i + 3 * a] = h->t[0];
+    steps[i] = k;
+    if (last_incr) last_incr[i] = (k >= 1) ? tr[k] - tr[k - 1] : 0.0;
+    if (logvalues) for (int j = 0; j <= k; ++j) logvalues[(size_t)i * (EMsteps + 1) + j] = tr[j];
+    // Xc <- Xc - (Xc w) w':  ||Xc||^2 drops by ||Xc w||^2 (w has unit norm), the Gram of the final pass
+    ssq[0] -= gram[0]; ssq[1] -= gram[2];
+    *comps_done = i + 1;
+  }
+  if (*comps_done > 0) { est->sigE = sig[*comps_done - 1]; est->sigF = sig[*comps_done - 1 + a]; est->sigH = sig[*comps_done - 1 + 2 * a]; }
+  return PPLS_OK;
+}
+
+// ---- log-likelihood of a parameter set: logl_W (EM_W_multi.R:296-326) -> loglC_fast (loglC.cpp:318-338) ------
+// One streaming pass (the same kernels as an EM iteration; the moments it needs are the Gram of (XW, YC)).
+extern "C" int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out) {
+  if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+  ppls_opts opts{};
+  opts.r = r; opts.max_steps = 1; opts.atol = 0.0; opts.orth_type = PPLS_ORTH_SVD; opts.check_every = 1;
+  ppls_fit* f = nullptr;
+  int rc = ppls_fit_create(ctx, d, &opts, theta, &f);
+  if (rc) return rc;
+  int32_t done = 0, fin = 0;
+  rc = ppls_fit_iterate(f, 1, &done, &fin);
+  if (rc == PPLS_OK) *out = f->st_host->loglik_last;
+  fit_free(f);
+  return rc;
 }

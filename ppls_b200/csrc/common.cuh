@@ -115,6 +115,10 @@ size_t update_grid_scratch_doubles(int ld, int R);
 // Prepare coefficients + Gram matrices for the start state (pass 0).
 cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream);
 
+// em_seq.cu: update of the sequential one-component fit (R = 1; `prev` = earlier components' loadings)
+cudaError_t launch_seq_update(const DataShape& s, const double* momvec, double* L, FitState* st, double* trace,
+                              const double* prev, int nprev, int prepare, cudaStream_t stream);
+
 // data.cu
 cudaError_t launch_retile(const double* colmajor, int64_t ldc, int64_t nrows, int ncols,
                           double* D, const DataShape& s, int col0, int64_t row0, cudaStream_t stream);

@@ -1,0 +1,113 @@
+"""GPU parity tests of the sequential PPLS fit (ppls_sequential_run / ppls_b200.PPLS) and of logl_W
+(ppls_loglik), called through the C ABI, against oracle/ppls_seq.py and its committed golden vectors.
+Tolerances: parameters 1e-8 relative, log-likelihood 1e-10 relative (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+from helpers import TOL_LOGLIK, TOL_PARAM, relmax
+from test_oracle_seq import load_seq, seq_cases
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from ppls_b200 import Context
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def _check(out, ref_W, ref_C, ref_B, ref_sig, ref_steps, ref_logv):
+    assert np.array_equal(out["Other_output"]["Number_steps"], ref_steps)
+    assert relmax(out["W"], ref_W) < TOL_PARAM and relmax(out["C"], ref_C) < TOL_PARAM
+    assert relmax(out["B"], ref_B) < TOL_PARAM
+    assert np.max(np.abs(out["sig"] / ref_sig - 1)) < TOL_PARAM
+    for i, t in enumerate(out["Other_output"]["logvalues"]):
+        assert relmax(t, ref_logv[i][:t.size]) < TOL_LOGLIK
+
+
+@pytest.mark.parametrize("name", seq_cases())
+def test_golden_sequential(ctx, name):
+    from ppls_b200 import PPLS
+    g = load_seq(name)
+    out = PPLS(g["X"], g["Y"], int(g["a"]), int(g["EMsteps"]), float(g["atol"]), g["guess"], g["custom"], ctx=ctx)
+    assert out["class"] == "PPLS" and out["sig"].shape == (int(g["a"]), 4)
+    _check(out, g["W"], g["C"], g["B"], g["sig"], g["Number_steps"], g["logvalues"])
+    li = out["Other_output"]["Last_increment"]
+    assert np.max(np.abs(li - g["Last_increment"])) < 1e-9 * np.max(np.abs(g["logvalues"][0, 0]))
+
+
+@pytest.mark.parametrize("name", ["seq_equal_3", "seq_odd_2"])
+@pytest.mark.parametrize("panel", ["0", "1"])
+def test_golden_sequential_through_the_wide_path(ctx, name, panel, monkeypatch):
+    from ppls_b200 import PPLS
+    monkeypatch.setenv("PPLS_FORCE_WIDE", "1")
+    monkeypatch.setenv("PPLS_PANEL", panel)
+    g = load_seq(name)
+    out = PPLS(g["X"], g["Y"], int(g["a"]), int(g["EMsteps"]), float(g["atol"]), g["guess"], g["custom"], ctx=ctx)
+    _check(out, g["W"], g["C"], g["B"], g["sig"], g["Number_steps"], g["logvalues"])
+
+
+@pytest.mark.parametrize("shape", [(3000, 300, 120, 3, 12), (1201, 1000, 200, 2, 8), (150, 2600, 40, 2, 6)])
+def test_fresh_inputs_sequential(ctx, shape):
+    """Seeded model data at sizes the numpy oracle finishes in seconds (the last one takes the wide path)."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    from make_golden_seq import model_data
+    from oracle import ppls_seq
+    from ppls_b200 import PPLS
+    n, p, q, a, steps = shape
+    X, Y = model_data(77 + n, n, p, q, a, 0.4)
+    ref = ppls_seq.ppls(X, Y, a, steps, 1e-4, "equal")
+    out = PPLS(X, Y, a, steps, 1e-4, "equal", ctx=ctx)
+    logv = [t for t in ref["logvalues"]]
+    _check(out, ref["W"], ref["C"], ref["B"], ref["sig"], ref["Number_steps"], logv)
+    # Other_output$Loglikelihoods (:275): logl_W of the first i components on the undeflated data
+    from oracle import ppls_ref
+    for i in range(a):
+        want = ppls_ref.logl_w(X, Y, ref["W"][:, :i + 1], ref["C"][:, :i + 1], np.diag(ref["B"][:i + 1]), ref["sig"][i, 0],
+                               ref["sig"][i, 1], ref["sig"][i, 2], np.diag(ref["sig"][:i + 1, 3]))
+        assert abs(out["Other_output"]["Loglikelihoods"][i] / want - 1) < 1e-9
+
+
+def test_logl_w_matches_oracle(ctx):
+    from oracle import ppls_ref
+    from ppls_b200 import logl_W
+    from helpers import init_of, load_golden
+    g = load_golden("r5_odd_shapes")
+    th = init_of(g)
+    want = ppls_ref.logl_w(g["X"], g["Y"], th["W"], th["C"], th["B"], th["sigE"], th["sigF"], th["sigH"], th["sigT"])
+    got = logl_W(g["X"], g["Y"], th["W"], th["C"], th["B"], th["sigE"], th["sigF"], th["sigH"], th["sigT"], ctx=ctx)
+    assert abs(got / want - 1) < TOL_LOGLIK
+
+
+def test_vanishing_noise_stops_the_fit(ctx):
+    """PPLSi returns NA when a noise s.d. is below 100 eps (:153-155); PPLS keeps the earlier components
+    and warns (:257-262).  Start the second component from such a state."""
+    from ppls_b200 import PPLS
+    g = load_seq("seq_odd_2")
+    p, q = g["X"].shape[1], g["Y"].shape[1]
+    ok = dict(W=np.ones(p) / np.sqrt(p), C=np.ones(q) / np.sqrt(q), B=1.0, sigE=1.0 / p, sigF=1.0 / q, sigH=1.0, sigT=1.0)
+    bad = dict(ok, sigE=1e-15)
+    with pytest.warns(UserWarning, match="calculations are stopped"):
+        out = PPLS(g["X"], g["Y"], 2, 5, 1e-4, "custom", [ok, bad], ctx=ctx)
+    assert out["W"].shape == (p, 1) and out["B"].shape == (1,) and out["sig"].shape == (1, 4)
+    with pytest.warns(UserWarning):
+        out0 = PPLS(g["X"], g["Y"], 1, 5, 1e-4, "custom", bad, ctx=ctx)
+    assert out0["W"].shape == (p, 0)
+
+
+def test_sequential_argument_errors(ctx):
+    from ppls_b200 import PPLS, PPLSError
+    g = load_seq("seq_p_lt_q_1")
+    with pytest.raises(ValueError):
+        PPLS(g["X"], g["Y"], 0, ctx=ctx)
+    with pytest.raises(ValueError):
+        PPLS(g["X"], g["Y"], 6, ctx=ctx)           # ncol(X) = 5 < nr_comp
+    with pytest.raises(ValueError):
+        PPLS(g["X"], g["Y"], 1, initialGuess="random", ctx=ctx)
+    with pytest.raises(PPLSError):
+        PPLS(g["X"], g["Y"], 1, EMsteps=0, ctx=ctx)
