@@ -18,7 +18,7 @@ import numpy as np
 from . import _lib as L
 
 __all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "normalise", "default_init",
-           "default_context"]
+           "sequential_init", "default_context"]
 
 
 def _f64(a, order="F"):
@@ -239,11 +239,8 @@ def normalise(W, C_, B, sigT):
 
 
 def default_init(p: int, q: int, a: int) -> dict:
-    """Deterministic start state used when the caller gives none.
-
-    DEVIATION (documented in DESIGN.md): the reference draws its start from 20 EM steps of
-    the sequential PPLS(..., 'random') fit (EM_W_multi.R:762-771), which is R-RNG dependent
-    and not on this path.  Here: the first `a` cosine basis vectors (orthonormal), B = I,
+    """A data-independent start state (used by tests and benchmarks; PPLS_simult's own default is
+    sequential_init): the first `a` cosine basis vectors (orthonormal), B = I,
     sigT = I with a mild decay, sigE = 1/sqrt(p), sigF = 1/sqrt(q), sigH = 0.1."""
     def basis(n):
         j = (np.arange(n) + 0.5)[:, None]
@@ -255,13 +252,26 @@ def default_init(p: int, q: int, a: int) -> dict:
                 sigE=1.0 / np.sqrt(p), sigF=1.0 / np.sqrt(q), sigH=0.1)
 
 
+def sequential_init(data: "Data", a: int) -> dict:
+    """Start state of PPLS_simult (EM_W_multi.R:762-771): 20 steps of the sequential fit per component,
+    run on the GPU over the resident data (ppls_sequential_run).
+    DEVIATION: the reference starts that fit from initialGuess='random' (R's RNG, :133, not reproducible
+    outside R); here it starts from 'equal'.  Pass `init=` to PPLS_simult for any other start."""
+    f0 = PPLS(None, None, a, 20, 1e-4, "equal", data=data, loglikelihoods=False)
+    if f0["W"].shape[1] < a:
+        raise RuntimeError("sequential start fit stopped early (rank-deficient residuals); pass init=")
+    sg = f0["sig"]
+    return dict(W=f0["W"], C=f0["C"], B=f0["B"], sigT=sg[:, 3], sigE=sg[a - 1, 0], sigF=sg[a - 1, 1], sigH=sg[a - 1, 2])
+
+
 def PPLS_simult(X, Y, a, EMsteps=10, atol=1e-4, type="SVD", init: Optional[dict] = None,
                 ctx: Optional[Context] = None, data: Optional[Data] = None, want_mu: bool = True, **kwargs):
     """Simultaneous PPLS fit -- drop-in for PPLS_simult (Package/PPLS/R/EM_W_multi.R:758-807).
 
     Returns {'Expectations': {mu_T, mu_U, Ctt, Cuu, Cut, Cee, Cff, Chh}, 'loglik', 'estimates':
     {W, C, B, sigE, sigF, sigH, sigT}} with the reference's shapes (B, sigT, Ctt, Cuu, Cut
-    r x r diagonal matrices; Cee, Cff 1 x 1).  `init` replaces the random start (:762-771).
+    r x r diagonal matrices; Cee, Cff 1 x 1).  `init` replaces the start of :762-771 (default:
+    sequential_init, the same 20-step sequential fit started from 'equal' instead of 'random').
     `debug=` (the dense Expect_M, :643-667) is accepted and ignored with a warning: the dense
     form is O((p+q)^3) and exists in this repo only inside the CPU oracle."""
     if isinstance(type, (tuple, list)):
@@ -281,7 +291,7 @@ def PPLS_simult(X, Y, a, EMsteps=10, atol=1e-4, type="SVD", init: Optional[dict]
         data = Data.from_host(ctx, X, Y)
     try:
         if init is None:
-            init = default_init(data.p, data.q, a)
+            init = sequential_init(data, a)                                                # :762-771
         W0, C0, B0, T0 = normalise(init["W"], init["C"], init["B"], init["sigT"])          # :773-778
         start = dict(W=W0, C=C0, B=B0, sigT=T0, sigE=init["sigE"], sigF=init["sigF"], sigH=init["sigH"])
         fit = Fit(data, start, a, EMsteps, atol, type)

@@ -111,3 +111,23 @@ def test_sequential_argument_errors(ctx):
         PPLS(g["X"], g["Y"], 1, initialGuess="random", ctx=ctx)
     with pytest.raises(PPLSError):
         PPLS(g["X"], g["Y"], 1, EMsteps=0, ctx=ctx)
+
+
+def test_ppls_simult_whole_call_with_its_own_start(ctx):
+    """PPLS_simult(X, Y, a, ...) without init=: start fit (:762-771, 'equal' instead of 'random'), start
+    normalisation (:773-778), loop (:780-793), result normalisation (:794-799) -- against the same chain of
+    oracle functions."""
+    from oracle import ppls_ref, ppls_seq
+    from ppls_b200 import PPLS_simult
+    g = load_seq("seq_equal_3")
+    X, Y, a = g["X"], g["Y"], 3
+    f0 = ppls_seq.ppls(X, Y, a, 20, 1e-4, "equal")
+    W0, C0, B0, T0 = ppls_ref.normalise(f0["W"], f0["C"], f0["B"], f0["sig"][:, 3])
+    ref = ppls_ref.ppls_simult_loop(X, Y, W0, C0, B0, f0["sig"][a - 1, 0], f0["sig"][a - 1, 1], f0["sig"][a - 1, 2], T0,
+                                    EMsteps=30, atol=1e-4)
+    out = PPLS_simult(X, Y, a, EMsteps=30, atol=1e-4, ctx=ctx)
+    assert len(out["loglik"]) == len(ref["loglik"]) and relmax(out["loglik"], ref["loglik"]) < TOL_LOGLIK
+    for k in ("W", "C", "B", "sigT"):
+        assert relmax(out["estimates"][k], ref["estimates"][k]) < TOL_PARAM, k
+    for k in ("sigE", "sigF", "sigH"):
+        assert abs(out["estimates"][k] / ref["estimates"][k] - 1) < TOL_PARAM, k
