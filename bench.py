@@ -190,6 +190,7 @@ def run_ours(args):
         barrier()
         e0 = time.perf_counter()
         d2 = Data.from_host_cols(ctx, Xn, Yn) if colmode else Data.from_host(ctx, Xn, Yn)
+        up_s = time.perf_counter() - e0                  # from_host returns after the upload has completed
         f2 = Fit(d2, start, r, EMsteps=K, atol=-float("inf"), type="SVD")
         f2.run()
         res = f2.result(want_mu=False)
@@ -205,7 +206,8 @@ def run_ours(args):
                "d2h_bytes_per_step": int(8 * ((p + q) * r + 2 * r + 3 + K) / K),
                "sample": f"one PPLS_simult-style call (upload {ns} rows/GPU from pinned host memory, {K} EM steps, "
                          f"download estimates+loglik), time scaled x{scale:.1f} to the full shard",
-               "seconds_sample": e_s, "loglik_last": float(res["loglik"][-1])}
+               "seconds_sample": e_s, "upload_seconds_sample": up_s,
+               "upload_gbs": 8 * ns * (data.p + data.q) / up_s / 1e9, "loglik_last": float(res["loglik"][-1])}
         del Xp, Yp
     data.close()
     # orderly teardown on EVERY rank (communicators are collective objects), then leave without
@@ -241,7 +243,10 @@ def run_ours(args):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"{args.workload}: N={N} p={p} q={q} r={r} " + (f"(column-sharded over {world} ranks)" if colmode else f"(row-sharded {world}x{n_local})"),
                    "l2": "inputs larger than L2 (no flush needed)" if bytes_pass > (256 << 20) else "inputs fit L2: L2-resident between iterations",
-                   "generate_s": round(gen_s, 2), "wall_ms_per_step": wall_ms / K},
+                   "generate_s": round(gen_s, 2), "wall_ms_per_step": wall_ms / K,
+                   "exchange": ("none (1 GPU)" if world == 1 else "one-shot peer stores + flags, summed in rank order inside the update kernel"
+                                if tm1.get("peer_exchange") else "NCCL allreduce"),
+                   "tail_ms_per_step": (tm1["tail_ms"] - tm0["tail_ms"]) / K},
         "clocks": clocks, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src,

@@ -82,6 +82,8 @@ typedef struct {
   int64_t kernel_launches;/* every kernel of ours launched by this fit           */
   int64_t passes;         /* data passes done                                    */
   int64_t bytes_per_pass; /* algorithmic bytes of one pass on this rank: 8*N*(p+q) */
+  double  tail_ms;        /* sum over passes of what follows K1: reduce, exchange, update (K2) */
+  int64_t peer_exchange;  /* 1: the moment vector travels by the one-shot peer exchange, 0: NCCL / single GPU */
 } ppls_timing;
 
 const char* ppls_version(void);

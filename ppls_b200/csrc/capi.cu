@@ -72,6 +72,11 @@ struct ppls_ctx {
   cudaStream_t stream = nullptr;
   nccl_comm comm = nullptr;
   double* d_small = nullptr;   // 8 doubles of device scratch for tiny collectives
+  // one-shot peer exchange (common.cuh::XchgDev): own block + the peers' blocks mapped through CUDA IPC
+  bool xchg_on = false;
+  char* xbuf = nullptr;
+  void* xpeer[XCHG_MAXW] = {};
+  XchgDev xdev{};
 };
 
 struct ppls_data {
@@ -136,6 +141,75 @@ extern "C" int ppls_nccl_unique_id(void* id_out, size_t nbytes) {
   return PPLS_OK;
 }
 
+static int allreduce_sum(ppls_ctx* ctx, double* dbuf, size_t count);
+
+// Peer exchange set-up: every rank allocates [control 1 KB | inbox 2 x world x slot doubles], publishes its
+// CUDA IPC handle (bytes carried as doubles through one NCCL sum) and maps every peer's block.  All ranks
+// then agree (a second sum) whether everybody succeeded; otherwise the NCCL allreduce stays in use.
+static const size_t XCHG_CTRL = 1024, XCHG_SLOT = 65536;
+static void xchg_setup(ppls_ctx* c) {
+  const char* env = getenv("PPLS_XCHG");
+  if (c->world < 2 || c->world > XCHG_MAXW || (env && *env && atoi(env) == 0)) return;
+  const int W = c->world;
+  const size_t bytes = XCHG_CTRL + (size_t)2 * W * XCHG_SLOT * sizeof(double);
+  int ok = 1;
+  double* hb = nullptr;      // [W][64] handle bytes + [1] failure count
+  const size_t nd = (size_t)W * 64 + 1;
+  if (cudaMalloc(&c->xbuf, bytes) != cudaSuccess) { c->xbuf = nullptr; ok = 0; }
+  if (ok && cudaMemset(c->xbuf, 0, bytes) != cudaSuccess) ok = 0;
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (ok && cudaIpcGetMemHandle(&mine, c->xbuf) != cudaSuccess) ok = 0;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  std::vector<double> host(nd, 0.0);
+  for (int i = 0; i < 64; ++i) host[(size_t)c->rank * 64 + i] = (double)((const unsigned char*)&mine)[i];
+  host[nd - 1] = ok ? 0.0 : 1.0;
+  if (cudaMalloc(&hb, nd * sizeof(double)) != cudaSuccess) { cudaGetLastError(); hb = nullptr; }
+  // from here on every rank must make the same collective calls
+  bool coll = hb != nullptr;
+  if (coll) coll = cudaMemcpyAsync(hb, host.data(), nd * sizeof(double), cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+  if (coll) coll = allreduce_sum(c, hb, nd) == PPLS_OK;
+  if (coll) coll = cudaMemcpyAsync(host.data(), hb, nd * sizeof(double), cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+  if (coll) coll = cudaStreamSynchronize(c->stream) == cudaSuccess;
+  if (!coll || host[nd - 1] != 0.0) ok = 0;
+  if (ok) {
+    for (int r = 0; r < W && ok; ++r) {
+      if (r == c->rank) { c->xpeer[r] = c->xbuf; continue; }
+      cudaIpcMemHandle_t h;
+      for (int i = 0; i < 64; ++i) ((unsigned char*)&h)[i] = (unsigned char)host[(size_t)r * 64 + i];
+      if (cudaIpcOpenMemHandle(&c->xpeer[r], h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { c->xpeer[r] = nullptr; ok = 0; }
+    }
+  }
+  cudaGetLastError();
+  if (coll) {                                   // agreement: everybody mapped everybody
+    double flag = ok ? 0.0 : 1.0;
+    bool c2 = cudaMemcpyAsync(hb, &flag, sizeof(double), cudaMemcpyHostToDevice, c->stream) == cudaSuccess;
+    if (c2) c2 = allreduce_sum(c, hb, 1) == PPLS_OK;
+    if (c2) c2 = cudaMemcpyAsync(&flag, hb, sizeof(double), cudaMemcpyDeviceToHost, c->stream) == cudaSuccess;
+    if (c2) c2 = cudaStreamSynchronize(c->stream) == cudaSuccess;
+    if (!c2 || flag != 0.0) ok = 0;
+  }
+  if (hb) cudaFree(hb);
+  if (!ok) {
+    for (int r = 0; r < W; ++r) if (r != c->rank && c->xpeer[r]) { cudaIpcCloseMemHandle(c->xpeer[r]); c->xpeer[r] = nullptr; }
+    if (c->xbuf) { cudaFree(c->xbuf); c->xbuf = nullptr; }
+    cudaGetLastError();
+    return;
+  }
+  XchgDev& x = c->xdev;
+  memset(&x, 0, sizeof(x));
+  for (int r = 0; r < W; ++r) {
+    char* base = (char*)c->xpeer[r];
+    x.flags[r] = (unsigned long long*)base;                     // [2][XCHG_MAXW] = 256 B
+    x.inbox[r] = (double*)(base + XCHG_CTRL);
+  }
+  x.epoch = (unsigned long long*)(c->xbuf + 512);
+  x.counter = (unsigned int*)(c->xbuf + 520);
+  x.failed = (int*)(c->xbuf + 524);
+  x.rank = c->rank; x.world = W; x.slot = (long long)XCHG_SLOT;
+  c->xchg_on = true;
+}
+
 extern "C" int ppls_ctx_create_dist(ppls_ctx** out, int device, int rank, int world, const void* nccl_id,
                                     size_t nbytes) {
   if (world < 1 || rank < 0 || rank >= world) return fail(PPLS_E_INVALID, "bad rank/world");
@@ -150,6 +224,7 @@ extern "C" int ppls_ctx_create_dist(ppls_ctx** out, int device, int rank, int wo
   memcpy(&id, nccl_id, sizeof(id));
   int nr = g_nccl.CommInitRank(&(*out)->comm, world, id, rank);
   if (nr) { ppls_ctx_destroy(*out); *out = nullptr; return nccl_fail(nr, "ncclCommInitRank"); }
+  xchg_setup(*out);
   return PPLS_OK;
 }
 
@@ -157,7 +232,10 @@ extern "C" int ppls_ctx_destroy(ppls_ctx* ctx) {
   if (!ctx) return PPLS_OK;
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  for (int r = 0; r < XCHG_MAXW; ++r)
+    if (r != ctx->rank && ctx->xpeer[r]) cudaIpcCloseMemHandle(ctx->xpeer[r]);
   if (ctx->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(ctx->comm);
+  if (ctx->xbuf) cudaFree(ctx->xbuf);
   if (ctx->d_small) cudaFree(ctx->d_small);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -468,7 +546,7 @@ struct ppls_fit {
   int32_t passes = 0;
   // timing
   std::vector<cudaEvent_t> ev_free;
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_k1;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_k1, ev_tail;
   ppls_timing tm{};
 };
 
@@ -476,6 +554,7 @@ static void fit_free(ppls_fit* f) {
   if (!f) return;
   if (f->ctx) cudaSetDevice(f->ctx->device);
   for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  for (auto& pr : f->ev_tail) cudaEventDestroy(pr.second);
   for (auto e : f->ev_free) cudaEventDestroy(e);
   cudaFree(f->wide_ws); cudaFree(f->upd_scratch); cudaFree(f->Gglob); cudaFree(f->Lglob); cudaFree(f->Lscratch_g); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
   cudaFree(f->st);
@@ -585,6 +664,12 @@ static int fit_poll(ppls_fit* f) {
   ppls_ctx* ctx = f->ctx;
   CU(cudaMemcpyAsync(f->st_host, f->st, sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
+  for (auto& pr : f->ev_tail) {       // .first is the K1 end event (owned by ev_k1, recycled below)
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) f->tm.tail_ms += ms;
+    f->ev_free.push_back(pr.second);
+  }
+  f->ev_tail.clear();
   for (auto& pr : f->ev_k1) {
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) { f->tm.stream_ms += ms; f->tm.stream_launches += 1; }
@@ -607,6 +692,8 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
   int check_every = f->opts.check_every > 0 ? f->opts.check_every : 16;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   if (timing) { ev0 = fit_event(f); ev1 = fit_event(f); cudaEventRecord(ev0, ctx->stream); }
+  // row-sharded multi-GPU, fused-kernel path: the moment vector travels by peer stores (em_update.cu)
+  const bool use_x = ctx->xchg_on && !f->wide && !f->cols && !f->seq && (size_t)f->veclen <= XCHG_SLOT;
   int32_t since_check = 0;
   // passes the device may still run: it stops by itself (done flag), the host only bounds the queue
   for (int32_t i = 0; i < n_passes && !f->finished; ++i) {
@@ -626,7 +713,8 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
     } else {
       e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream);
       if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
-      if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
+      if (e == cudaSuccess && use_x) e = launch_xsend(f->partials, f->plan.grid, f->veclen, ctx->xdev, f->st, ctx->stream);
+      else if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
     }
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
     if (f->cols) {
@@ -645,6 +733,8 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
       if (e == cudaSuccess) rows_global_to_local<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->Lglob, f->L, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
       if (e == cudaSuccess) e = cudaGetLastError();
       f->tm.kernel_launches += 2;
+    } else if (use_x) {
+      e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream, &ctx->xdev);
     } else {
       rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
       if (rc) return rc;
@@ -652,6 +742,8 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
       else e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
     }
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
+    if (timing) { cudaEvent_t c = fit_event(f); cudaEventRecord(c, ctx->stream); f->ev_tail.emplace_back(b, c); }
+    f->tm.peer_exchange = use_x ? 1 : 0;
     f->tm.kernel_launches += 3;
     f->passes += 1;
     if (++since_check >= check_every) {

@@ -100,12 +100,30 @@ cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const d
                              const double* L, const FitState* st, double* partials,
                              double* muT, double* muU, int write_mu, cudaStream_t stream);
 // Sum the per-CTA partials in CTA order -> momvec.
+// One-shot peer exchange of the moment vector (multi-GPU, one node): every rank stores its reduced vector
+// straight into every peer's inbox over NVLink (peer-mapped cudaIpc memory), raises a flag there, and the
+// update kernel of each rank sums the world's inbox slots in rank order (bitwise identical on all ranks).
+constexpr int XCHG_MAXW = 16;
+struct XchgDev {
+  double* inbox[XCHG_MAXW];               // rank r's inbox [2 parities][world][slot] (own rank: local pointer)
+  unsigned long long* flags[XCHG_MAXW];   // rank r's flag words [2 parities][XCHG_MAXW]: epoch of the last arrival
+  unsigned long long* epoch;              // local: exchanges completed
+  unsigned int* counter;                  // local: send blocks finished (threadfence-reduction pattern)
+  int* failed;                            // local: a wait timed out (a peer died)
+  int rank, world;
+  long long slot;                         // doubles per (parity, source rank) slot
+};
+// reduce the per-CTA partial vectors (as launch_reduce_partials) and send the result to every rank's inbox
+cudaError_t launch_xsend(const double* partials, int nparts, int64_t len, const XchgDev& x, const FitState* st,
+                         cudaStream_t stream);
 cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t len, double* momvec,
                                    const FitState* st, cudaStream_t stream);
 // K2: loglik, E-step moments, break rule, M-step, next coefficients.
 // orth_type SVD + gscratch != null: the grid (cooperative) kernel; else the single-CTA kernel.
+// xchg != null: momvec is first assembled from the peer-exchange inbox (wait for the world's flags, sum).
 cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
-                             FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream);
+                             FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream,
+                             const XchgDev* xchg = nullptr);
 // batched multi-start: S starts, g per pack of RP = g*R components (em_update.cu)
 cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int S, int tracelen, int prepare,
                                    const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,

@@ -12,6 +12,7 @@
 //   coefficients of mu_T, mu_U for the next pass (:691-694 with the diagonal algebra collapsed)
 #include "common.cuh"
 #include <math.h>
+#include <string.h>
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
@@ -281,7 +282,41 @@ struct UpdateArgs {
   double* trace;          // [max_steps]
   double* gscratch;       // grid kernel: [3 phases][row blocks][2 matrices][R*R] Gram partials
   int32_t p, q, p2, q2, ld;
+  int32_t use_x;          // 1: momvec comes out of the peer-exchange inbox (x)
+  XchgDev x;
 };
+
+// ---- peer exchange, receive side -----------------------------------------------------------------
+__device__ inline unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ inline void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ inline unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// ONE thread: wait until every rank's vector of exchange `next` has landed in the local inbox.
+__device__ inline void xchg_wait(const XchgDev& x, unsigned long long next) {
+  const unsigned long long* fl = x.flags[x.rank] + (next & 1ull) * XCHG_MAXW;
+  const unsigned long long t0 = global_timer_ns();
+  for (int r = 0; r < x.world; ++r) {
+    while (ld_acquire_sys(fl + r) < next) {
+      if (global_timer_ns() - t0 > 20000000000ull) { atomicExch(x.failed, 1); return; }   // 20 s: a peer is gone
+    }
+  }
+}
+// element e of the summed vector, ranks added in rank order (the same bits on every rank)
+__device__ inline double xchg_sum(const XchgDev& x, unsigned long long next, long long e) {
+  const double* in = x.inbox[x.rank] + (size_t)(next & 1ull) * x.world * x.slot + e;
+  double s = __ldcg(in);
+  for (int r = 1; r < x.world; ++r) s += __ldcg(in + (size_t)r * x.slot);
+  return s;
+}
 
 __device__ inline bool finite_d(double x) { return isfinite(x); }
 
@@ -458,7 +493,22 @@ __device__ void update_body(const UpdateArgs& a) {
 }
 
 template <int R>
-__global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateArgs a) { update_body<R>(a); }
+__global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateArgs a) {
+  if (a.use_x) {
+    if (a.st->done) return;
+    __shared__ int bad;
+    const unsigned long long next = *a.x.epoch + 1;
+    if (threadIdx.x == 0) { xchg_wait(a.x, next); bad = *a.x.failed; }
+    __syncthreads();
+    if (bad) { if (threadIdx.x == 0) { a.st->status = PPLS_E_NCCL; a.st->done = 1; } return; }
+    double* mv = const_cast<double*>(a.momvec);
+    const long long len = (long long)a.ld * R + 3 * R * R;
+    for (long long e = threadIdx.x; e < len; e += blockDim.x) mv[e] = xchg_sum(a.x, next, e);
+    __syncthreads();
+    if (threadIdx.x == 0) *a.x.epoch = next;
+  }
+  update_body<R>(a);
+}
 
 // ---- batched multi-start: one block per start ------------------------------------------------------
 // The streaming kernel runs `g` starts at once as g*R "components" (the E-step is diagonal in the
@@ -488,7 +538,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_batch_kernel(const B
   UpdateArgs a;
   a.momvec = b.momvec_s + sidx * veclen; a.L = b.L_s + (size_t)sidx * b.ld * R;
   a.Lscratch = b.Lscratch_s + (size_t)sidx * b.ld * R; a.st = b.st + sidx; a.trace = b.trace + (size_t)sidx * b.tracelen;
-  a.gscratch = nullptr; a.p = b.p; a.q = b.q; a.p2 = b.p2; a.q2 = b.q2; a.ld = b.ld;
+  a.gscratch = nullptr; a.p = b.p; a.q = b.q; a.p2 = b.p2; a.q2 = b.q2; a.ld = b.ld; a.use_x = 0;
   FitState* st = a.st;
   FitState* ps = b.pack_st + group;
   double* Lp = b.L_pack + (size_t)group * b.ld * RP;
@@ -591,6 +641,22 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   double* ph1 = ph0 + (size_t)nb * 2 * R * R;
   double* ph2 = ph1 + (size_t)nb * 2 * R * R;
   const double* G = a.momvec;
+  // ---- phase 0 (multi-GPU peer exchange): wait for the world's vectors, sum them in rank order ------
+  if (a.use_x) {
+    const unsigned long long next = *a.x.epoch + 1;       // written below, after every block has read it
+    if (threadIdx.x == 0) xchg_wait(a.x, next);
+    __syncthreads();
+    double* mv = const_cast<double*>(a.momvec);
+    const long long len = (long long)a.ld * R + 3 * R * R;
+    for (long long e = (long long)blockIdx.x * GT + threadIdx.x; e < len; e += (long long)gridDim.x * GT)
+      mv[e] = xchg_sum(a.x, next, e);
+    grid.sync();
+    if (*a.x.failed) {                                    // same on every block (raised before the sync)
+      if (blockIdx.x == 0 && threadIdx.x == 0) { st->status = PPLS_E_NCCL; st->done = 1; }
+      return;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) *a.x.epoch = next;
+  }
   // ---- phase 1: scalars | Gram of G1, G2 ---------------------------------------------------------
   // st->done is read by every block at entry, so it may only be raised after the first grid-wide
   // sync; until then the decision travels in a scratch flag.
@@ -643,16 +709,18 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
     grid_partial_gram<R>(a.L, a.p2, a.ld, rb, nb, ph1 + ((size_t)rb * 2 + 1) * R * R, scratch);
   }
   grid.sync();
-  // ---- phase 3: one Newton-Schulz step L <- L (3I - L'L)/2, Gram of the result ----------------------
+  // ---- phase 3: one Newton-Schulz step L <- L M, M = (3I - S)/2 with S = L'L --------------------------
+  // The Gram of the result is M S M exactly (L is well conditioned here, so S carries full accuracy):
+  // block 0 forms W'W, C'C from it while the row blocks apply the step -- no further pass, no further sync.
+  grid_sum_gram<R>(ph1, nb, 0, S[0]);
+  grid_sum_gram<R>(ph1, nb, 1, S[1]);
+  __syncthreads();
+  if (threadIdx.x < 2 * R * R) {
+    const int w = threadIdx.x / (R * R), e = threadIdx.x - w * R * R;
+    Mat[w][e] = ((e / R) == (e % R) ? 1.5 : 0.0) - 0.5 * S[w][e];
+  }
+  __syncthreads();
   if (rb >= 0) {
-    grid_sum_gram<R>(ph1, nb, 0, S[0]);
-    grid_sum_gram<R>(ph1, nb, 1, S[1]);
-    __syncthreads();
-    if (threadIdx.x < 2 * R * R) {
-      const int w = threadIdx.x / (R * R), e = threadIdx.x - w * R * R;
-      Mat[w][e] = ((e / R) == (e % R) ? 1.5 : 0.0) - 0.5 * S[w][e];
-    }
-    __syncthreads();
     for (int j = rb * GT + threadIdx.x; j < a.ld; j += nb * GT) {
       const double* M = Mat[j >= a.p2 ? 1 : 0];
       double row[R], res[R];
@@ -668,17 +736,22 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
 #pragma unroll
       for (int l = 0; l < R; ++l) a.L[(size_t)j * R + l] = res[l];
     }
+  } else {
+    __shared__ double SM[2][R * R];
+    if (threadIdx.x < 2 * R * R) {                          // S M
+      const int w = threadIdx.x / (R * R), e = threadIdx.x - w * R * R, i = e / R, j = e % R;
+      double sacc = 0.0;
+      for (int k = 0; k < R; ++k) sacc += S[w][i * R + k] * Mat[w][k * R + j];
+      SM[w][e] = sacc;
+    }
     __syncthreads();
-    grid_partial_gram<R>(a.L, 0, a.p2, rb, nb, ph2 + ((size_t)rb * 2 + 0) * R * R, scratch);
-    grid_partial_gram<R>(a.L, a.p2, a.ld, rb, nb, ph2 + ((size_t)rb * 2 + 1) * R * R, scratch);
-  }
-  grid.sync();
-  // ---- phase 4: W'W, C'C of the new loadings -----------------------------------------------------------
-  if (rb < 0) {
-    grid_sum_gram<R>(ph2, nb, 0, S[0]);
-    grid_sum_gram<R>(ph2, nb, 1, S[1]);
-    __syncthreads();
-    if (threadIdx.x < R * R) { st->WtW[threadIdx.x] = S[0][threadIdx.x]; st->CtC[threadIdx.x] = S[1][threadIdx.x]; }
+    if (threadIdx.x < 2 * R * R) {                          // M (S M); M is symmetric
+      const int w = threadIdx.x / (R * R), e = threadIdx.x - w * R * R, i = e / R, j = e % R;
+      double sacc = 0.0;
+      for (int k = 0; k < R; ++k) sacc += Mat[w][i * R + k] * SM[w][k * R + j];
+      (w ? st->CtC : st->WtW)[e] = sacc;
+      S[w][e] = sacc;
+    }
     __syncthreads();
     if (threadIdx.x == 0) {
       bool ok = true;
@@ -767,6 +840,48 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __re
   }
 }
 
+// The same reduction, with the result stored straight into every rank's inbox slot for this rank (peer
+// stores over NVLink; thread row y serves destination ranks y, y+8, ...).  The last block to finish raises
+// this rank's flag on every rank (fence / counter / fence: all blocks' stores are visible system-wide first).
+__global__ void __launch_bounds__(256) xsend_kernel(const double* __restrict__ partials, int nparts, int64_t len,
+                                                    const XchgDev x, const FitState* st) {
+  if (st->done) return;
+  __shared__ double sh[8][33];
+  const int64_t e = (int64_t)blockIdx.x * 32 + threadIdx.x;
+  double s0 = 0.0, s1 = 0.0;
+  if (e < len) {
+    int c = threadIdx.y;
+    for (; c + 8 < nparts; c += 16) { s0 += partials[(size_t)c * len + e]; s1 += partials[(size_t)(c + 8) * len + e]; }
+    if (c < nparts) s0 += partials[(size_t)c * len + e];
+  }
+  sh[threadIdx.y][threadIdx.x] = s0 + s1;
+  __syncthreads();
+  const unsigned long long next = *x.epoch + 1;           // epoch moves only in the update kernel (stream order)
+  if (e < len) {
+    double t = 0.0;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += sh[y][threadIdx.x];
+    const size_t off = ((size_t)(next & 1ull) * x.world + x.rank) * x.slot + e;
+    for (int r = threadIdx.y; r < x.world; r += 8) x.inbox[r][off] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && threadIdx.y == 0) {
+    __threadfence_system();                                 // cumulative: orders the whole block's stores (bar.sync above)
+    const unsigned int prev = atomicAdd(x.counter, 1u);
+    if (prev == gridDim.x - 1) {
+      *x.counter = 0;
+      __threadfence_system();
+      for (int r = 0; r < x.world; ++r) st_release_sys(x.flags[r] + (next & 1ull) * XCHG_MAXW + x.rank, next);
+    }
+  }
+}
+
+cudaError_t launch_xsend(const double* partials, int nparts, int64_t len, const XchgDev& x, const FitState* st,
+                         cudaStream_t stream) {
+  xsend_kernel<<<(unsigned)((len + 31) / 32), dim3(32, 8), 0, stream>>>(partials, nparts, len, x, st);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t len, double* momvec,
                                    const FitState* st, cudaStream_t stream) {
   reduce_partials_kernel<<<(unsigned)((len + 31) / 32), dim3(32, 8), 0, stream>>>(partials, nparts, len, momvec, st);
@@ -784,8 +899,10 @@ static void launch_update_R(const UpdateArgs& a, bool prepare, int orth_type, cu
 
 static cudaError_t dispatch_update(const DataShape& s, int R, const double* momvec, double* L,
                                    double* Lscratch, FitState* st, double* trace, bool prepare,
-                                   int orth_type, double* gscratch, cudaStream_t stream) {
+                                   int orth_type, double* gscratch, cudaStream_t stream, const XchgDev* xchg = nullptr) {
   UpdateArgs a;
+  a.use_x = xchg ? 1 : 0;
+  if (xchg) a.x = *xchg; else memset(&a.x, 0, sizeof(a.x));
   a.momvec = momvec; a.L = L; a.Lscratch = Lscratch; a.st = st; a.trace = trace; a.gscratch = gscratch;
   a.p = s.p; a.q = s.q; a.p2 = s.p2; a.q2 = s.q2; a.ld = s.ld;
   switch (R) {
@@ -803,8 +920,9 @@ static cudaError_t dispatch_update(const DataShape& s, int R, const double* momv
 }
 
 cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, double* L, double* Lscratch,
-                             FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream) {
-  return dispatch_update(s, R, momvec, L, Lscratch, st, trace, false, orth_type, gscratch, stream);
+                             FitState* st, double* trace, int orth_type, double* gscratch, cudaStream_t stream,
+                             const XchgDev* xchg) {
+  return dispatch_update(s, R, momvec, L, Lscratch, st, trace, false, orth_type, gscratch, stream, xchg);
 }
 cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream) {
   return dispatch_update(s, R, nullptr, const_cast<double*>(L), nullptr, st, nullptr, true, 0, nullptr, stream);

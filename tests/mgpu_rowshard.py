@@ -1,0 +1,74 @@
+"""Row-sharded EM on N GPUs (torchrun): one process per GPU, the moment vector exchanged once per EM
+iteration -- by the one-shot peer exchange (peer stores + flags, em_update.cu::xsend_kernel) and, for
+comparison, by the NCCL allreduce (PPLS_XCHG=0).  Checked on rank 0 against the CPU oracle on the whole data.
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/mgpu_rowshard.py [N p q r steps]"""
+import os, sys
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+from ppls_b200 import Context, Data, Fit, synth   # noqa: E402
+
+
+def fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, xchg):
+    os.environ["PPLS_XCHG"] = "1" if xchg else "0"
+    idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+    if rank == 0:
+        idt.copy_(torch.frombuffer(bytearray(Context.nccl_unique_id()), dtype=torch.uint8))
+    dist.broadcast(idt, 0)
+    ctx = Context(local, rank, world, bytes(idt.cpu().numpy().tobytes()))
+    lo, hi = N * rank // world, N * (rank + 1) // world
+    d = Data.synthetic(ctx, hi - lo, p, q, truth, seed=4242, row0=lo)
+    out = []
+    for rep in range(2):                       # two fits on one context: the exchange epoch carries over
+        f = Fit(d, st, r, steps, -np.inf, "SVD")
+        f.run()
+        out.append(f.result(want_mu=False))
+        f.close()
+    d.close()
+    dist.barrier()
+    ctx.close()
+    dist.barrier()
+    return out
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    N, p, q, r, steps = (int(a) for a in sys.argv[1:6]) if len(sys.argv) >= 6 else (20001, 301, 77, 3, 12)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
+    st = synth.start_params(truth, 3)
+    xa, xb = fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, True)
+    na, _ = fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, False)
+    # every rank must hold bit-identical parameters (rank-ordered sums on every rank)
+    t = torch.from_numpy(np.concatenate([xa["W"].ravel(), xa["C"].ravel(), xa["loglik"]])).to(dev)
+    ts = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(ts, t)
+    same_ranks = all(torch.equal(ts[0], x) for x in ts)
+    ok = True
+    if rank == 0:
+        from oracle import cbind, ppls_fused as F
+        from helpers import relmax
+        Lo = cbind.load()
+        X, Y = cbind.gen_data(Lo, 4242, 0, N, truth)
+        o = F.fused_loop(Lo, X, Y, st["W"], st["C"], st["B"], st["sigE"], st["sigF"], st["sigH"], st["sigT"],
+                         EMsteps=steps, atol=-np.inf)
+        errs = dict(loglik=relmax(xa["loglik"], o["loglik"]), W=relmax(xa["W"], o["W"]), C=relmax(xa["C"], o["C"]),
+                    B=relmax(xa["B"], o["B"]), sigT=relmax(xa["sigT"], o["sigT"]), sigE=abs(xa["sigE"] / o["sigE"] - 1),
+                    vs_nccl=relmax(xa["W"], na["W"]), repeat=relmax(xa["W"], xb["W"]))
+        ok = (same_ranks and errs["loglik"] < 1e-10 and all(v < 1e-8 for v in errs.values()) and errs["repeat"] == 0.0
+              and (world != 2 or errs["vs_nccl"] == 0.0))
+        print("ROWSHARD", "OK" if ok else "FAIL", world, "ranks", (N, p, q, r), "same_on_all_ranks", same_ranks,
+              {k: float(f"{v:.2e}") for k, v in errs.items()}, flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.stdout.flush()
+    os._exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -210,3 +210,16 @@ def test_column_sharded_two_gpus():
                         "127.0.0.1", "--master-port", "29541", os.path.join(root, "tests", "mgpu_colshard.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "COLSHARD OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_row_sharded_two_gpus_peer_exchange():
+    """Row-sharded EM over 2 ranks with the one-shot peer exchange (and the NCCL allreduce beside it) vs the
+    oracle; skipped on a 1-GPU box (tests/mgpu_rowshard.py is the torchrun entry)."""
+    import os, subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29543", os.path.join(root, "tests", "mgpu_rowshard.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "ROWSHARD OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
