@@ -52,8 +52,11 @@ class ClockSampler:
         self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
         self.index = index
         self._t = None
+        self.active = False
 
-    def start(self):
+    def prepare(self):
+        """NVML set-up and the sampling thread, BEFORE the barrier that opens the timed region (NVML
+        initialisation takes milliseconds and would skew the ranks); samples are kept once `start()` ran."""
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -66,6 +69,9 @@ class ClockSampler:
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
 
+    def start(self):
+        self.active = True
+
     def _run(self):
         nv = self.nv
         names = {
@@ -75,6 +81,9 @@ class ClockSampler:
             getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
         }
         while not self._stop.is_set():
+            if not self.active:
+                self._stop.wait(0.002)
+                continue
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
                 try:
@@ -86,7 +95,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.02)
 
     def stop(self):
         self._stop.set()
@@ -159,6 +168,7 @@ def run_ours(args):
         fit.iterate(W)
     tm0 = fit.timing()
     sampler = ClockSampler(local)
+    sampler.prepare()
     barrier()
     sampler.start()
     h0 = time.perf_counter()
@@ -171,10 +181,14 @@ def run_ours(args):
     loop_ms = tm1["loop_ms"] - tm0["loop_ms"]
     k1_ms = (tm1["stream_ms"] - tm0["stream_ms"]) / max(tm1["stream_launches"] - tm0["stream_launches"], 1)
     launches = tm1["kernel_launches"] - tm0["kernel_launches"]
+    per_rank = None
     if world > 1:
-        t = torch.tensor([loop_ms, k1_ms, wall_ms], dtype=torch.float64, device=dev)
+        t = torch.tensor([loop_ms, k1_ms, wall_ms, (tm1["tail_ms"] - tm0["tail_ms"]) / K], dtype=torch.float64, device=dev)
+        ts = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(ts, t)
+        per_rank = [[round(float(x), 4) for x in (u[0] / K, u[1], u[3])] for u in (v.cpu() for v in ts)]
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        loop_ms, k1_ms, wall_ms = (float(x) for x in t.cpu())
+        loop_ms, k1_ms, wall_ms = (float(x) for x in t.cpu()[:3])
     fit.close()
 
     # ---- e2e: the public call with HOST buffers (upload + K steps + download), on a row sample ----
@@ -246,7 +260,8 @@ def run_ours(args):
                    "generate_s": round(gen_s, 2), "wall_ms_per_step": wall_ms / K,
                    "exchange": ("none (1 GPU)" if world == 1 else "one-shot peer stores + flags, summed in rank order inside the update kernel"
                                 if tm1.get("peer_exchange") else "NCCL allreduce"),
-                   "tail_ms_per_step": (tm1["tail_ms"] - tm0["tail_ms"]) / K},
+                   "tail_ms_per_step": (tm1["tail_ms"] - tm0["tail_ms"]) / K,
+                   "per_rank_ms_step_k1_tail": per_rank},
         "clocks": clocks, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src,
@@ -278,6 +293,7 @@ def run_c5(args):
     K, W = args.steps, max(args.warmup, 1)
     PPLS_simult_batched(None, None, r, inits, EMsteps=W, atol=-float("inf"), data=data)
     sampler = ClockSampler(0)
+    sampler.prepare()
     ctx.sync(); torch.cuda.synchronize()
     sampler.start()
     h0 = time.perf_counter()

@@ -300,15 +300,28 @@ __device__ inline unsigned long long global_timer_ns() {
   asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
   return t;
 }
-// ONE thread: wait until every rank's vector of exchange `next` has landed in the local inbox.
+__device__ inline unsigned long long ld_relaxed_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ inline void st_relaxed_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+// ONE WARP (all 32 lanes call): wait until every rank's vector of exchange `next` has landed in the local
+// inbox.  Lane r polls rank r's flag (relaxed loads, all ranks in parallel); one system-scope fence then
+// orders the inbox reads of the whole block (the caller's __syncthreads follows) after the flags.
 __device__ inline void xchg_wait(const XchgDev& x, unsigned long long next) {
+  const int lane = threadIdx.x & 31;
   const unsigned long long* fl = x.flags[x.rank] + (next & 1ull) * XCHG_MAXW;
   const unsigned long long t0 = global_timer_ns();
-  for (int r = 0; r < x.world; ++r) {
-    while (ld_acquire_sys(fl + r) < next) {
-      if (global_timer_ns() - t0 > 20000000000ull) { atomicExch(x.failed, 1); return; }   // 20 s: a peer is gone
+  if (lane < x.world) {
+    while (ld_relaxed_sys(fl + lane) < next) {
+      if (global_timer_ns() - t0 > 20000000000ull) { atomicExch(x.failed, 1); break; }   // 20 s: a peer is gone
     }
   }
+  __syncwarp();
+  __threadfence_system();
 }
 // element e of the summed vector, ranks added in rank order (the same bits on every rank)
 __device__ inline double xchg_sum(const XchgDev& x, unsigned long long next, long long e) {
@@ -498,7 +511,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateA
     if (a.st->done) return;
     __shared__ int bad;
     const unsigned long long next = *a.x.epoch + 1;
-    if (threadIdx.x == 0) { xchg_wait(a.x, next); bad = *a.x.failed; }
+    if (threadIdx.x < 32) { xchg_wait(a.x, next); if (threadIdx.x == 0) bad = *a.x.failed; }
     __syncthreads();
     if (bad) { if (threadIdx.x == 0) { a.st->status = PPLS_E_NCCL; a.st->done = 1; } return; }
     double* mv = const_cast<double*>(a.momvec);
@@ -644,7 +657,7 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   // ---- phase 0 (multi-GPU peer exchange): wait for the world's vectors, sum them in rank order ------
   if (a.use_x) {
     const unsigned long long next = *a.x.epoch + 1;       // written below, after every block has read it
-    if (threadIdx.x == 0) xchg_wait(a.x, next);
+    if (threadIdx.x < 32) xchg_wait(a.x, next);
     __syncthreads();
     double* mv = const_cast<double*>(a.momvec);
     const long long len = (long long)a.ld * R + 3 * R * R;
@@ -865,14 +878,17 @@ __global__ void __launch_bounds__(256) xsend_kernel(const double* __restrict__ p
     for (int r = threadIdx.y; r < x.world; r += 8) x.inbox[r][off] = t;
   }
   __syncthreads();
+  __shared__ int last;
   if (threadIdx.x == 0 && threadIdx.y == 0) {
     __threadfence_system();                                 // cumulative: orders the whole block's stores (bar.sync above)
     const unsigned int prev = atomicAdd(x.counter, 1u);
-    if (prev == gridDim.x - 1) {
-      *x.counter = 0;
-      __threadfence_system();
-      for (int r = 0; r < x.world; ++r) st_release_sys(x.flags[r] + (next & 1ull) * XCHG_MAXW + x.rank, next);
-    }
+    last = (prev == gridDim.x - 1);
+    if (last) { *x.counter = 0; __threadfence_system(); }  // every block's stores are now ordered before the flags
+  }
+  __syncthreads();
+  if (last && threadIdx.y == 0 && threadIdx.x < x.world) {  // one lane per destination rank, in parallel
+    __threadfence_system();                                 // release pattern on the storing thread itself
+    st_relaxed_sys(x.flags[threadIdx.x] + (next & 1ull) * XCHG_MAXW + x.rank, next);
   }
 }
 
