@@ -175,6 +175,16 @@ int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int3
  * for r components: one streaming pass over the resident data. */
 int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out);
 
+/* ---- standard errors of the loadings: variances.PPLS_simult(fit, data, XorY) (EM_W_multi.R:830-860) ---- */
+/* which = 0: data = X, mu = fit$Expectations$mu_T (n x r column-major, host, this rank's rows), Cdiag =
+ * diag(fit$Expectations$Ctt); which = 1: data = Y, mu = mu_U, Cdiag = diag(Cuu).  sigE = fit$estimates$sigE
+ * for both sides, as the reference has it.  Outputs (host, column-major; w = p or q): seLoad w x r;
+ * varMatrix, SSt_exp, SSt_star r blocks of w x w (each may be NULL); B_exp r scalars (B_exp = scalar * I, may
+ * be NULL); W = orth(t(data) %*% mu) w x r (may be NULL). */
+int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, int32_t r, const double* mu, int64_t ldmu,
+                   const double* Cdiag, double sigE, double* seLoad, double* varMatrix, double* SSt_exp,
+                   double* SSt_star, double* B_exp, double* W);
+
 /* ---- batched multi-start: n_starts start states over one resident dataset ----------------- */
 /* Every start is an independent run of EM_W_multi.R:780-793 (its own break rule and trace); the
  * starts share each pass over the data (floor(8/r) starts per streaming-kernel launch).

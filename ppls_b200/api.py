@@ -18,7 +18,7 @@ import numpy as np
 from . import _lib as L
 
 __all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "normalise", "default_init",
-           "sequential_init", "default_context"]
+           "sequential_init", "default_context", "variances"]
 
 
 def _f64(a, order="F"):
@@ -448,3 +448,53 @@ def logl_W(X, Y, W, C_, B_T, sigX, sigY, sigH, sigT, ctx: Optional[Context] = No
         if own:
             data.close()
     return float(out.value)
+
+
+def variances(fit, data, XorY="X", ctx: Optional[Context] = None, dev_data: Optional[Data] = None, matrices: bool = True):
+    """Standard errors of the loadings -- mirror of variances.PPLS_simult(fit, data, XorY)
+    (Package/PPLS/R/EM_W_multi.R:830-860) on the GPU (ppls_variances).
+
+    fit: what PPLS_simult returns; data: the X (XorY='X') or Y (XorY='Y') matrix the fit was made on, or None
+    with dev_data= a resident Data handle.  Returns a dict with one entry per component 0..a-1 (each
+    {'B_exp', 'SSt_exp', 'SSt_star'}, p x p), 'varMatrix' (list of p x p) and 'seLoad' (p x a), as the
+    reference's list; matrices=False skips everything but seLoad."""
+    if isinstance(XorY, (tuple, list)):
+        XorY = XorY[0]
+    if XorY not in ("X", "Y"):
+        raise ValueError("XorY must be 'X' or 'Y'")
+    which = 0 if XorY == "X" else 1
+    Ex, est = fit["Expectations"], fit["estimates"]
+    mu = np.asfortranarray(_f64(Ex["mu_T" if which == 0 else "mu_U"]))
+    n, r = mu.shape
+    cd = _diagvec(Ex["Ctt" if which == 0 else "Cuu"], r)
+    ctx = ctx or (dev_data.ctx if dev_data is not None else default_context())
+    own = dev_data is None
+    if dev_data is None:
+        M = _f64(data)
+        if M.shape[0] != n:
+            raise ValueError("data and fit$Expectations have different numbers of rows")
+        # only one side is needed: the other is a one-column placeholder
+        z = np.zeros((n, 1))
+        dev_data = Data.from_host(ctx, M, z) if which == 0 else Data.from_host(ctx, z, M)
+    try:
+        w = dev_data.p if which == 0 else dev_data.q
+        se = np.zeros((w, r), order="F")
+        var = np.zeros((r, w, w)) if matrices else None
+        e1 = np.zeros((r, w, w)) if matrices else None
+        e2 = np.zeros((r, w, w)) if matrices else None
+        bexp = np.zeros(r)
+        Wp = np.zeros((w, r), order="F")
+        ptr = lambda a: a.ctypes.data if a is not None else None     # noqa: E731
+        L.check(L.lib().ppls_variances(ctx._h, dev_data._h, which, r, mu.ctypes.data, mu.shape[0], cd.ctypes.data,
+                                       float(np.ravel(est["sigE"])[0]), se.ctypes.data, ptr(var), ptr(e1), ptr(e2),
+                                       bexp.ctypes.data, Wp.ctypes.data))
+    finally:
+        if own:
+            dev_data.close()
+    out = dict(seLoad=se, W=Wp)
+    if matrices:
+        # blocks arrive column-major; every one of these matrices is symmetric, .T restores the orientation
+        for i in range(r):
+            out[i] = dict(B_exp=bexp[i] * np.eye(w), SSt_exp=e1[i].T, SSt_star=e2[i].T)
+        out["varMatrix"] = [var[i].T for i in range(r)]
+    return out

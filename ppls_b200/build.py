@@ -18,6 +18,7 @@ UNITS = {
     "em_wide.cu": [],
     "em_update.cu": ["-fmad=false"],
     "em_seq.cu": ["-fmad=false"],
+    "em_var.cu": [],
     "data.cu": ["-fmad=false"],
     "capi.cu": [],
 }

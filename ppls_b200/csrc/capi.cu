@@ -1054,3 +1054,89 @@ extern "C" int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const p
   fit_free(f);
   return rc;
 }
+
+// ---- standard errors of the loadings: variances.PPLS_simult (EM_W_multi.R:830-860) -----------------------
+// which = 0: data = X, mu = fit$Expectations$mu_T, Cdiag = diag(fit$Expectations$Ctt);
+// which = 1: data = Y, mu = mu_U, Cdiag = diag(Cuu).  sigE = fit$estimates$sigE in BOTH cases (the reference
+// divides by sigE also for Y, :844,:848,:851).  Kernels: csrc/em_var.cu.
+extern "C" int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, int32_t r, const double* mu, int64_t ldmu,
+                              const double* Cdiag, double sigE, double* seLoad, double* varMatrix, double* SSt_exp,
+                              double* SSt_star, double* B_exp, double* Wout) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!d || !mu || !Cdiag || !seLoad) return fail(PPLS_E_INVALID, "null argument");
+  if (d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
+  if (d->colshard) return fail(PPLS_E_UNSUPPORTED, "variances: row-sharded data only");
+  if (r < 1 || r > MAXR) return fail(PPLS_E_INVALID, "nr_comp outside 1..8");
+  if (which != 0 && which != 1) return fail(PPLS_E_INVALID, "which must be 0 (X) or 1 (Y)");
+  const DataShape& sh = d->s;
+  if (ldmu < sh.n) return fail(PPLS_E_INVALID, "leading dimension of mu smaller than the row count");
+  if (!(sigE > 0.0)) return fail(PPLS_E_INVALID, "sigE must be positive");
+  VarPlan vp;
+  plan_var(sh, which, ctx->sm_count, &vp);
+  const int w = vp.w, R = r;
+  const size_t ww = (size_t)w * w;
+  struct Bufs {
+    double *ws = nullptr, *S = nullptr, *G = nullptr, *cp = nullptr, *mu = nullptr, *Wp = nullptr, *aug = nullptr,
+           *rowbuf = nullptr, *se = nullptr, *var = nullptr, *e1 = nullptr, *e2 = nullptr;
+    int* info = nullptr;
+    ~Bufs() {
+      cudaFree(ws); cudaFree(S); cudaFree(G); cudaFree(cp); cudaFree(mu); cudaFree(Wp); cudaFree(aug); cudaFree(rowbuf);
+      cudaFree(se); cudaFree(var); cudaFree(e1); cudaFree(e2); cudaFree(info);
+    }
+  } B;
+  CU(cudaMalloc(&B.ws, var_workspace_doubles(vp, R) * sizeof(double)));
+  CU(cudaMalloc(&B.S, ww * sizeof(double)));
+  CU(cudaMalloc(&B.G, ((size_t)w * R + R) * sizeof(double)));
+  B.cp = nullptr;
+  CU(cudaMalloc(&B.mu, (size_t)sh.n * R * sizeof(double)));
+  CU(cudaMalloc(&B.Wp, (size_t)w * R * sizeof(double)));
+  CU(cudaMalloc(&B.aug, 2 * ww * sizeof(double)));
+  CU(cudaMalloc(&B.rowbuf, (size_t)5 * w * sizeof(double)));
+  CU(cudaMalloc(&B.se, (size_t)w * sizeof(double)));
+  CU(cudaMalloc(&B.info, 2 * sizeof(int)));
+  if (varMatrix) CU(cudaMalloc(&B.var, ww * sizeof(double)));
+  if (SSt_exp) CU(cudaMalloc(&B.e1, ww * sizeof(double)));
+  if (SSt_star) CU(cudaMalloc(&B.e2, ww * sizeof(double)));
+  double* cpd = B.G + (size_t)w * R;               // cp rides behind G: one allreduce for both
+  {  // mu: column-major n x r on the host -> [n][R] row-major on the device
+    std::vector<double> t((size_t)sh.n * R);
+    for (int k = 0; k < R; ++k)
+      for (int64_t i = 0; i < sh.n; ++i) t[(size_t)i * R + k] = mu[i + (size_t)k * ldmu];
+    CU(cudaMemcpyAsync(B.mu, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+  }
+  CU(launch_var_gram(vp, sh, d->D, B.ws, B.S, ctx->stream));
+  CU(launch_var_xtmu(vp, sh, d->D, B.mu, R, B.ws, B.G, cpd, ctx->stream));
+  rc = allreduce_sum(ctx, B.S, ww);
+  if (rc) return rc;
+  rc = allreduce_sum(ctx, B.G, (size_t)w * R + R);
+  if (rc) return rc;
+  CU(launch_orth_polar(R, B.G, w, B.Wp, ctx->stream));                                    // :831-832
+  double cph[MAXR];
+  CU(cudaMemcpyAsync(cph, cpd, R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  const double N = (double)d->n_total;
+  for (int i = 0; i < R; ++i) {
+    const double CttN = N * Cdiag[i];                                                     // :840
+    CU(launch_var_assemble(w, R, i, B.S, B.G, B.Wp, CttN, cph[i], sigE, N, B.aug, B.e1, B.e2, ctx->stream));
+    CU(launch_var_invert(w, B.aug, B.rowbuf, B.info, B.var, B.se, ctx->stream));
+    int info[2] = {0, 0};
+    CU(cudaMemcpyAsync(info, B.info, sizeof(info), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaMemcpyAsync(seLoad + (size_t)i * w, B.se, (size_t)w * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (varMatrix) CU(cudaMemcpyAsync(varMatrix + (size_t)i * ww, B.var, ww * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (SSt_exp) CU(cudaMemcpyAsync(SSt_exp + (size_t)i * ww, B.e1, ww * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    if (SSt_star) CU(cudaMemcpyAsync(SSt_star + (size_t)i * ww, B.e2, ww * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (info[0]) return fail(PPLS_E_NONFINITE, "variances: B_exp - SSt_exp is singular (zero pivot)");
+    if (B_exp) B_exp[i] = CttN / (sigE * sigE) * 1.0 / N;                                   // :844 (times I_p)
+  }
+  if (Wout) {
+    std::vector<double> t((size_t)w * R);
+    CU(cudaMemcpyAsync(t.data(), B.Wp, t.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < R; ++k)
+      for (int j = 0; j < w; ++j) Wout[j + (size_t)k * w] = t[(size_t)j * R + k];
+  }
+  return PPLS_OK;
+}

@@ -129,6 +129,31 @@ cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int
                                    const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,
                                    double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream);
 int update_grid_blocks(int ld);
+cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream);
+
+// ---- standard errors of the loadings (em_var.cu; variances.PPLS_simult, EM_W_multi.R:830-860) -----------
+struct VarPlan {
+  int w;              // columns of the side (p or q)
+  int c0;             // first column of the side in a data row (0 or p2)
+  int nb, ntiles;     // 128-column blocks, block pairs bi <= bj
+  int nsplit;         // row splits of the Gram kernel
+  int64_t rows_per_split;
+  int gsplit;         // row splits of the X'mu kernel
+  int64_t grows_per_split;
+};
+void plan_var(const DataShape& s, int which, int sm_count, VarPlan* plan);
+size_t var_workspace_doubles(const VarPlan& p, int R);
+// S = side' side (w x w, row-major, both triangles), summed over this rank's rows
+cudaError_t launch_var_gram(const VarPlan& p, const DataShape& s, const double* D, double* partial, double* S, cudaStream_t stream);
+// G = side' mu (w x R row-major), cp[k] = sum_i mu[i][k]^2; mu: [n][R] row-major on the device
+cudaError_t launch_var_xtmu(const VarPlan& p, const DataShape& s, const double* D, const double* mu, int R, double* partial,
+                            double* G, double* cp, cudaStream_t stream);
+// per component: A = B_exp I - SSt_exp into the augmented matrix [A | I] (w x 2w), optional copies of SSt_exp, SSt_star
+cudaError_t launch_var_assemble(int w, int R, int comp, const double* S, const double* G, const double* Wpol, double CttN,
+                                double cp, double sigE, double Ntot, double* aug, double* SSt_exp, double* SSt_star,
+                                cudaStream_t stream);
+// in-place Gauss-Jordan with partial pivoting on [A | I]; then var = -inv(A) (column-major w x w, optional), se = sqrt(diag)
+cudaError_t launch_var_invert(int w, double* aug, double* rowbuf, int* info, double* var_out, double* se_out, cudaStream_t stream);
 size_t update_grid_scratch_doubles(int ld, int R);
 // Prepare coefficients + Gram matrices for the start state (pass 0).
 cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream);

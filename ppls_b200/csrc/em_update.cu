@@ -774,6 +774,27 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   }
 }
 
+// orth(G, "SVD") alone (variances.PPLS_simult, EM_W_multi.R:831-832): out = polar factor of G [n][R].
+template <int R>
+__global__ void __launch_bounds__(UPD_THREADS, 1) orth_only_kernel(const double* G, int n, double* out) {
+  __shared__ double scratch[UPD_WARPS * 36], S[R * R], Mat[R * R];
+  orth_polar<R>(G, n, out, S, Mat, scratch);
+}
+cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream) {
+  switch (R) {
+    case 1: orth_only_kernel<1><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 2: orth_only_kernel<2><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 3: orth_only_kernel<3><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 4: orth_only_kernel<4><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 5: orth_only_kernel<5><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 6: orth_only_kernel<6><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 7: orth_only_kernel<7><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 8: orth_only_kernel<8><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
 int update_grid_blocks(int ld) {
   int nb = (ld + GT - 1) / GT;
   if (nb > 96) nb = 96;
