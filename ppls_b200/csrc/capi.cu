@@ -1106,8 +1106,14 @@ extern "C" int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, 
     CU(cudaMemcpyAsync(B.mu, t.data(), t.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
   }
+  const char* vb = getenv("PPLS_VAR_VERBOSE");
+  const bool verbose = vb && *vb && atoi(vb) != 0;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  if (verbose) { for (auto& x : ev) cudaEventCreate(&x); cudaEventRecord(ev[0], ctx->stream); }
   CU(launch_var_gram(vp, sh, d->D, B.ws, B.S, ctx->stream));
+  if (verbose) cudaEventRecord(ev[1], ctx->stream);
   CU(launch_var_xtmu(vp, sh, d->D, B.mu, R, B.ws, B.G, cpd, ctx->stream));
+  if (verbose) cudaEventRecord(ev[2], ctx->stream);
   rc = allreduce_sum(ctx, B.S, ww);
   if (rc) return rc;
   rc = allreduce_sum(ctx, B.G, (size_t)w * R + R);
@@ -1130,6 +1136,17 @@ extern "C" int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, 
     CU(cudaStreamSynchronize(ctx->stream));
     if (info[0]) return fail(PPLS_E_NONFINITE, "variances: B_exp - SSt_exp is singular (zero pivot)");
     if (B_exp) B_exp[i] = CttN / (sigE * sigE) * 1.0 / N;                                   // :844 (times I_p)
+  }
+  if (verbose) {
+    cudaEventRecord(ev[3], ctx->stream);
+    cudaEventSynchronize(ev[3]);
+    float g = 0, x = 0, rest = 0;
+    cudaEventElapsedTime(&g, ev[0], ev[1]); cudaEventElapsedTime(&x, ev[1], ev[2]); cudaEventElapsedTime(&rest, ev[2], ev[3]);
+    const double flop = 2.0 * vp.ntiles * 128.0 * 128.0 * (double)sh.n, bytes = 8.0 * (double)sh.n * (which ? sh.q2 : sh.p2);
+    fprintf(stderr, "[ppls] variances: n=%lld w=%d r=%d | gram %.3f ms (%d tiles x %d splits, %.2f TFLOP/s FP64) | "
+                    "X'mu %.3f ms (%.0f GB/s) | %d x (assemble + invert) %.3f ms\n",
+            (long long)sh.n, w, R, g, vp.ntiles, vp.nsplit, flop / (g * 1e-3) / 1e12, x, bytes / (x * 1e-3) / 1e9, R, rest);
+    for (auto& e : ev) cudaEventDestroy(e);
   }
   if (Wout) {
     std::vector<double> t((size_t)w * R);

@@ -267,7 +267,8 @@ __global__ void __launch_bounds__(256) gj_elim_kernel(double* aug, int w, int k,
   const int i = blockIdx.y;
   const double* prow = rowbuf; const double* krow = rowbuf + 2 * w; const double* fcol = rowbuf + 4 * w;
   double* row = aug + (size_t)i * 2 * w;
-  for (int j = blockIdx.x * 256 + threadIdx.x; j < 2 * w; j += gridDim.x * 256) {
+  // columns j < k of the left half are unit vectors already and the pivot row is zero there: nothing changes
+  for (int j = k + blockIdx.x * 256 + threadIdx.x; j < 2 * w; j += gridDim.x * 256) {
     if (i == k) row[j] = prow[j];
     else if (i == r) row[j] = krow[j] - krow[k] * prow[j];        // the old row k lands in row r, eliminated
     else row[j] = row[j] - fcol[i] * prow[j];
@@ -290,11 +291,20 @@ void plan_var(const DataShape& s, int which, int sm_count, VarPlan* p) {
   const int w2 = which ? s.q2 : s.p2;
   p->nb = (w2 + VT - 1) / VT;
   p->ntiles = p->nb * (p->nb + 1) / 2;
-  // Gram: about 2 waves of one CTA per SM, at least 8 stages of rows per CTA
-  int64_t ns = (2 * (int64_t)sm_count + p->ntiles - 1) / p->ntiles;
+  // Gram: one CTA per SM (232 registers); the row split is chosen so that tiles x splits fills whole waves
+  // of sm_count CTAs (>= 4 waves when the rows allow), at least 8 stages of rows per CTA
   const int64_t max_ns = (s.n + 8 * VK - 1) / (8 * VK);
-  if (ns > max_ns) ns = max_ns;
-  if (ns < 1) ns = 1;
+  int64_t lo = (4 * (int64_t)sm_count + p->ntiles - 1) / p->ntiles, ns = 1;
+  if (lo < 1) lo = 1;
+  double best = -1.0;
+  for (int64_t c = lo; c < lo + 64; ++c) {
+    const int64_t cc = c > max_ns ? max_ns : c;
+    if (cc < 1) continue;
+    const int64_t ctas = cc * p->ntiles, waves = (ctas + sm_count - 1) / sm_count;
+    const double eff = (double)ctas / (double)(waves * sm_count);
+    if (eff > best + 1e-9) { best = eff; ns = cc; }
+    if (cc == max_ns) break;
+  }
   int64_t rps = (s.n + ns - 1) / ns;
   rps = (rps + VK - 1) / VK * VK;
   p->nsplit = (int)((s.n + rps - 1) / rps);
