@@ -113,6 +113,15 @@ int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, const doubl
  * any sharding).  `truth` holds the generating parameters with r components. */
 int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
                         uint64_t seed, const ppls_params* truth, ppls_data** out);
+/* simulC(N, W, C, P_Yosc, P_Xosc, B_T, sigX, sigY, sigH, sigT, sigTo, sigUo) of Package/PPLS/src/loglC.cpp:269-315
+ * (R/RcppExports.R:12-30) as a resident dataset: X = T W' + TYo P_Yosc' + E, Y = U C' + UXo P_Xosc' + F with
+ * T = Z diag(sigT), U = T diag(B) + H, TYo = Z diag(sigTo), UXo = Z diag(sigUo); r >= 1 components (the reference's
+ * code type-checks for one).  P_Yosc p x nx, P_Xosc q x ny column-major (nx, ny in 0..8); normals from the
+ * counter-based generator (seed, global row, column), so any row range [row0, row0+n) gives the same sample. */
+int ppls_data_simulc(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r, int32_t nx, int32_t ny,
+                     uint64_t seed, const ppls_params* truth, const double* P_Yosc, const double* P_Xosc,
+                     const double* sigTo, const double* sigUo, ppls_data** out);
+
 /* Column-sharded variants (wide shapes, p >> N): every rank holds ALL n rows of a block of
  * p_local columns of X and q_local columns of Y (blocks in rank order).  Start values / estimates passed
  * to ppls_fit_* are then the rank's ROWS of W (p_local x r) and C (q_local x r); per EM iteration the

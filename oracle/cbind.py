@@ -20,6 +20,10 @@ def declare(L):
     L.ppls_gen_data.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double,
                                 C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
+    L.ppls_gen_data_orth.restype = None
+    L.ppls_gen_data_orth.argtypes = [C.c_uint64, C.c_uint64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64]
     L.ppls_oracle_moments.restype = None
     L.ppls_oracle_moments.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -53,6 +57,22 @@ def gen_data(L, seed, row0, nrows, truth):
     L.ppls_gen_data(seed, row0, nrows, p, q, r, W.ctypes.data, Cm.ctypes.data, b.ctypes.data, t.ctypes.data,
                     float(truth["sigE"]), float(truth["sigF"]), float(truth["sigH"]),
                     X.ctypes.data, max(nrows, 1), Y.ctypes.data, max(nrows, 1))
+    return X, Y
+
+
+def gen_data_orth(L, seed, row0, nrows, truth, P_Yosc, P_Xosc, sigTo, sigUo):
+    """simulC's model with orthogonal parts (loglC.cpp:288-311) on the counter-based generator."""
+    W = _f(truth["W"]); Cm = _f(truth["C"])
+    p, r = W.shape; q = Cm.shape[0]
+    PY = _f(np.reshape(P_Yosc, (p, -1))); PX = _f(np.reshape(P_Xosc, (q, -1)))
+    nx, ny = PY.shape[1], PX.shape[1]
+    b = np.ascontiguousarray(truth["B"], dtype=np.float64); t = np.ascontiguousarray(truth["sigT"], dtype=np.float64)
+    to = np.ascontiguousarray(np.ravel(sigTo), dtype=np.float64); uo = np.ascontiguousarray(np.ravel(sigUo), dtype=np.float64)
+    X = np.empty((nrows, p), order="F"); Y = np.empty((nrows, q), order="F")
+    L.ppls_gen_data_orth(seed, row0, nrows, p, q, r, nx, ny, W.ctypes.data, Cm.ctypes.data, PY.ctypes.data, PX.ctypes.data,
+                         b.ctypes.data, t.ctypes.data, to.ctypes.data, uo.ctypes.data,
+                         float(truth["sigE"]), float(truth["sigF"]), float(truth["sigH"]),
+                         X.ctypes.data, max(nrows, 1), Y.ctypes.data, max(nrows, 1))
     return X, Y
 
 

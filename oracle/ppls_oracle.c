@@ -152,6 +152,48 @@ void ppls_gen_data(uint64_t seed, uint64_t row0, int64_t nrows, int32_t p, int32
   }
 }
 
+/* The same sample with simulC's orthogonal parts (Package/PPLS/src/loglC.cpp:288-311):
+ *   X = T W' + TYo P_Yosc' + sigE Z_E,  Y = U C' + UXo P_Xosc' + sigF Z_F,
+ *   TYo = Z_To diag(sigTo) (stream 4), UXo = Z_Uo diag(sigUo) (stream 5).
+ * P_Yosc (p x nx), P_Xosc (q x ny) column-major.  nx = ny = 0 gives ppls_gen_data's bits. */
+void ppls_gen_data_orth(uint64_t seed, uint64_t row0, int64_t nrows, int32_t p, int32_t q, int32_t r,
+                        int32_t nx, int32_t ny, const double* W, const double* C, const double* PYo,
+                        const double* PXo, const double* b, const double* t, const double* sigTo,
+                        const double* sigUo, double sigE, double sigF, double sigH,
+                        double* X, int64_t ldX, double* Y, int64_t ldY) {
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < nrows; ++i) {
+    double T[16], U[16], To[16], Uo[16];
+    uint64_t row = row0 + (uint64_t)i;
+    for (int k = 0; k < r; ++k) {
+      T[k] = t[k] * ppls_gen_normal(seed, 0u, row, (uint32_t)k);
+      U[k] = T[k] * b[k] + sigH * ppls_gen_normal(seed, 1u, row, (uint32_t)k);
+    }
+    for (int k = 0; k < nx; ++k) To[k] = sigTo[k] * ppls_gen_normal(seed, 4u, row, (uint32_t)k);
+    for (int k = 0; k < ny; ++k) Uo[k] = sigUo[k] * ppls_gen_normal(seed, 5u, row, (uint32_t)k);
+    for (int32_t j = 0; j < p; ++j) {
+      double acc = 0.0;
+      for (int k = 0; k < r; ++k) acc = acc + T[k] * W[j + (int64_t)k * p];
+      if (nx > 0) {
+        double ao = 0.0;
+        for (int k = 0; k < nx; ++k) ao = ao + To[k] * PYo[j + (int64_t)k * p];
+        acc = acc + ao;
+      }
+      X[i + (int64_t)j * ldX] = acc + sigE * ppls_gen_normal(seed, 2u, row, (uint32_t)j);
+    }
+    for (int32_t j = 0; j < q; ++j) {
+      double acc = 0.0;
+      for (int k = 0; k < r; ++k) acc = acc + U[k] * C[j + (int64_t)k * q];
+      if (ny > 0) {
+        double ao = 0.0;
+        for (int k = 0; k < ny; ++k) ao = ao + Uo[k] * PXo[j + (int64_t)k * q];
+        acc = acc + ao;
+      }
+      Y[i + (int64_t)j * ldY] = acc + sigF * ppls_gen_normal(seed, 3u, row, (uint32_t)j);
+    }
+  }
+}
+
 /* One fused pass over X and Y (the data-dependent part of one EM iteration).
  *   Xw = X W, Yc = Y C                                   EM_W_multi.R:689-690
  *   mu_T[:,k] = aT[k] Xw[:,k] + bT[k] Yc[:,k]            :691-692 (diagonal algebra collapsed)

@@ -18,7 +18,7 @@ import numpy as np
 from . import _lib as L
 
 __all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "normalise", "default_init",
-           "sequential_init", "default_context", "variances"]
+           "sequential_init", "default_context", "variances", "simulC"]
 
 
 def _f64(a, order="F"):
@@ -126,6 +126,24 @@ class Data:
         pb = _ParamsBuf(p, q, r, truth["W"], truth["C"], truth["B"], truth["sigT"], truth["sigE"], truth["sigF"], truth["sigH"])
         h = C.c_void_p()
         L.check(L.lib().ppls_data_synthetic(ctx._h, n, row0, p, q, r, seed, C.byref(pb.struct), C.byref(h)))
+        return cls(ctx, h)
+
+    @classmethod
+    def simulc(cls, ctx: Context, n: int, truth: dict, P_Yosc=None, P_Xosc=None, sigTo=None, sigUo=None, seed: int = 1,
+               row0: int = 0) -> "Data":
+        """Resident sample of simulC's model (loglC.cpp:269-315) with optional orthogonal parts."""
+        W = _f64(truth["W"]); Cm = _f64(truth["C"])
+        p, r = W.shape; q = Cm.shape[0]
+        PY = np.asfortranarray(_f64(P_Yosc).reshape(p, -1)) if P_Yosc is not None else np.zeros((p, 0), order="F")
+        PX = np.asfortranarray(_f64(P_Xosc).reshape(q, -1)) if P_Xosc is not None else np.zeros((q, 0), order="F")
+        nx, ny = PY.shape[1], PX.shape[1]
+        to = _diagvec(sigTo if sigTo is not None else np.zeros(nx), nx)
+        uo = _diagvec(sigUo if sigUo is not None else np.zeros(ny), ny)
+        pb = _ParamsBuf(p, q, r, W, Cm, truth["B"], truth["sigT"], truth["sigE"], truth["sigF"], truth["sigH"])
+        h = C.c_void_p()
+        L.check(L.lib().ppls_data_simulc(ctx._h, n, row0, p, q, r, nx, ny, seed, C.byref(pb.struct),
+                                         PY.ctypes.data if nx else None, PX.ctypes.data if ny else None,
+                                         to.ctypes.data if nx else None, uo.ctypes.data if ny else None, C.byref(h)))
         return cls(ctx, h)
 
     @classmethod
@@ -498,3 +516,20 @@ def variances(fit, data, XorY="X", ctx: Optional[Context] = None, dev_data: Opti
             out[i] = dict(B_exp=bexp[i] * np.eye(w), SSt_exp=e1[i].T, SSt_star=e2[i].T)
         out["varMatrix"] = [var[i].T for i in range(r)]
     return out
+
+
+def simulC(N, W, C_, P_Yosc, P_Xosc, B_T, sigX, sigY, sigH, sigT, sigTo, sigUo, seed: int = 1, ctx: Optional[Context] = None):
+    """Mirror of simulC (Package/PPLS/src/loglC.cpp:269-315; R/RcppExports.R:12-30): returns Dat, N x (p+q),
+    rows = samples, columns = X and Y side by side.  Generated on the GPU (ppls_data_simulc) from a
+    counter-based generator -- `seed` replaces R's RNG state, which cannot be reproduced outside R.
+    B_T, sigT, sigTo, sigUo: diagonal matrices or vectors.  Use Data.simulc to keep the sample resident."""
+    ctx = ctx or default_context()
+    W = _f64(W); W = W.reshape(W.shape[0], -1)
+    truth = dict(W=W, C=_f64(C_).reshape(-1, W.shape[1]), B=B_T, sigT=sigT, sigE=float(np.ravel(sigX)[0]),
+                 sigF=float(np.ravel(sigY)[0]), sigH=float(np.ravel(sigH)[0]))
+    d = Data.simulc(ctx, int(N), truth, P_Yosc, P_Xosc, sigTo, sigUo, seed)
+    try:
+        X, Y = d.export()
+    finally:
+        d.close()
+    return np.hstack([X, Y])

@@ -398,8 +398,10 @@ static int check_params(const ppls_params* P, const char* what) {
   return PPLS_OK;
 }
 
+struct HostOrth { int nx = 0, ny = 0; const double *PYo = nullptr, *PXo = nullptr, *sigTo = nullptr, *sigUo = nullptr; };
 static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int64_t colX0, int64_t colY0,
-                               int colshard, int32_t r, uint64_t seed, const ppls_params* truth, ppls_data** out);
+                               int colshard, int32_t r, uint64_t seed, const ppls_params* truth, ppls_data** out,
+                               const HostOrth* ho = nullptr);
 extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
                                    uint64_t seed, const ppls_params* truth, ppls_data** out) {
   return data_synthetic_impl(ctx, n, row0, p, q, 0, 0, 0, r, seed, truth, out);
@@ -410,7 +412,8 @@ extern "C" int ppls_data_synthetic_cols(ppls_ctx* ctx, int64_t n, int64_t p_loca
   return data_synthetic_impl(ctx, n, 0, p_local, q_local, colX0, colY0, 1, r, seed, truth_local, out);
 }
 static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int64_t colX0, int64_t colY0,
-                               int colshard, int32_t r, uint64_t seed, const ppls_params* truth, ppls_data** out) {
+                               int colshard, int32_t r, uint64_t seed, const ppls_params* truth, ppls_data** out,
+                               const HostOrth* ho) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   *out = nullptr;
   int rc = ctx_activate(ctx);
@@ -436,9 +439,24 @@ static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p
   for (int k = 0; k < r; ++k) { bt[k] = truth->B[k]; bt[MAXR + k] = truth->sigT[k]; }
   if (e == cudaSuccess) e = cudaMemcpyAsync(dL, L.data(), L.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(dbt, bt, sizeof(bt), cudaMemcpyHostToDevice, ctx->stream);
+  // orthogonal parts: P_Yosc (p x nx), P_Xosc (q x ny) column-major on the host -> row-major on the device
+  SynthOrth so{};
+  double* dO = nullptr;
+  std::vector<double> ob;
+  if (ho && (ho->nx > 0 || ho->ny > 0)) {
+    so.nx = ho->nx; so.ny = ho->ny;
+    const size_t o1 = 0, o2 = o1 + (size_t)p * so.nx, o3 = o2 + (size_t)q * so.ny, o4 = o3 + MAXR;
+    ob.assign(o4 + MAXR, 0.0);
+    for (int k = 0; k < so.nx; ++k) { for (int64_t j = 0; j < p; ++j) ob[o1 + (size_t)j * so.nx + k] = ho->PYo[j + (size_t)k * p]; ob[o3 + k] = ho->sigTo[k]; }
+    for (int k = 0; k < so.ny; ++k) { for (int64_t j = 0; j < q; ++j) ob[o2 + (size_t)j * so.ny + k] = ho->PXo[j + (size_t)k * q]; ob[o4 + k] = ho->sigUo[k]; }
+    if (e == cudaSuccess) e = cudaMalloc(&dO, ob.size() * sizeof(double));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dO, ob.data(), ob.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+    so.PYo = dO + o1; so.PXo = dO + o2; so.sigTo = dO + o3; so.sigUo = dO + o4;
+  }
   if (e == cudaSuccess)
-    e = launch_synth(d->D, d->s, row0, (uint32_t)colX0, (uint32_t)colY0, r, seed, dL, dbt, dbt + MAXR, truth->sigE, truth->sigF, truth->sigH, ctx->stream);
+    e = launch_synth(d->D, d->s, row0, (uint32_t)colX0, (uint32_t)colY0, r, seed, dL, dbt, dbt + MAXR, truth->sigE, truth->sigF, truth->sigH, ctx->stream, &so);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (dO) cudaFree(dO);
   if (dL) cudaFree(dL);
   if (dbt) cudaFree(dbt);
   if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_CUDA, std::string("synthetic generator: ") + cudaGetErrorString(e)); }
@@ -446,6 +464,19 @@ static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p
   if (rc) { cudaFree(d->D); delete d; return rc; }
   *out = d;
   return PPLS_OK;
+}
+
+// simulC(N, W, C, P_Yosc, P_Xosc, B_T, sigX, sigY, sigH, sigT, sigTo, sigUo) (Package/PPLS/src/loglC.cpp:269-315,
+// R doc R/RcppExports.R:12-30) as a resident dataset: the same model, generalised to r components, on the
+// counter-based generator (R's RNG stream cannot be reproduced outside R).
+extern "C" int ppls_data_simulc(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r, int32_t nx, int32_t ny,
+                                uint64_t seed, const ppls_params* truth, const double* P_Yosc, const double* P_Xosc,
+                                const double* sigTo, const double* sigUo, ppls_data** out) {
+  if (nx < 0 || ny < 0 || nx > MAXR || ny > MAXR) return fail(PPLS_E_INVALID, "orthogonal components outside 0..8");
+  if ((nx > 0 && (!P_Yosc || !sigTo)) || (ny > 0 && (!P_Xosc || !sigUo))) return fail(PPLS_E_INVALID, "null orthogonal loadings");
+  HostOrth ho;
+  ho.nx = nx; ho.ny = ny; ho.PYo = P_Yosc; ho.PXo = P_Xosc; ho.sigTo = sigTo; ho.sigUo = sigUo;
+  return data_synthetic_impl(ctx, n, row0, p, q, 0, 0, 0, r, seed, truth, out, &ho);
 }
 
 extern "C" int ppls_data_export(ppls_ctx* ctx, const ppls_data* d, int64_t row0, int64_t n, double* X, int64_t ldX,

@@ -170,8 +170,16 @@ cudaError_t launch_untile(const double* D, const DataShape& s, int col0, int64_t
 cudaError_t launch_zero_pad(double* D, const DataShape& s, cudaStream_t stream);
 cudaError_t launch_ssq(const double* D, const DataShape& s, double* out2, double* scratch, int nblocks,
                        cudaStream_t stream);
+// orthogonal parts of simulC (loglC.cpp:269-315): X += TYo P_Yosc', Y += UXo P_Xosc'; device pointers
+struct SynthOrth {
+  int nx = 0, ny = 0;
+  const double* PYo = nullptr;    // [p][nx] row-major
+  const double* PXo = nullptr;    // [q][ny] row-major
+  const double* sigTo = nullptr;  // [nx]
+  const double* sigUo = nullptr;  // [ny]
+};
 cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t colX0, uint32_t colY0, int R, uint64_t seed,
                          const double* Ltruth /*[ld][R]*/, const double* b, const double* t,
-                         double sigE, double sigF, double sigH, cudaStream_t stream);
+                         double sigE, double sigF, double sigH, cudaStream_t stream, const SynthOrth* orth = nullptr);
 
 }  // namespace ppls

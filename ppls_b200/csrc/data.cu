@@ -196,7 +196,7 @@ __device__ double det_ndtri(double u) {
   return (q < 0.0) ? -z : z;
 }
 
-// streams: 0 Z_T, 1 Z_H, 2 Z_E, 3 Z_F
+// streams: 0 Z_T, 1 Z_H, 2 Z_E, 3 Z_F, 4 Z_To (Y-orthogonal part of X), 5 Z_Uo (X-orthogonal part of Y)
 __device__ __forceinline__ double gen_normal(uint64_t seed, uint32_t stream, uint64_t row, uint32_t col) {
   uint32_t c[4] = {(uint32_t)row, (uint32_t)(row >> 32), col, stream};
   philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
@@ -209,8 +209,8 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, cons
                                                     uint32_t cx0, uint32_t cy0, int R, uint64_t seed,
                                                     const double* __restrict__ Lt, const double* __restrict__ b,
                                                     const double* __restrict__ t, double sigE, double sigF,
-                                                    double sigH) {
-  __shared__ double Ts[SYN_ROWS][MAXR], Us[SYN_ROWS][MAXR];
+                                                    double sigH, const SynthOrth o) {
+  __shared__ double Ts[SYN_ROWS][MAXR], Us[SYN_ROWS][MAXR], Tos[SYN_ROWS][MAXR], Uos[SYN_ROWS][MAXR];
   const int64_t n = s.n; const int ld = s.ld, p = s.p, p2 = s.p2, q = s.q;
   const int64_t ngroups = (n + SYN_ROWS - 1) / SYN_ROWS;
   for (int64_t g = blockIdx.x; g < ngroups; g += gridDim.x) {
@@ -225,6 +225,15 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, cons
         Us[i][k] = T * b[k] + sigH * gen_normal(seed, 1u, row, (uint32_t)k);
       }
     }
+    // simulC's orthogonal parts (loglC.cpp:290-291,304-305): TYo = Z_To diag(sigTo), UXo = Z_Uo diag(sigUo)
+    if ((int)threadIdx.x < SYN_ROWS * MAXR) {
+      const int i = threadIdx.x / MAXR, k = threadIdx.x - i * MAXR;
+      if (i0 + i < n) {
+        const uint64_t row = (uint64_t)(row0 + i0 + i);
+        if (k < o.nx) Tos[i][k] = o.sigTo[k] * gen_normal(seed, 4u, row, (uint32_t)k);
+        if (k < o.ny) Uos[i][k] = o.sigUo[k] * gen_normal(seed, 5u, row, (uint32_t)k);
+      }
+    }
     __syncthreads();
     for (int i = 0; i < SYN_ROWS && i0 + i < n; ++i) {
       const uint64_t row = (uint64_t)(row0 + i0 + i);
@@ -233,10 +242,20 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, cons
         if (j < p) {
           double acc = 0.0;
           for (int k = 0; k < R; ++k) acc = acc + Ts[i][k] * Lt[(size_t)j * R + k];
+          if (o.nx > 0) {
+            double ao = 0.0;
+            for (int k = 0; k < o.nx; ++k) ao = ao + Tos[i][k] * o.PYo[(size_t)j * o.nx + k];
+            acc = acc + ao;
+          }
           v = acc + sigE * gen_normal(seed, 2u, row, cx0 + (uint32_t)j);
         } else if (j >= p2 && j - p2 < q) {
           double acc = 0.0;
           for (int k = 0; k < R; ++k) acc = acc + Us[i][k] * Lt[(size_t)j * R + k];
+          if (o.ny > 0) {
+            double ao = 0.0;
+            for (int k = 0; k < o.ny; ++k) ao = ao + Uos[i][k] * o.PXo[(size_t)(j - p2) * o.ny + k];
+            acc = acc + ao;
+          }
           v = acc + sigF * gen_normal(seed, 3u, row, cy0 + (uint32_t)(j - p2));
         }
         D[data_index(s, i0 + i, j)] = v;
@@ -247,10 +266,12 @@ __global__ void __launch_bounds__(256) synth_kernel(double* __restrict__ D, cons
 
 cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t colX0, uint32_t colY0, int R, uint64_t seed, const double* Ltruth,
                          const double* b, const double* t, double sigE, double sigF, double sigH,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, const SynthOrth* orth) {
+  SynthOrth o{};
+  if (orth) o = *orth;
   int64_t ngroups = (s.n + SYN_ROWS - 1) / SYN_ROWS;
   int grid = (int)(ngroups < 148 * 8 ? (ngroups < 1 ? 1 : ngroups) : 148 * 8);
-  synth_kernel<<<grid, 256, 0, stream>>>(D, s, row0, colX0, colY0, R, seed, Ltruth, b, t, sigE, sigF, sigH);
+  synth_kernel<<<grid, 256, 0, stream>>>(D, s, row0, colX0, colY0, R, seed, Ltruth, b, t, sigE, sigF, sigH, o);
   return cudaGetLastError();
 }
 
