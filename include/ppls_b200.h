@@ -194,6 +194,16 @@ int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, int32_t r, 
                    const double* Cdiag, double sigE, double* seLoad, double* varMatrix, double* SSt_exp,
                    double* SSt_star, double* B_exp, double* W);
 
+/* ---- multi-population ("meta") fit: meta_PPLSi(X, Y, Ipopu, EMsteps, atol, initialGuess, customGuess) ---------- */
+/* EM_W_multi.R:509-589 (meta_EMstep :446-485; meta_Estep / meta_Mstep, loglC.cpp:399-474): one component, loadings
+ * shared by all populations, B_T / sigX / sigY / sigH / sigT per population.  Populations are contiguous row blocks
+ * of pop_rows[j] rows in row order.  guess: one-component start state used for every population.  Outputs: W[p],
+ * C[q], params n_pop x 5 column-major (B_T, sigX, sigY, sigH, sigT), logvalues steps x n_pop ROW-major (the
+ * reference's `log`, rows 2..steps+1 of logvalue; room for EMsteps rows; may be NULL), steps. */
+int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, const int64_t* pop_rows, int32_t EMsteps,
+                  double atol, const ppls_params* guess, double* W, double* C, double* params, double* logvalues,
+                  int32_t* steps);
+
 /* ---- batched multi-start: n_starts start states over one resident dataset ----------------- */
 /* Every start is an independent run of EM_W_multi.R:780-793 (its own break rule and trace); the
  * starts share each pass over the data (floor(8/r) starts per streaming-kernel launch).

@@ -72,6 +72,7 @@ SIGNATURES = {
     "ppls_variances": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, _vp, C.c_int64, _vp, C.c_double, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ppls_data_simulc": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_uint64,
                                    C.POINTER(Params), _vp, _vp, _vp, _vp, _vpp]),
+    "ppls_meta_run": (C.c_int, [_vp, _vp, C.c_int32, _vp, C.c_int32, C.c_double, C.POINTER(Params), _vp, _vp, _vp, _vp, _i32p]),
     "ppls_simult_run_batched": (C.c_int, [_vp, _vp, C.POINTER(Opts), C.c_int32, _vp, _vp, _vp, _i32p, C.POINTER(Timing)]),
     "ppls_simult_run": (C.c_int, [_vp, _vp, C.POINTER(Opts), C.POINTER(Params), C.POINTER(Params), _vp, _i32p,
                                   _vp, _vp, _vp]),

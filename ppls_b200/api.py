@@ -18,7 +18,7 @@ import numpy as np
 from . import _lib as L
 
 __all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "normalise", "default_init",
-           "sequential_init", "default_context", "variances", "simulC"]
+           "sequential_init", "default_context", "variances", "simulC", "meta_PPLSi"]
 
 
 def _f64(a, order="F"):
@@ -533,3 +533,39 @@ def simulC(N, W, C_, P_Yosc, P_Xosc, B_T, sigX, sigY, sigH, sigT, sigTo, sigUo, 
     finally:
         d.close()
     return np.hstack([X, Y])
+
+
+def meta_PPLSi(X, Y, Ipopu, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None,
+               ctx: Optional[Context] = None, data: Optional[Data] = None):
+    """Multi-population one-component fit -- mirror of meta_PPLSi (Package/PPLS/R/EM_W_multi.R:509-589) on the GPU
+    (ppls_meta_run).  Ipopu: population label per row; rows must be grouped by population in the order of the sorted
+    labels (the reference slices contiguous blocks by table(Ipopu), :455-456,:551-554).  critfunc = identity, no
+    constraints.  Returns {'W', 'C', 'params': [{'B_T','sigX','sigY','sigH','sigT'}, ...], 'log': steps x n_pop}."""
+    if isinstance(initialGuess, (tuple, list)):
+        initialGuess = initialGuess[0]
+    lab = np.asarray(Ipopu)
+    levels, counts = np.unique(lab, return_counts=True)
+    if not np.array_equal(lab, np.repeat(levels, counts)):
+        raise ValueError("rows must be sorted by population (contiguous blocks in the order of the sorted labels)")
+    ctx = ctx or (data.ctx if data is not None else default_context())
+    own = data is None
+    if data is None:
+        data = Data.from_host(ctx, X, Y)
+    try:
+        if data.n != lab.shape[0]:
+            raise ValueError("nrow(X) == length(Ipopu) is required")
+        J = len(counts)
+        g = _guess(data.p, data.q, initialGuess, customGuess)
+        cnt = np.ascontiguousarray(counts, dtype=np.int64)
+        W = np.zeros(data.p); Cm = np.zeros(data.q)
+        par = np.zeros((J, 5), order="F")
+        logv = np.zeros((int(EMsteps), J))
+        steps = C.c_int32(0)
+        L.check(L.lib().ppls_meta_run(ctx._h, data._h, J, cnt.ctypes.data, int(EMsteps), float(atol), C.byref(g.struct),
+                                      W.ctypes.data, Cm.ctypes.data, par.ctypes.data, logv.ctypes.data, C.byref(steps)))
+    finally:
+        if own:
+            data.close()
+    k = int(steps.value)
+    params = [dict(B_T=par[j, 0], sigX=par[j, 1], sigY=par[j, 2], sigH=par[j, 3], sigT=par[j, 4]) for j in range(J)]
+    return dict(W=W, C=Cm, params=params, log=logv[:k].copy(), Number_steps=k)

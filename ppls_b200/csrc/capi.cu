@@ -1188,3 +1188,107 @@ extern "C" int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, 
   }
   return PPLS_OK;
 }
+
+// ---- multi-population ("meta") fit: meta_PPLSi (EM_W_multi.R:509-589) --------------------------------------------
+// Populations are contiguous row blocks (pop_rows[j] rows each, in row order -- the reference slices
+// (1+Ni[i]):Ni[i+1], :455-456).  One component; critfunc = identity, no constraints.  Per pass the streaming
+// kernel K1 (R = 1) runs once per population on its row block with that population's coefficients and the
+// shared loadings; em_seq.cu::meta_update_kernel does the per-population scalars and pools the loadings.
+extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, const int64_t* pop_rows, int32_t EMsteps,
+                             double atol, const ppls_params* guess, double* W, double* Cout, double* params,
+                             double* logvalues, int32_t* steps) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!d || !pop_rows || !guess || !W || !Cout || !params || !steps) return fail(PPLS_E_INVALID, "null argument");
+  if (d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
+  if (ctx->world != 1 || d->colshard) return fail(PPLS_E_UNSUPPORTED, "meta fit: one GPU, row-major data");
+  if (d->s.panel) return fail(PPLS_E_UNSUPPORTED, "meta fit: wide-row (panel-major) data is not supported");
+  if (n_pop < 1 || n_pop > 64) return fail(PPLS_E_INVALID, "number of populations outside 1..64");
+  if (EMsteps < 1) return fail(PPLS_E_INVALID, "EMsteps must be a strictly positive integer");
+  rc = check_params(guess, "guess");
+  if (rc) return rc;
+  const DataShape& sh = d->s;
+  const int J = n_pop;
+  int64_t tot = 0;
+  for (int j = 0; j < J; ++j) { if (pop_rows[j] < 1) return fail(PPLS_E_INVALID, "empty population"); tot += pop_rows[j]; }
+  if (tot != sh.n) return fail(PPLS_E_INVALID, "nrow(X) == length(Ipopu) is required");
+  const int64_t veclen = momvec_len(sh.ld, 1);
+  struct PopPlan { DataShape s; StreamPlan plan; const double* D; };
+  std::vector<PopPlan> pops(J);
+  int maxgrid = 1;
+  int64_t row = 0;
+  for (int j = 0; j < J; ++j) {
+    pops[j].s = sh; pops[j].s.n = pop_rows[j];
+    pops[j].D = d->D + (size_t)row * sh.ld;
+    const char* why = "";
+    if (plan_stream(pops[j].s, 1, ctx->sm_count, &pops[j].plan, &why) != cudaSuccess)
+      return fail(PPLS_E_UNSUPPORTED, std::string("meta fit: no streaming plan for this shape: ") + why);
+    if (pops[j].plan.grid > maxgrid) maxgrid = pops[j].plan.grid;
+    row += pop_rows[j];
+  }
+  struct Bufs {
+    double *partials = nullptr, *momvecs = nullptr, *L = nullptr, *trace = nullptr, *ssq = nullptr, *scr = nullptr;
+    FitState* sts = nullptr;
+    ~Bufs() { cudaFree(partials); cudaFree(momvecs); cudaFree(L); cudaFree(trace); cudaFree(ssq); cudaFree(scr); cudaFree(sts); }
+  } B;
+  const int nblocks = ctx->sm_count * 4;
+  CU(cudaMalloc(&B.partials, (size_t)maxgrid * veclen * sizeof(double)));
+  CU(cudaMalloc(&B.momvecs, (size_t)J * veclen * sizeof(double)));
+  CU(cudaMalloc(&B.L, (size_t)sh.ld * sizeof(double)));
+  CU(cudaMalloc(&B.trace, (size_t)(EMsteps + 1) * J * sizeof(double)));
+  CU(cudaMalloc(&B.ssq, (size_t)2 * J * sizeof(double)));
+  CU(cudaMalloc(&B.scr, (size_t)2 * nblocks * sizeof(double)));
+  CU(cudaMalloc(&B.sts, (size_t)J * sizeof(FitState)));
+  CU(cudaMemsetAsync(B.trace, 0, (size_t)(EMsteps + 1) * J * sizeof(double), ctx->stream));
+  // per-population sums of squares (loglC.cpp:421,425: X.array().square().sum() of the population's rows)
+  for (int j = 0; j < J; ++j) CU(launch_ssq(pops[j].D, pops[j].s, B.ssq + 2 * j, B.scr, nblocks, ctx->stream));
+  std::vector<double> ssq((size_t)2 * J);
+  CU(cudaMemcpyAsync(ssq.data(), B.ssq, ssq.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  std::vector<FitState> hst(J);
+  std::vector<double> L0;
+  pack_loadings(sh, 1, guess->W, guess->C, L0);
+  for (int j = 0; j < J; ++j) {
+    FitState& h = hst[j];
+    memset(&h, 0, sizeof(h));
+    h.b[0] = guess->B[0]; h.t[0] = guess->sigT[0]; h.sigE = guess->sigE; h.sigF = guess->sigF; h.sigH = guess->sigH;
+    h.ssqX = ssq[2 * j]; h.ssqY = ssq[2 * j + 1]; h.Ntot = (double)pop_rows[j];
+    h.max_steps = EMsteps; h.atol = atol; h.R = 1; h.orth_type = PPLS_ORTH_SVD;
+  }
+  CU(cudaMemcpyAsync(B.sts, hst.data(), (size_t)J * sizeof(FitState), cudaMemcpyHostToDevice, ctx->stream));
+  CU(cudaMemcpyAsync(B.L, L0.data(), (size_t)sh.ld * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  CU(launch_meta_update(sh, J, B.momvecs, B.L, B.sts, B.trace, 1, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  int passes = 0;
+  bool finished = false;
+  while (!finished) {
+    for (int rep = 0; rep < 8 && passes <= EMsteps; ++rep, ++passes) {
+      for (int j = 0; j < J; ++j) {
+        CU(launch_em_stream(pops[j].plan, pops[j].s, pops[j].D, B.L, B.sts + j, B.partials, nullptr, nullptr, 0, ctx->stream));
+        CU(launch_reduce_partials(B.partials, pops[j].plan.grid, veclen, B.momvecs + (size_t)j * veclen, B.sts + j, ctx->stream));
+      }
+      CU(launch_meta_update(sh, J, B.momvecs, B.L, B.sts, B.trace, 0, ctx->stream));
+    }
+    CU(cudaMemcpyAsync(hst.data(), B.sts, (size_t)J * sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    finished = hst[0].done != 0;
+    if (!finished && passes > EMsteps) return fail(PPLS_E_CUDA, "meta EM loop did not terminate");
+  }
+  if (hst[0].status != PPLS_OK) return fail(hst[0].status, "meta fit: a parameter became non-finite");
+  const int k = hst[0].steps_done;
+  std::vector<double> L(sh.ld), tr((size_t)(k + 1) * J);
+  CU(cudaMemcpyAsync(L.data(), B.L, (size_t)sh.ld * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaMemcpyAsync(tr.data(), B.trace, tr.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  for (int j = 0; j < sh.p; ++j) W[j] = L[j];
+  for (int j = 0; j < sh.q; ++j) Cout[j] = L[sh.p2 + j];
+  for (int j = 0; j < J; ++j) {       // column-major J x 5: B_T, sigX, sigY, sigH, sigT
+    params[j + 0 * J] = hst[j].b[0]; params[j + 1 * J] = hst[j].sigE; params[j + 2 * J] = hst[j].sigF;
+    params[j + 3 * J] = hst[j].sigH; params[j + 4 * J] = hst[j].t[0];
+  }
+  *steps = k;
+  if (logvalues)                        // rows 1..k of the trace = logvalue[2 .. k+1, ] (:586), row-major k x J
+    for (int i = 1; i <= k; ++i)
+      for (int j = 0; j < J; ++j) logvalues[(size_t)(i - 1) * J + j] = tr[(size_t)i * J + j];
+  return PPLS_OK;
+}

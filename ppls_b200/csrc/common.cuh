@@ -129,6 +129,9 @@ cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int
                                    const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,
                                    double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream);
 int update_grid_blocks(int ld);
+// multi-population fit (em_seq.cu): J populations, momvecs [J][ld+3], sts [J]
+cudaError_t launch_meta_update(const DataShape& s, int J, const double* momvecs, double* L, FitState* sts, double* trace,
+                               int prepare, cudaStream_t stream);
 cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream);
 
 // ---- standard errors of the loadings (em_var.cu; variances.PPLS_simult, EM_W_multi.R:830-860) -----------

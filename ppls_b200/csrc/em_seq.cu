@@ -69,6 +69,54 @@ __device__ void seq_coefficients(FitState* st) {
   st->WtW[0] = c1; st->WtW[1] = c2; st->WtW[2] = c3;
 }
 
+// logl_W(Xc, Yc, theta) (EM_W_multi.R:297-323: coefficients :312-320 with g re-squared; loglC.cpp:319-338) from the
+// Gram of (Xw, Yc); st->ssqX / ssqY = ||Xc||^2, ||Yc||^2, N = rows
+__device__ double seq_loglik(const FitState* st, double xx, double xy, double yy, double N, double p, double q) {
+  const double B = st->b[0], sigT = st->t[0], sigX = st->sigE, sigY = st->sigF, sigH = st->sigH;
+  const double sT2 = sigT * sigT, sT4 = sT2 * sT2, sT6 = sT4 * sT2, B2 = B * B;
+  const double sX2 = sigX * sigX, sY2 = sigY * sigY, sH2 = sigH * sigH;
+  double g = sqrt(sT2 * B2 + sH2); g = g * g;
+  const double Kw = sT2 - sT4 * B2 / sY2 + sT4 * B2 * g / (sY2 * (g + sY2));
+  const double Kc = g - sT4 * B2 / sX2 + sT6 * B2 / (sX2 * (sT2 + sX2));
+  const double Kwc = sT2 * B / (sX2 * sY2) - Kc * sT2 * B / (sX2 * sY2 * (Kc + sY2)) -
+                     sT4 * B / (sX2 * sY2 * (sT2 + sX2)) + Kc * sT4 * B / (sX2 * sY2 * (Kc + sY2) * (sT2 + sX2));
+  const double c1 = Kw / (sX2 * (Kw + sX2)), c3 = Kc / (sY2 * (Kc + sY2)), c2 = Kwc;
+  const double Logdiag = log(sX2 + sT2) + (p - 1) * log(sX2) + log(sY2 + Kc) + (q - 1) * log(sY2);
+  double traceL = 1 / sX2 * st->ssqX + 1 / sY2 * st->ssqY;
+  traceL += -c1 * xx - 2 * c2 * xy - c3 * yy;
+  return -0.5 * N * (p + q) * log(2 * 3.14159265358979323846) - 0.5 * N * Logdiag - 0.5 * traceL;
+}
+
+// EMstepC_fast / meta_Estep expectations at theta_k (loglC.cpp:357-375 / :414-434) from the Gram of (Xw, Yc), then the
+// maximisation of the scalars (loglC.cpp:377-386 / meta_Mstep :452-474) -> theta_{k+1} in st.  c1, c2, c3 of theta_k are
+// in st->WtW[0..2], the mu coefficients in st->aT.. (seq_coefficients).
+__device__ void seq_em_scalars(FitState* st, double xx, double xy, double yy, double N, double p, double q) {
+  const double B = st->b[0], sigT = st->t[0], sigX = st->sigE, sigY = st->sigF, sigH = st->sigH;
+  const double sT2 = sigT * sigT, sX2 = sigX * sigX, sY2 = sigY * sigY, sH2 = sigH * sigH;
+  const double c1 = st->WtW[0], c2 = st->WtW[1], c3 = st->WtW[2];
+  const double aT = st->aT[0], bT = st->bT[0], aU = st->aU[0], bU = st->bU[0];
+  const double varU = sT2 * B * B + sH2;
+  const double mTT = aT * aT * xx + 2.0 * aT * bT * xy + bT * bT * yy;
+  const double mUU = aU * aU * xx + 2.0 * aU * bU * xy + bU * bU * yy;
+  const double mUT = aU * aT * xx + (aU * bT + bU * aT) * xy + bU * bT * yy;
+  const double Ctt = sT2 - sT2 * sT2 * (-c1 - 2 * B * c2 - B * B * (c3 - 1 / sY2) + 1 / sX2) + mTT / N;
+  const double Cuu = varU - (-(c1 - 1 / sX2) * sT2 * sT2 * B * B - 2 * sT2 * B * varU * c2 - varU * varU * (c3 - 1 / sY2)) + mUU / N;
+  const double Cut = sT2 * B - (-sT2 * sT2 * B * (c1 - 1 / sX2) - sT2 * sT2 * B * B * c2 - sT2 * varU * c2 -
+                                varU * sT2 * B * (c3 - 1 / sY2)) + mUT / N;
+  const double Ceetmp = c1 * c1 * sX2 * sX2 * xx + st->ssqX + c2 * c2 * sX2 * sX2 * yy - 2 * c1 * sX2 * xx +
+                        2 * c1 * c2 * sX2 * sX2 * xy - 2 * c2 * sX2 * xy;
+  const double Cee = sX2 - (-sX2 * sX2 * c1 + p * sX2) / p + Ceetmp / N / p;
+  const double Cfftmp = c3 * c3 * sY2 * sY2 * yy + st->ssqY + c2 * c2 * sY2 * sY2 * xx - 2 * c3 * sY2 * yy +
+                        2 * c3 * c2 * sY2 * sY2 * xy - 2 * c2 * sY2 * xy;
+  const double Cff = sY2 - (-sY2 * sY2 * c3 + q * sY2) / q + Cfftmp / N / q;
+  const double hX = -c2 * sH2, hY = -(c3 - 1 / sY2) * sH2;
+  const double mHH = hX * hX * xx + 2.0 * hX * hY * xy + hY * hY * yy;
+  const double Chh = sH2 - (-sH2 * sH2 * (c3 - 1 / sY2)) + mHH / N;
+  st->Ctt[0] = Ctt; st->Cuu[0] = Cuu; st->Cut[0] = Cut; st->Cee = Cee; st->Cff = Cff; st->Chh[0] = Chh;
+  st->b[0] = Cut / Ctt;
+  st->sigE = sqrt(Cee); st->sigF = sqrt(Cff); st->sigH = sqrt(Chh); st->t[0] = sqrt(Ctt);
+}
+
 __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArgs a) {
   __shared__ double scratch[SEQ_THREADS / 32];
   __shared__ int s_done;
@@ -93,21 +141,8 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
     const double B = st->b[0], sigT = st->t[0], sigX = st->sigE, sigY = st->sigF, sigH = st->sigH;
     const double sT2 = sigT * sigT, sT4 = sT2 * sT2, sT6 = sT4 * sT2, B2 = B * B;
     const double sX2 = sigX * sigX, sY2 = sigY * sigY, sH2 = sigH * sigH;
-    // ---- logvalue[k] = logl_W(Xc, Yc, theta_k)  (:150 / :171; coefficients :312-320 with g re-squared) ----
-    {
-      double g = sqrt(sT2 * B2 + sH2); g = g * g;
-      const double Kw = sT2 - sT4 * B2 / sY2 + sT4 * B2 * g / (sY2 * (g + sY2));
-      const double Kc = g - sT4 * B2 / sX2 + sT6 * B2 / (sX2 * (sT2 + sX2));
-      const double Kwc = sT2 * B / (sX2 * sY2) - Kc * sT2 * B / (sX2 * sY2 * (Kc + sY2)) -
-                         sT4 * B / (sX2 * sY2 * (sT2 + sX2)) + Kc * sT4 * B / (sX2 * sY2 * (Kc + sY2) * (sT2 + sX2));
-      const double c1 = Kw / (sX2 * (Kw + sX2)), c3 = Kc / (sY2 * (Kc + sY2)), c2 = Kwc;
-      const double Logdiag = log(sX2 + sT2) + (p - 1) * log(sX2) + log(sY2 + Kc) + (q - 1) * log(sY2);
-      double traceL = 1 / sX2 * st->ssqX + 1 / sY2 * st->ssqY;
-      traceL += -c1 * xx - 2 * c2 * xy - c3 * yy;
-      const double ll = -0.5 * N * (p + q) * log(2 * 3.14159265358979323846) - 0.5 * N * Logdiag - 0.5 * traceL;
-      st->loglik_last = ll;
-      a.trace[k] = ll;
-    }
+    st->loglik_last = seq_loglik(st, xx, xy, yy, N, p, q);      // logvalue[k] = logl_W(Xc, Yc, theta_k), :150 / :171
+    a.trace[k] = st->loglik_last;
     // ---- end of the component?  (:172 break rule, EMsteps exhausted, :153-155 vanishing noise variance) ----
     bool done = false;
     if (k >= 1 && (a.trace[k] - a.trace[k - 1]) < st->atol) done = true;
@@ -119,30 +154,7 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
     if (done) { st->done = 1; st->steps_done = k; }
     s_done = done ? 1 : 0;
     if (!done) {
-      // ---- EMstepC_fast expectations at theta_k (loglC.cpp:357-375) from the Gram of (Xw, Yc) -----------
-      const double c1 = st->WtW[0], c2 = st->WtW[1], c3 = st->WtW[2];
-      const double aT = st->aT[0], bT = st->bT[0], aU = st->aU[0], bU = st->bU[0];
-      const double varU = sT2 * B * B + sH2;
-      const double mTT = aT * aT * xx + 2.0 * aT * bT * xy + bT * bT * yy;
-      const double mUU = aU * aU * xx + 2.0 * aU * bU * xy + bU * bU * yy;
-      const double mUT = aU * aT * xx + (aU * bT + bU * aT) * xy + bU * bT * yy;
-      const double Ctt = sT2 - sT2 * sT2 * (-c1 - 2 * B * c2 - B * B * (c3 - 1 / sY2) + 1 / sX2) + mTT / N;
-      const double Cuu = varU - (-(c1 - 1 / sX2) * sT2 * sT2 * B * B - 2 * sT2 * B * varU * c2 - varU * varU * (c3 - 1 / sY2)) + mUU / N;
-      const double Cut = sT2 * B - (-sT2 * sT2 * B * (c1 - 1 / sX2) - sT2 * sT2 * B * B * c2 - sT2 * varU * c2 -
-                                    varU * sT2 * B * (c3 - 1 / sY2)) + mUT / N;
-      const double Ceetmp = c1 * c1 * sX2 * sX2 * xx + st->ssqX + c2 * c2 * sX2 * sX2 * yy - 2 * c1 * sX2 * xx +
-                            2 * c1 * c2 * sX2 * sX2 * xy - 2 * c2 * sX2 * xy;
-      const double Cee = sX2 - (-sX2 * sX2 * c1 + p * sX2) / p + Ceetmp / N / p;
-      const double Cfftmp = c3 * c3 * sY2 * sY2 * yy + st->ssqY + c2 * c2 * sY2 * sY2 * xx - 2 * c3 * sY2 * yy +
-                            2 * c3 * c2 * sY2 * sY2 * xy - 2 * c2 * sY2 * xy;
-      const double Cff = sY2 - (-sY2 * sY2 * c3 + q * sY2) / q + Cfftmp / N / q;
-      const double hX = -c2 * sH2, hY = -(c3 - 1 / sY2) * sH2;
-      const double mHH = hX * hX * xx + 2.0 * hX * hY * xy + hY * hY * yy;
-      const double Chh = sH2 - (-sH2 * sH2 * (c3 - 1 / sY2)) + mHH / N;
-      st->Ctt[0] = Ctt; st->Cuu[0] = Cuu; st->Cut[0] = Cut; st->Cee = Cee; st->Cff = Cff; st->Chh[0] = Chh;
-      // ---- maximisation (loglC.cpp:377-386) -> theta_{k+1} -----------------------------------------------
-      st->b[0] = Cut / Ctt;
-      st->sigE = sqrt(Cee); st->sigF = sqrt(Cff); st->sigH = sqrt(Chh); st->t[0] = sqrt(Ctt);
+      seq_em_scalars(st, xx, xy, yy, N, p, q);
       st->pass = k + 1;
       const bool ok = isfinite(st->b[0]) && isfinite(st->sigE) && isfinite(st->sigF) && isfinite(st->sigH) && isfinite(st->t[0]);
       if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = k; s_done = 1; }
@@ -173,6 +185,109 @@ cudaError_t launch_seq_update(const DataShape& s, const double* momvec, double* 
   a.momvec = momvec; a.L = L; a.st = st; a.trace = trace; a.prev = prev; a.nprev = nprev; a.prepare = prepare;
   a.p = s.p; a.q = s.q; a.p2 = s.p2; a.q2 = s.q2; a.ld = s.ld;
   seq_update_kernel<<<1, SEQ_THREADS, 0, stream>>>(a);
+  return cudaGetLastError();
+}
+
+// ---- multi-population ("meta") fit: meta_PPLSi / meta_EMstep (EM_W_multi.R:509-589 / :446-485), -----------------
+// meta_Estep / meta_Mstep (loglC.cpp:399-474).  One component, loadings shared by all populations, scalars per
+// population.  Pass k: the streaming kernel ran once per population (its own coefficients, the shared loadings)
+// and left momvec_j = [X_j'mu_T ; Y_j'mu_U | Gram]; this kernel then does, for every population j, the scalar part
+// of EMstepC_fast on (Gram_j, ssq_j, N_j), and pools the loadings:
+//   W = orth(sum_j s_j Cxt_j), C = orth(sum_j s_j Cyu_j), Cxt_j = X_j'mu_T / N_j, s_j = sign(Cxt_1'Cxt_j)   (:481-482)
+constexpr int META_MAXJ = 64;
+struct MetaArgs {
+  const double* momvecs;  // [J][ld + 3]
+  double* L;              // [ld]
+  FitState* sts;          // [J]; sts[0] carries the control words (pass, steps_done, status, max_steps, atol)
+  double* trace;          // [max_steps + 1][J]: trace[k][j] = logl_W(X_j, Y_j, theta_k)
+  int32_t J, p, q, p2, q2, ld, prepare;
+};
+
+__global__ void __launch_bounds__(SEQ_THREADS, 1) meta_update_kernel(const MetaArgs a) {
+  __shared__ double scratch[SEQ_THREADS / 32];
+  __shared__ double sgn[META_MAXJ];
+  __shared__ int s_done, s_k;
+  const int J = a.J, veclen = a.ld + 3;
+  if (a.prepare) {
+    if ((int)threadIdx.x < J) {
+      FitState* st = a.sts + threadIdx.x;
+      seq_coefficients(st);
+      st->pass = 0; st->done = 0; st->steps_done = 0; st->status = PPLS_OK;
+    }
+    return;
+  }
+  if (threadIdx.x == 0) { s_done = a.sts[0].done; s_k = a.sts[0].pass; }
+  __syncthreads();
+  if (s_done) return;
+  const int k = s_k;
+  const double p = (double)a.p, q = (double)a.q;
+  if ((int)threadIdx.x < J) {                                                                  // :574-576
+    FitState* st = a.sts + threadIdx.x;
+    const double* g = a.momvecs + (size_t)threadIdx.x * veclen + a.ld;
+    st->loglik_last = seq_loglik(st, g[0], g[1], g[2], st->Ntot, p, q);
+    a.trace[(size_t)k * J + threadIdx.x] = st->loglik_last;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    bool done = false, finite = true;
+    double cur = 0.0, prev = 0.0;
+    for (int j = 0; j < J; ++j) { cur += a.trace[(size_t)k * J + j]; finite = finite && isfinite(a.trace[(size_t)k * J + j]); }
+    if (k >= 1) {
+      for (int j = 0; j < J; ++j) prev += a.trace[(size_t)(k - 1) * J + j];
+      if (k == 1) prev = prev * J;        // logvalue[1,] = rep(full-data log-likelihood, nlevels)  (:548)
+      if (cur - prev < a.sts[0].atol) done = true;                                              // :578
+    }
+    if (k >= a.sts[0].max_steps) done = true;
+    if (!finite) { a.sts[0].status = PPLS_E_NONFINITE; done = true; }
+    if (done) { for (int j = 0; j < J; ++j) a.sts[j].done = 1; a.sts[0].steps_done = k; }
+    s_done = done ? 1 : 0;
+  }
+  __syncthreads();
+  if (s_done) return;
+  if ((int)threadIdx.x < J) {                                        // meta_Estep + meta_Mstep scalars, next coefficients
+    FitState* st = a.sts + threadIdx.x;
+    const double* g = a.momvecs + (size_t)threadIdx.x * veclen + a.ld;
+    seq_em_scalars(st, g[0], g[1], g[2], st->Ntot, p, q);
+    const bool ok = isfinite(st->b[0]) && isfinite(st->sigE) && isfinite(st->sigF) && isfinite(st->sigH) && isfinite(st->t[0]);
+    if (!ok) a.sts[0].status = PPLS_E_NONFINITE;
+    seq_coefficients(st);
+    st->pass = k + 1;
+  }
+  // signs from the X side
+  const double N0 = a.sts[0].Ntot;
+  for (int j = 0; j < J; ++j) {
+    const double Nj = a.sts[j].Ntot;
+    const double* g0 = a.momvecs;
+    const double* gj = a.momvecs + (size_t)j * veclen;
+    double d = 0.0;
+    for (int e = threadIdx.x; e < a.p2; e += SEQ_THREADS) d += (g0[e] / N0) * (gj[e] / Nj);
+    d = seq_block_sum(d, scratch);
+    if (threadIdx.x == 0) sgn[j] = (d > 0.0) ? 1.0 : ((d < 0.0) ? -1.0 : 0.0);
+  }
+  __syncthreads();
+  for (int part = 0; part < 2; ++part) {
+    const int lo = part ? a.p2 : 0, hi = part ? a.ld : a.p2;
+    double ss = 0.0;
+    for (int e = lo + threadIdx.x; e < hi; e += SEQ_THREADS) {
+      double v = 0.0;
+      for (int j = 0; j < J; ++j) v += sgn[j] * (a.momvecs[(size_t)j * veclen + e] / a.sts[j].Ntot);
+      a.L[e] = v; ss += v * v;
+    }
+    ss = seq_block_sum(ss, scratch);
+    const double nrm = sqrt(ss);
+    for (int e = lo + threadIdx.x; e < hi; e += SEQ_THREADS) a.L[e] = a.L[e] / nrm;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && a.sts[0].status != PPLS_OK) { for (int j = 0; j < J; ++j) a.sts[j].done = 1; a.sts[0].steps_done = k; }
+}
+
+cudaError_t launch_meta_update(const DataShape& s, int J, const double* momvecs, double* L, FitState* sts, double* trace,
+                               int prepare, cudaStream_t stream) {
+  if (J < 1 || J > META_MAXJ) return cudaErrorInvalidValue;
+  MetaArgs a;
+  a.momvecs = momvecs; a.L = L; a.sts = sts; a.trace = trace; a.J = J; a.prepare = prepare;
+  a.p = s.p; a.q = s.q; a.p2 = s.p2; a.q2 = s.q2; a.ld = s.ld;
+  meta_update_kernel<<<1, SEQ_THREADS, 0, stream>>>(a);
   return cudaGetLastError();
 }
 
