@@ -305,7 +305,7 @@ def run_c5(args):
     out = {"metric": METRIC, "value": K / (loop_ms * 1e-3), "unit": "batch EM iterations/s (64 starts each)", "n_gpus": 1,
            "steps": K, "warmup": W, "ms_per_step": loop_ms / K, "higher_is_better": True, "scaling": "strong",
            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-           "config": {"workload": f"c5: {C5_STARTS} starts x N={N} p={p} q={q} r={r}, starts packed 4 per data pass",
+           "config": {"workload": f"c5: {C5_STARTS} starts x N={N} p={p} q={q} r={r}, all {C5_STARTS * r} components per data pass (two FP64 GEMMs, em_batch.cu)",
                       "wall_ms_per_step_incl_setup": wall_ms / K}, "clocks": clocks, "gpu_launches": int(tm["kernel_launches"]),
            "roofline": {"bound": "fp64 (vector FMA; SURVEY.md 8d config 5)", "achieved": flops / (loop_ms * 1e-3) / 1e12,
                         "peak": 37.0, "unit": "TFLOP/s", "frac": flops / (loop_ms * 1e-3) / 1e12 / 37.0, "traffic": None,

@@ -19,6 +19,7 @@ UNITS = {
     "em_update.cu": ["-fmad=false"],
     "em_seq.cu": ["-fmad=false"],
     "em_var.cu": [],
+    "em_batch.cu": [],
     "data.cu": ["-fmad=false"],
     "capi.cu": [],
 }

@@ -910,18 +910,31 @@ extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const 
   if (opts->max_steps < 0) return fail(PPLS_E_INVALID, "EMsteps must be >= 0");
   for (int s = 0; s < S; ++s) { rc = check_params(&inits[s], "init"); if (rc) return rc; rc = check_params(&ests[s], "est"); if (rc) return rc; }
   const DataShape& sh = d->s;
-  const int g = (MAXR / R) < S ? (MAXR / R) : S, RP = g * R, groups = (S + g - 1) / g;
+  // Two data paths: many components in flight (S*r >= 64) -> two FP64 GEMMs per pass over groups of up to 128
+  // components (em_batch.cu); otherwise packs of <= 8 components through the streaming kernel K1.
+  const char* eg = getenv("PPLS_BATCH_GEMM");
+  const bool gemm = !sh.panel && ((eg && *eg) ? atoi(eg) != 0 : (int64_t)S * R >= 64);
+  int g, RP, groups;
+  if (gemm) {
+    g = (128 / R) < S ? (128 / R) : S;                   // starts per group
+    RP = ((g * R + 127) / 128) * 128;                    // the GEMM tile is 128 components wide (pad columns are zero)
+  } else {
+    g = (MAXR / R) < S ? (MAXR / R) : S; RP = g * R;
+  }
+  groups = (S + g - 1) / g;
   StreamPlan plan{};
+  BGemmPlan bplan{};
   const char* why = "";
-  if (plan_stream(sh, RP, ctx->sm_count, &plan, &why) != cudaSuccess)
+  if (gemm) plan_bgemm(sh, RP, R, g, ctx->sm_count, &bplan);
+  else if (plan_stream(sh, RP, ctx->sm_count, &plan, &why) != cudaSuccess)
     return fail(PPLS_E_UNSUPPORTED, std::string("batched run: streaming-kernel plan: ") + why);
   const size_t veclen = (size_t)momvec_len(sh.ld, R), veclenP = (size_t)momvec_len(sh.ld, RP);
   const int tracelen = opts->max_steps + 1;
   struct Bufs {
-    double *Lp = nullptr, *Ls = nullptr, *Lsc = nullptr, *mp = nullptr, *ms = nullptr, *tr = nullptr, *part = nullptr;
+    double *Lp = nullptr, *Ls = nullptr, *Lsc = nullptr, *mp = nullptr, *ms = nullptr, *tr = nullptr, *part = nullptr, *coef = nullptr;
     FitState *pst = nullptr, *st = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
-    ~Bufs() { cudaFree(Lp); cudaFree(Ls); cudaFree(Lsc); cudaFree(mp); cudaFree(ms); cudaFree(tr); cudaFree(part); cudaFree(pst); cudaFree(st);
+    ~Bufs() { cudaFree(Lp); cudaFree(Ls); cudaFree(Lsc); cudaFree(mp); cudaFree(ms); cudaFree(tr); cudaFree(part); cudaFree(coef); cudaFree(pst); cudaFree(st);
               if (e0) cudaEventDestroy(e0); if (e1) cudaEventDestroy(e1); }
   } B;
   CU(cudaMalloc(&B.Lp, (size_t)groups * sh.ld * RP * sizeof(double)));
@@ -930,7 +943,12 @@ extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const 
   CU(cudaMalloc(&B.mp, (size_t)groups * veclenP * sizeof(double)));
   CU(cudaMalloc(&B.ms, (size_t)S * veclen * sizeof(double)));
   CU(cudaMalloc(&B.tr, (size_t)S * tracelen * sizeof(double)));
-  CU(cudaMalloc(&B.part, (size_t)plan.grid * veclenP * sizeof(double)));
+  if (gemm) {
+    CU(cudaMalloc(&B.part, bgemm_workspace_doubles(sh, bplan) * sizeof(double)));
+    CU(cudaMalloc(&B.coef, (size_t)groups * 4 * RP * sizeof(double)));
+    CU(cudaMemsetAsync(B.coef, 0, (size_t)groups * 4 * RP * sizeof(double), ctx->stream));
+    CU(cudaMemsetAsync(B.mp, 0, (size_t)groups * veclenP * sizeof(double), ctx->stream));
+  } else CU(cudaMalloc(&B.part, (size_t)plan.grid * veclenP * sizeof(double)));
   CU(cudaMalloc(&B.pst, (size_t)groups * sizeof(FitState)));
   CU(cudaMalloc(&B.st, (size_t)S * sizeof(FitState)));
   CU(cudaEventCreate(&B.e0)); CU(cudaEventCreate(&B.e1));
@@ -952,20 +970,27 @@ extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const 
   CU(cudaMemsetAsync(B.Lp, 0, (size_t)groups * sh.ld * RP * sizeof(double), st));
   CU(cudaMemsetAsync(B.pst, 0, (size_t)groups * sizeof(FitState), st));
   CU(cudaMemsetAsync(B.tr, 0, (size_t)S * tracelen * sizeof(double), st));
-  CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 1, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st));
+  CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 1, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st, B.coef));
   CU(cudaStreamSynchronize(st));            // host vectors must outlive the copies
   const int check_every = opts->check_every > 0 ? opts->check_every : 16;
   int64_t launches = 1, passes = 0;
   CU(cudaEventRecord(B.e0, st));
   for (int pass = 0; pass <= opts->max_steps; ++pass) {
     for (int gr = 0; gr < groups; ++gr) {
+      if (gemm) {
+        BGemmPlan bp = bplan;
+        bp.nstart = (S - gr * g < g) ? S - gr * g : g;
+        CU(launch_bgemm_pass(bp, sh, d->D, B.Lp + (size_t)gr * sh.ld * RP, B.coef + (size_t)gr * 4 * RP, B.part,
+                             B.mp + (size_t)gr * veclenP, st));
+        continue;
+      }
       CU(launch_em_stream(plan, sh, d->D, B.Lp + (size_t)gr * sh.ld * RP, B.pst + gr, B.part, nullptr, nullptr, 0, st));
       CU(launch_reduce_partials(B.part, plan.grid, (int64_t)veclenP, B.mp + (size_t)gr * veclenP, B.pst + gr, st));
     }
     rc = allreduce_sum(ctx, B.mp, (size_t)groups * veclenP);
     if (rc) return rc;
-    CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 0, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st));
-    launches += 2 * groups + 2; passes += 1;
+    CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 0, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st, B.coef));
+    launches += (gemm ? 4 : 2) * groups + 2; passes += 1;
     if ((pass + 1) % check_every == 0 && pass < opts->max_steps) {
       CU(cudaMemcpyAsync(hst.data(), B.st, (size_t)S * sizeof(FitState), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));

@@ -127,8 +127,21 @@ cudaError_t launch_em_update(const DataShape& s, int R, const double* momvec, do
 // batched multi-start: S starts, g per pack of RP = g*R components (em_update.cu)
 cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int S, int tracelen, int prepare,
                                    const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,
-                                   double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream);
+                                   double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream,
+                                   double* coef = nullptr);
 int update_grid_blocks(int ld);
+// batched multi-start as two FP64 GEMMs per pass (em_batch.cu)
+struct BGemmPlan {
+  int RP, R, nstart;            // components of the group (multiple of 128), per start, starts in the group
+  int ncb, nbx, nby, ntiles, rowtiles;
+  int nsplit; int64_t rows_per_split;
+  int nchunk; int64_t rows_per_chunk;
+};
+void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGemmPlan* p);
+size_t bgemm_workspace_doubles(const DataShape& s, const BGemmPlan& p);
+// one data pass for a group: Lpack [ld][RP], coef [4][RP] -> momvec_pack [ld*RP + 3*RP*RP] (block diagonal of the Grams)
+cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const double* D, const double* Lpack, const double* coef,
+                              double* ws, double* momvec_pack, cudaStream_t stream);
 // multi-population fit (em_seq.cu): J populations, momvecs [J][ld+3], sts [J]
 cudaError_t launch_meta_update(const DataShape& s, int J, const double* momvecs, double* L, FitState* sts, double* trace,
                                int prepare, cudaStream_t stream);

@@ -1,0 +1,344 @@
+// Batched multi-start EM (C5) as two FP64 GEMMs per pass -- SURVEY 8e "batched multi-start", kernel K5.
+// With S starts of r components the data-dependent part of one EM pass is, for ALL starts at once (RP = S*r
+// "components", padded to the 128-wide tile):
+//   P  = [X W | Y C]                      (n x 2RP)   bproj_kernel    GEMM "NN": rows x K(columns) x comps
+//   mu = [aT.Xw + bT.Yc | aU.Xw + bU.Yc]  (n x 2RP)   bmu_kernel      elementwise + the r x r Gram blocks per start
+//   G  = [X' mu_T ; Y' mu_U]              (ld x RP)   baccum_kernel   GEMM "TN": columns x K(rows) x comps
+// 4 (p+q) r S flop per row against 8 (p+q) bytes: S r / 2 flop per byte -- FP64-pipe bound for S r >= 32, so the
+// streaming kernel K1 (built for the HBM-bound r <= 8 case, 4 rows per tile at r = 8) is the wrong tool here.
+// Register-tiled DFMA kernels (no FP64 path on tcgen05; DMMA has the DFMA rate): 128 x 128 tile per CTA, 256
+// threads x (8 x 8) accumulators, cp.async double-buffered operand stages, column pairs interleaved over the
+// threads (pair tx + 16 m) so that every LDS.128 quarter-warp reads 128 contiguous bytes.
+#include "common.cuh"
+#include <math.h>
+
+namespace ppls {
+
+constexpr int BT = 128;         // tile edge
+constexpr int BK = 16;          // K per stage
+constexpr int BTHREADS = 256;
+constexpr int BAP = BK + 2;     // pitch of the row-major A tile of bproj (16-byte aligned rows, conflict-free broadcasts)
+
+__device__ __forceinline__ void bcp16(void* smem_dst, const void* gsrc, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void bcommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bwait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// ---- P[row][side*RP + c] = sum_j D[row][c0 + j] * L[c0 + j][c]   (side 0: X columns, side 1: Y columns) -------
+struct ProjArgs {
+  const double* D; const double* L; double* P;
+  int64_t n;
+  int ld, p2, q2, RP;            // RP: multiple of BT
+};
+__global__ void __launch_bounds__(BTHREADS, 1) bproj_kernel(const ProjArgs a) {
+  extern __shared__ __align__(16) double sm[];    // [2 stages][ A: BT x BAP | B: BK x BT ]
+  const int side = blockIdx.z, cb = blockIdx.y;
+  const int64_t row0 = (int64_t)blockIdx.x * BT;
+  const int c0 = side ? a.p2 : 0, K = side ? a.q2 : a.p2;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int nst = (K + BK - 1) / BK;
+  constexpr int STAGE = BT * BAP + BK * BT;
+
+  auto issue = [&](int s, int buf) {
+    double* As = sm + (size_t)buf * STAGE;
+    double* Bs = As + BT * BAP;
+    const int k0 = s * BK;
+#pragma unroll
+    for (int c = 0; c < (BT * BK / 2) / BTHREADS; ++c) {          // A: 128 rows x 8 chunks
+      const int chunk = tid + c * BTHREADS, r = chunk >> 3, kc = (chunk & 7) * 2;
+      const bool ok = (row0 + r < a.n) && (k0 + kc < K);
+      bcp16(As + r * BAP + kc, ok ? a.D + (size_t)(row0 + r) * a.ld + c0 + k0 + kc : a.D, ok ? 16 : 0);
+    }
+#pragma unroll
+    for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {          // B: 16 k x 64 pairs, pair t*4+m -> slot t + 16 m
+      const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63;
+      const int slot = (pr >> 2) + 16 * (pr & 3);
+      const bool ok = k0 + kk < K;
+      bcp16(Bs + kk * BT + slot * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * BT + pr * 2 : a.L, ok ? 16 : 0);
+    }
+    bcommit();
+  };
+
+  double acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+  issue(0, 0);
+  for (int s = 0; s < nst; ++s) {
+    if (s + 1 < nst) { issue(s + 1, (s + 1) & 1); bwait<1>(); } else bwait<0>();
+    __syncthreads();
+    const double* As = sm + (size_t)(s & 1) * STAGE;
+    const double* Bs = As + BT * BAP;
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      double af[8], bf[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) af[i] = As[(ty * 8 + i) * BAP + kk];
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const double2 vb = *reinterpret_cast<const double2*>(Bs + kk * BT + tx * 2 + 32 * m);
+        bf[2 * m] = vb.x; bf[2 * m + 1] = vb.y;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fma(af[i], bf[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  // thread (ty, tx): rows ty*8 + i, logical comps cb*128 + tx*8 + 2m + e (slot tx + 16 m holds pair tx*4 + m)
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int64_t row = row0 + ty * 8 + i;
+    if (row >= a.n) continue;
+    double* out = a.P + (size_t)row * 2 * a.RP + (size_t)side * a.RP + cb * BT + tx * 8;
+#pragma unroll
+    for (int m = 0; m < 4; ++m) *reinterpret_cast<double2*>(out + 2 * m) = make_double2(acc[i][2 * m], acc[i][2 * m + 1]);
+  }
+}
+
+// ---- mu and the per-start Gram blocks ------------------------------------------------------------------------
+// P -> mu in place: P[row][c] = aT[c] Xw + bT[c] Yc, P[row][RP + c] = aU[c] Xw + bU[c] Yc.
+// Gram: gpart[chunk][start][3][R*R] = sum over the chunk's rows of Xw_k Xw_l, Xw_k Yc_l, Yc_k Yc_l.
+// Lane = one component (coalesced 8-byte accesses along a row of P); a warp covers 32/R whole starts, lane (s, k)
+// keeps row k of its start's three blocks and gets the other components of the start by shuffles; the block's
+// 8 warps take every 8th row of the chunk.
+struct MuArgs {
+  double* P; const double* coef /*[4][RP]: aT bT aU bU*/; double* gpart;
+  int64_t n, rows_per_chunk;
+  int RP, R, nstart;             // nstart: starts in this group
+};
+template <int R>
+__global__ void __launch_bounds__(256) bmu_kernel(const MuArgs a) {
+  constexpr int SW = 32 / R;                      // starts per warp
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int sl = lane / R, k = lane - sl * R;
+  const int s = blockIdx.x * SW + sl;
+  const bool active = (sl < SW) && (s < a.nstart);
+  const int c = active ? s * R + k : 0;
+  const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_chunk;
+  const int64_t r1 = (r0 + a.rows_per_chunk < a.n) ? r0 + a.rows_per_chunk : a.n;
+  const double aT = a.coef[c], bT = a.coef[a.RP + c], aU = a.coef[2 * a.RP + c], bU = a.coef[3 * a.RP + c];
+  double gxx[R], gxy[R], gyy[R];
+#pragma unroll
+  for (int l = 0; l < R; ++l) { gxx[l] = 0.0; gxy[l] = 0.0; gyy[l] = 0.0; }
+  const int base = sl * R;                        // first lane of this start
+  for (int64_t i = r0 + warp; i < r1; i += 8) {
+    double* px = a.P + (size_t)i * 2 * a.RP + c;
+    double* py = px + a.RP;
+    const double xw = active ? *px : 0.0, yc = active ? *py : 0.0;
+#pragma unroll
+    for (int l = 0; l < R; ++l) {
+      const double xl = __shfl_sync(0xffffffffu, xw, (base + l) & 31), yl = __shfl_sync(0xffffffffu, yc, (base + l) & 31);
+      gxx[l] = fma(xw, xl, gxx[l]); gxy[l] = fma(xw, yl, gxy[l]); gyy[l] = fma(yc, yl, gyy[l]);
+    }
+    if (active) { *px = aT * xw + bT * yc; *py = aU * xw + bU * yc; }
+  }
+  __shared__ double fold[8][32][3 * R];
+#pragma unroll
+  for (int l = 0; l < R; ++l) { fold[warp][lane][l] = gxx[l]; fold[warp][lane][R + l] = gxy[l]; fold[warp][lane][2 * R + l] = gyy[l]; }
+  __syncthreads();
+  if (warp == 0 && active) {                       // warps added in order: deterministic
+    double* out = a.gpart + ((size_t)blockIdx.y * a.nstart + s) * 3 * R * R;
+#pragma unroll
+    for (int v = 0; v < 3 * R; ++v) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += fold[w][lane][v];
+      out[(v / R) * R * R + k * R + (v % R)] = t;
+    }
+  }
+}
+
+// ---- partial[split][tile] = D[:, col block]' mu_side[:, comp block] over the split's rows ----------------------
+struct AccArgs {
+  const double* D; const double* MU; double* partial;
+  int64_t n, rows_per_split;
+  int ld, p2, q2, RP, nbx, nby, ncb;     // column blocks of X / Y (BT wide), comp blocks
+};
+__global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
+  extern __shared__ __align__(16) double sm[];    // [2 stages][2 operands][BK][BT]
+  const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block (X blocks, then Y blocks)
+  const int side = db >= a.nbx;
+  const int col0 = side ? a.p2 + (db - a.nbx) * BT : db * BT;              // first data column of the block
+  const int cend = side ? a.ld : a.p2;                                    // columns of the side end here
+  const double* Bbase = a.MU + (size_t)side * a.RP + (size_t)cb * BT;
+  const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_split;
+  const int64_t r1 = (r0 + a.rows_per_split < a.n) ? r0 + a.rows_per_split : a.n;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int nst = (r1 > r0) ? (int)((r1 - r0 + BK - 1) / BK) : 0;
+
+  auto issue = [&](int s, int buf) {
+    double* As = sm + (size_t)(buf * 2 + 0) * BK * BT;
+    double* Bs = sm + (size_t)(buf * 2 + 1) * BK * BT;
+#pragma unroll
+    for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {
+      const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63, slot = (pr >> 2) + 16 * (pr & 3);
+      const int64_t grow = r0 + (int64_t)s * BK + kk;
+      const bool rok = grow < r1;
+      const bool okA = rok && (col0 + pr * 2 < cend);
+      bcp16(As + kk * BT + slot * 2, okA ? a.D + (size_t)grow * a.ld + col0 + pr * 2 : a.D, okA ? 16 : 0);
+      bcp16(Bs + kk * BT + slot * 2, rok ? Bbase + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
+    }
+    bcommit();
+  };
+  double acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+  if (nst > 0) issue(0, 0);
+  for (int s = 0; s < nst; ++s) {
+    if (s + 1 < nst) { issue(s + 1, (s + 1) & 1); bwait<1>(); } else bwait<0>();
+    __syncthreads();
+    const double* As = sm + (size_t)((s & 1) * 2 + 0) * BK * BT;
+    const double* Bs = As + BK * BT;
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      double af[8], bf[8];
+#pragma unroll
+      for (int m = 0; m < 4; ++m) {
+        const double2 va = *reinterpret_cast<const double2*>(As + kk * BT + ty * 2 + 32 * m);
+        const double2 vb = *reinterpret_cast<const double2*>(Bs + kk * BT + tx * 2 + 32 * m);
+        af[2 * m] = va.x; af[2 * m + 1] = va.y; bf[2 * m] = vb.x; bf[2 * m + 1] = vb.y;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fma(af[i], bf[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  // thread (ty, tx): data columns ty*8 + 2m + e of the block, comps tx*8 + 2m' + e'
+  double* out = a.partial + ((size_t)blockIdx.y * gridDim.x + tile) * BT * BT;
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int m = 0; m < 4; ++m)
+      *reinterpret_cast<double2*>(out + (ty * 8 + i) * BT + tx * 8 + 2 * m) = make_double2(acc[i][2 * m], acc[i][2 * m + 1]);
+}
+
+// momvec_pack = [G (ld x RP) | Gxx (RP x RP) | Gxy | Gyy]: G summed over the row splits in fixed order, the Gram
+// blocks of every start summed over the row chunks and written on the block diagonal (nothing else is read).
+struct FinArgs {
+  const double* partial; const double* gpart; double* momvec;
+  int nsplit, ntiles, ncb, nbx, ld, p2, RP, R, nstart, nchunk;
+};
+__global__ void __launch_bounds__(256) bfinal_kernel(const FinArgs a) {
+  __shared__ double sh[8][33];
+  const size_t e = (size_t)blockIdx.x * 32 + threadIdx.x;
+  const size_t ng = (size_t)a.ld * a.RP;
+  const int R2 = a.R * a.R;
+  const size_t nall = ng + (size_t)a.nstart * 3 * R2;
+  double s0 = 0.0;
+  size_t dst = 0;
+  if (e < ng) {
+    const int j = (int)(e / a.RP), c = (int)(e % a.RP);
+    const int side = j >= a.p2, jj = side ? j - a.p2 : j;
+    const int db = (side ? a.nbx : 0) + jj / BT, cb = c / BT, tile = db * a.ncb + cb;
+    const size_t off = (size_t)tile * BT * BT + (size_t)(jj % BT) * BT + (c % BT);
+    for (int sp = threadIdx.y; sp < a.nsplit; sp += 8) s0 += a.partial[(size_t)sp * a.ntiles * BT * BT + off];
+    dst = e;
+  } else if (e < nall) {
+    const size_t f = e - ng;
+    const int s = (int)(f / (3 * R2)), w = (int)(f % (3 * R2)), which = w / R2, kl = w % R2, k = kl / a.R, l = kl % a.R;
+    for (int ch = threadIdx.y; ch < a.nchunk; ch += 8) s0 += a.gpart[((size_t)ch * a.nstart + s) * 3 * R2 + w];
+    dst = ng + (size_t)which * a.RP * a.RP + (size_t)(s * a.R + k) * a.RP + s * a.R + l;
+  }
+  sh[threadIdx.y][threadIdx.x] = s0;
+  __syncthreads();
+  if (threadIdx.y == 0 && e < nall) {
+    double t = 0.0;
+#pragma unroll
+    for (int y = 0; y < 8; ++y) t += sh[y][threadIdx.x];
+    a.momvec[dst] = t;
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------------------------------
+void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGemmPlan* p) {
+  p->RP = RP; p->R = R; p->nstart = nstart;
+  p->ncb = RP / BT;
+  p->nbx = (s.p2 + BT - 1) / BT; p->nby = (s.q2 + BT - 1) / BT;
+  p->ntiles = (p->nbx + p->nby) * p->ncb;
+  p->rowtiles = (int)((s.n + BT - 1) / BT);
+  // accumulate GEMM: row splits so that tiles x splits fills whole waves of one CTA per SM
+  const int64_t max_ns = (s.n + 8 * BK - 1) / (8 * BK);
+  int64_t lo = (4 * (int64_t)sm_count + p->ntiles - 1) / p->ntiles, ns = 1;
+  double best = -1.0;
+  for (int64_t c = lo < 1 ? 1 : lo; c < lo + 64; ++c) {
+    const int64_t cc = c > max_ns ? max_ns : c;
+    if (cc < 1) continue;
+    const int64_t ctas = cc * p->ntiles, waves = (ctas + sm_count - 1) / sm_count;
+    const double eff = (double)ctas / (double)(waves * sm_count);
+    if (eff > best + 1e-9) { best = eff; ns = cc; }
+    if (cc == max_ns) break;
+  }
+  int64_t rps = (s.n + ns - 1) / ns;
+  rps = (rps + BK - 1) / BK * BK;
+  p->nsplit = (int)((s.n + rps - 1) / rps);
+  p->rows_per_split = rps;
+  // mu kernel: (32/R starts per warp) x row chunks, about 8 blocks per SM
+  const int sb = (nstart + (32 / R) - 1) / (32 / R);
+  int64_t nc = (4 * (int64_t)sm_count + sb - 1) / sb;
+  const int64_t max_nc = (s.n + 255) / 256;
+  if (nc > max_nc) nc = max_nc;
+  if (nc < 1) nc = 1;
+  int64_t rpc = (s.n + nc - 1) / nc;
+  p->nchunk = (int)((s.n + rpc - 1) / rpc);
+  p->rows_per_chunk = rpc;
+}
+size_t bgemm_workspace_doubles(const DataShape& s, const BGemmPlan& p) {
+  return (size_t)s.n * 2 * p.RP                                   // P / mu
+         + (size_t)p.nsplit * p.ntiles * BT * BT                   // accumulate partials
+         + (size_t)p.nchunk * p.nstart * 3 * p.R * p.R;            // Gram partials
+}
+
+template <int R>
+static void launch_bmu(const MuArgs& m, const BGemmPlan& p, cudaStream_t stream) {
+  constexpr int SW = 32 / R;
+  bmu_kernel<R><<<dim3((p.nstart + SW - 1) / SW, p.nchunk), 256, 0, stream>>>(m);
+}
+
+cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const double* D, const double* Lpack, const double* coef,
+                              double* ws, double* momvec_pack, cudaStream_t stream) {
+  double* P = ws;
+  double* partial = P + (size_t)s.n * 2 * p.RP;
+  double* gpart = partial + (size_t)p.nsplit * p.ntiles * BT * BT;
+  const size_t smemA = (size_t)2 * (BT * BAP + BK * BT) * sizeof(double), smemB = (size_t)2 * 2 * BK * BT * sizeof(double);
+  cudaError_t e = cudaFuncSetAttribute((const void*)bproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)baccum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemB);
+  if (e != cudaSuccess) return e;
+  ProjArgs pa{};
+  pa.D = D; pa.L = Lpack; pa.P = P; pa.n = s.n; pa.ld = s.ld; pa.p2 = s.p2; pa.q2 = s.q2; pa.RP = p.RP;
+  bproj_kernel<<<dim3(p.rowtiles, p.ncb, 2), BTHREADS, smemA, stream>>>(pa);
+  MuArgs m{};
+  m.P = P; m.coef = coef; m.gpart = gpart; m.n = s.n; m.rows_per_chunk = p.rows_per_chunk; m.RP = p.RP; m.R = p.R; m.nstart = p.nstart;
+  switch (p.R) {
+    case 1: launch_bmu<1>(m, p, stream); break;
+    case 2: launch_bmu<2>(m, p, stream); break;
+    case 3: launch_bmu<3>(m, p, stream); break;
+    case 4: launch_bmu<4>(m, p, stream); break;
+    case 5: launch_bmu<5>(m, p, stream); break;
+    case 6: launch_bmu<6>(m, p, stream); break;
+    case 7: launch_bmu<7>(m, p, stream); break;
+    case 8: launch_bmu<8>(m, p, stream); break;
+    default: return cudaErrorInvalidValue;
+  }
+  AccArgs aa{};
+  aa.D = D; aa.MU = P; aa.partial = partial; aa.n = s.n; aa.rows_per_split = p.rows_per_split;
+  aa.ld = s.ld; aa.p2 = s.p2; aa.q2 = s.q2; aa.RP = p.RP; aa.nbx = p.nbx; aa.nby = p.nby; aa.ncb = p.ncb;
+  baccum_kernel<<<dim3(p.ntiles, p.nsplit), BTHREADS, smemB, stream>>>(aa);
+  FinArgs f{};
+  f.partial = partial; f.gpart = gpart; f.momvec = momvec_pack; f.nsplit = p.nsplit; f.ntiles = p.ntiles; f.ncb = p.ncb;
+  f.nbx = p.nbx; f.ld = s.ld; f.p2 = s.p2; f.RP = p.RP; f.R = p.R; f.nstart = p.nstart; f.nchunk = p.nchunk;
+  const size_t ne = (size_t)s.ld * p.RP + (size_t)p.nstart * 3 * p.R * p.R;
+  bfinal_kernel<<<(unsigned)((ne + 31) / 32), dim3(32, 8), 0, stream>>>(f);
+  return cudaGetLastError();
+}
+
+}  // namespace ppls

@@ -539,6 +539,7 @@ struct BatchArgs {
   double* trace;               // [S][tracelen]
   int32_t RP, g, S, tracelen, prepare;
   int32_t p, q, p2, q2, ld;
+  double* coef;                // GEMM path (em_batch.cu): [groups][4][RP] aT bT aU bU instead of pack_st's arrays
 };
 
 template <int R>
@@ -573,7 +574,12 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_batch_kernel(const B
   for (int e = threadIdx.x; e < b.ld * R; e += UPD_THREADS) { const int j = e / R, k = e - j * R; Lp[(size_t)j * RP + k0 + k] = a.L[e]; }
   if (threadIdx.x < R) {
     const int k = threadIdx.x;
-    ps->aT[k0 + k] = st->aT[k]; ps->bT[k0 + k] = st->bT[k]; ps->aU[k0 + k] = st->aU[k]; ps->bU[k0 + k] = st->bU[k];
+    if (b.coef) {
+      double* cf = b.coef + (size_t)group * 4 * RP;
+      cf[k0 + k] = st->aT[k]; cf[RP + k0 + k] = st->bT[k]; cf[2 * RP + k0 + k] = st->aU[k]; cf[3 * RP + k0 + k] = st->bU[k];
+    } else {
+      ps->aT[k0 + k] = st->aT[k]; ps->bT[k0 + k] = st->bT[k]; ps->aU[k0 + k] = st->aU[k]; ps->bU[k0 + k] = st->bU[k];
+    }
   }
 }
 
@@ -830,8 +836,10 @@ static void launch_batch_R(const BatchArgs& b, cudaStream_t stream) {
 }
 cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int S, int tracelen, int prepare,
                                    const double* momvec_pack, double* L_pack, FitState* pack_st, FitState* st,
-                                   double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream) {
+                                   double* momvec_s, double* L_s, double* Lscratch_s, double* trace, cudaStream_t stream,
+                                   double* coef) {
   BatchArgs b;
+  b.coef = coef;
   b.momvec_pack = momvec_pack; b.L_pack = L_pack; b.pack_st = pack_st; b.st = st; b.momvec_s = momvec_s; b.L_s = L_s;
   b.Lscratch_s = Lscratch_s; b.trace = trace; b.RP = RP; b.g = g; b.S = S; b.tracelen = tracelen; b.prepare = prepare;
   b.p = s.p; b.q = s.q; b.p2 = s.p2; b.q2 = s.q2; b.ld = s.ld;
