@@ -646,7 +646,11 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     e = cudaMalloc(&f->wide_ws, wide_workspace_doubles(d->s, f->wplan, &f->woff) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->momvec, (size_t)f->veclen * sizeof(double));
   if (e == cudaSuccess && !(getenv("PPLS_K2_SINGLE") && atoi(getenv("PPLS_K2_SINGLE"))))
-    e = cudaMalloc(&f->upd_scratch, update_grid_scratch_doubles(f->cols ? f->sg.ld : d->s.ld, R) * sizeof(double));
+  {
+    const size_t ub = update_grid_scratch_doubles(f->cols ? f->sg.ld : d->s.ld, R) * sizeof(double);
+    e = cudaMalloc(&f->upd_scratch, ub);
+    if (e == cudaSuccess) e = cudaMemsetAsync(f->upd_scratch, 0, ub, ctx->stream);     // holds the row-block barrier counter
+  }
   if (e == cudaSuccess && f->cols) e = cudaMalloc(&f->Gglob, (size_t)momvec_len(f->sg.ld, R) * sizeof(double));
   if (e == cudaSuccess && f->cols) e = cudaMalloc(&f->Lglob, (size_t)f->sg.ld * R * sizeof(double));
   if (e == cudaSuccess && f->cols) e = cudaMalloc(&f->Lscratch_g, (size_t)f->sg.ld * R * sizeof(double));

@@ -676,24 +676,29 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) *a.x.epoch = next;
   }
-  // ---- phase 1: scalars | Gram of G1, G2 ---------------------------------------------------------
-  // st->done is read by every block at entry, so it may only be raised after the first grid-wide
-  // sync; until then the decision travels in a scratch flag.
+  // ---- phase 1 + 2.  Block 0: the scalar part (log-likelihood, E-step moments, break rule, M-step scalars), which
+  // needs only the Gram tail.  Row blocks, meanwhile: Gram of G1, G2 | barrier among the ROW blocks only (a counter;
+  // all blocks are co-resident under the cooperative launch) | T = G (G'G)^{-1/2} into Lscratch and its Gram.
+  // Whether the run ends with this pass is known only after block 0 is through, so theta_k's loadings in L stay
+  // untouched until the grid-wide sync.  st->done is read by every block at entry, so it may only be raised after
+  // that sync; until then the decision travels in a scratch flag.
   int* done_now = reinterpret_cast<int*>(a.gscratch + (size_t)3 * nb * 2 * R * R);
+  unsigned int* rowbar = reinterpret_cast<unsigned int*>(a.gscratch + (size_t)3 * nb * 2 * R * R + 2);
+  double* T = a.Lscratch;
   if (rb < 0) {
     __shared__ ScalarShared ssh;
     if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) *done_now = d; }
   } else {
     grid_partial_gram<R>(G, 0, a.p2, rb, nb, ph0 + ((size_t)rb * 2 + 0) * R * R, scratch);
     grid_partial_gram<R>(G, a.p2, a.ld, rb, nb, ph0 + ((size_t)rb * 2 + 1) * R * R, scratch);
-  }
-  grid.sync();
-  if (*done_now) {                                        // the run ended with this pass: keep theta_k
-    if (rb < 0 && threadIdx.x == 0) st->done = 1;
-    return;
-  }
-  // ---- phase 2: L = G (G'G)^{-1/2}, Gram of it ------------------------------------------------------
-  if (rb >= 0) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      atomicAdd(rowbar, 1u);
+      while (*reinterpret_cast<volatile unsigned int*>(rowbar) < (unsigned int)nb) { }
+      __threadfence();
+    }
+    __syncthreads();
     grid_sum_gram<R>(ph0, nb, 0, S[0]);
     grid_sum_gram<R>(ph0, nb, 1, S[1]);
     __syncthreads();
@@ -720,14 +725,19 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
         double sacc = 0.0;
 #pragma unroll
         for (int k = 0; k < R; ++k) sacc += row[k] * M[k * R + l];
-        a.L[(size_t)j * R + l] = sacc;
+        T[(size_t)j * R + l] = sacc;
       }
     }
     __syncthreads();
-    grid_partial_gram<R>(a.L, 0, a.p2, rb, nb, ph1 + ((size_t)rb * 2 + 0) * R * R, scratch);
-    grid_partial_gram<R>(a.L, a.p2, a.ld, rb, nb, ph1 + ((size_t)rb * 2 + 1) * R * R, scratch);
+    grid_partial_gram<R>(T, 0, a.p2, rb, nb, ph1 + ((size_t)rb * 2 + 0) * R * R, scratch);
+    grid_partial_gram<R>(T, a.p2, a.ld, rb, nb, ph1 + ((size_t)rb * 2 + 1) * R * R, scratch);
   }
   grid.sync();
+  if (rb < 0 && threadIdx.x == 0) *rowbar = 0u;             // every row block is past the barrier: arm it for the next launch
+  if (*done_now) {                                        // the run ended with this pass: keep theta_k
+    if (rb < 0 && threadIdx.x == 0) st->done = 1;
+    return;
+  }
   // ---- phase 3: one Newton-Schulz step L <- L M, M = (3I - S)/2 with S = L'L --------------------------
   // The Gram of the result is M S M exactly (L is well conditioned here, so S carries full accuracy):
   // block 0 forms W'W, C'C from it while the row blocks apply the step -- no further pass, no further sync.
@@ -744,7 +754,7 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
       const double* M = Mat[j >= a.p2 ? 1 : 0];
       double row[R], res[R];
 #pragma unroll
-      for (int k = 0; k < R; ++k) row[k] = a.L[(size_t)j * R + k];
+      for (int k = 0; k < R; ++k) row[k] = T[(size_t)j * R + k];
 #pragma unroll
       for (int l = 0; l < R; ++l) {
         double sacc = 0.0;
@@ -807,7 +817,7 @@ int update_grid_blocks(int ld) {
   if (nb < 1) nb = 1;
   return nb + 1;
 }
-size_t update_grid_scratch_doubles(int ld, int R) { return (size_t)3 * (update_grid_blocks(ld) - 1) * 2 * R * R + 2; }
+size_t update_grid_scratch_doubles(int ld, int R) { return (size_t)3 * (update_grid_blocks(ld) - 1) * 2 * R * R + 4; }
 
 // Start state: coefficients and Gram matrices for theta_0.
 template <int R>
@@ -936,7 +946,7 @@ cudaError_t launch_reduce_partials(const double* partials, int nparts, int64_t l
 template <int R>
 static void launch_update_R(const UpdateArgs& a, bool prepare, int orth_type, cudaStream_t stream) {
   if (prepare) em_prepare_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
-  else if (orth_type == PPLS_ORTH_SVD && a.gscratch) {
+  else if (orth_type == PPLS_ORTH_SVD && a.gscratch && a.Lscratch) {
     void* args[] = {(void*)&a};
     cudaLaunchCooperativeKernel((const void*)em_update_grid_kernel<R>, dim3(update_grid_blocks(a.ld)), dim3(GT), args, 0, stream);
   } else em_update_kernel<R><<<1, UPD_THREADS, 0, stream>>>(a);
