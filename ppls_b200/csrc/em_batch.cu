@@ -6,9 +6,10 @@
 //   G  = [X' mu_T ; Y' mu_U]              (ld x RP)   baccum_kernel   GEMM "TN": columns x K(rows) x comps
 // 4 (p+q) r S flop per row against 8 (p+q) bytes: S r / 2 flop per byte -- FP64-pipe bound for S r >= 32, so the
 // streaming kernel K1 (built for the HBM-bound r <= 8 case, 4 rows per tile at r = 8) is the wrong tool here.
-// Register-tiled DFMA kernels (no FP64 path on tcgen05; DMMA has the DFMA rate): 128 x 128 tile per CTA, 256
-// threads x (8 x 8) accumulators, cp.async double-buffered operand stages, column pairs interleaved over the
-// threads (pair tx + 16 m) so that every LDS.128 quarter-warp reads 128 contiguous bytes.
+// FP64 tensor-core kernels (mma.sync m8n8k4 f64 -- there is no FP64 kind on tcgen05): 128 x 128 tile per CTA, 8 warps
+// of 64 x 32 (8 x 4 DMMA tiles, accumulators in registers), cp.async double-buffered operand stages in shared memory
+// with pitches chosen so that the 4 k-rows of a fragment fall into disjoint banks.  tools/dmma_probe.cu: DMMA
+// sustains 37 TFLOP/s where a shared-memory-fed DFMA register tile stops at 25 (3 operand reads per FMA).
 #include "common.cuh"
 #include <math.h>
 
@@ -17,13 +18,17 @@ namespace ppls {
 constexpr int BT = 128;         // tile edge
 constexpr int BK = 16;          // K per stage
 constexpr int BTHREADS = 256;
-constexpr int BAP = BK + 2;     // pitch of the row-major A tile of bproj (16-byte aligned rows, conflict-free broadcasts)
+constexpr int BAP = BK + 4;     // pitch of the row-major A tile of bproj: 4 consecutive rows -> disjoint banks
+constexpr int BP = BT + 4;      // pitch of the k-major tiles: 4 consecutive k-rows -> disjoint banks
 
 __device__ __forceinline__ void bcp16(void* smem_dst, const void* gsrc, int src_bytes) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void bcommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bdmma(double (&c)[2], double a, double b) {   // lane l: A[l>>2][l&3], B[l&3][l>>2], C[l>>2][2(l&3)+{0,1}]
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
 template <int N>
 __device__ __forceinline__ void bwait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -34,39 +39,39 @@ struct ProjArgs {
   int ld, p2, q2, RP;            // RP: multiple of BT
 };
 __global__ void __launch_bounds__(BTHREADS, 1) bproj_kernel(const ProjArgs a) {
-  extern __shared__ __align__(16) double sm[];    // [2 stages][ A: BT x BAP | B: BK x BT ]
+  extern __shared__ __align__(16) double sm[];    // [2 stages][ A: BT x BAP | B: BK x BP ]
   const int side = blockIdx.z, cb = blockIdx.y;
   const int64_t row0 = (int64_t)blockIdx.x * BT;
   const int c0 = side ? a.p2 : 0, K = side ? a.q2 : a.p2;
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
+  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;         // this warp's rows / components of the tile
   const int nst = (K + BK - 1) / BK;
-  constexpr int STAGE = BT * BAP + BK * BT;
+  constexpr int STAGE = BT * BAP + BK * BP;
 
   auto issue = [&](int s, int buf) {
     double* As = sm + (size_t)buf * STAGE;
     double* Bs = As + BT * BAP;
     const int k0 = s * BK;
 #pragma unroll
-    for (int c = 0; c < (BT * BK / 2) / BTHREADS; ++c) {          // A: 128 rows x 8 chunks
+    for (int c = 0; c < (BT * BK / 2) / BTHREADS; ++c) {          // A: 128 rows x 8 chunks (row-major, as the data lie)
       const int chunk = tid + c * BTHREADS, r = chunk >> 3, kc = (chunk & 7) * 2;
       const bool ok = (row0 + r < a.n) && (k0 + kc < K);
       bcp16(As + r * BAP + kc, ok ? a.D + (size_t)(row0 + r) * a.ld + c0 + k0 + kc : a.D, ok ? 16 : 0);
     }
 #pragma unroll
-    for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {          // B: 16 k x 64 pairs, pair t*4+m -> slot t + 16 m
+    for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {          // B: 16 k x 64 pairs of components
       const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63;
-      const int slot = (pr >> 2) + 16 * (pr & 3);
       const bool ok = k0 + kk < K;
-      bcp16(Bs + kk * BT + slot * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * BT + pr * 2 : a.L, ok ? 16 : 0);
+      bcp16(Bs + kk * BP + pr * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * BT + pr * 2 : a.L, ok ? 16 : 0);
     }
     bcommit();
   };
 
-  double acc[8][8];
+  double acc[8][4][2];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+    for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
   issue(0, 0);
   for (int s = 0; s < nst; ++s) {
     if (s + 1 < nst) { issue(s + 1, (s + 1) & 1); bwait<1>(); } else bwait<0>();
@@ -74,30 +79,28 @@ __global__ void __launch_bounds__(BTHREADS, 1) bproj_kernel(const ProjArgs a) {
     const double* As = sm + (size_t)(s & 1) * STAGE;
     const double* Bs = As + BT * BAP;
 #pragma unroll
-    for (int kk = 0; kk < BK; ++kk) {
-      double af[8], bf[8];
+    for (int k4 = 0; k4 < BK / 4; ++k4) {
+      const double* ar = As + (wm + gid) * BAP + k4 * 4 + tig;      // A[m = row][k = data column]
+      const double* br = Bs + (k4 * 4 + tig) * BP + wn + gid;       // B[k][n = component]
+      double af[8], bf[4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) af[i] = As[(ty * 8 + i) * BAP + kk];
+      for (int i = 0; i < 8; ++i) af[i] = ar[i * 8 * BAP];
 #pragma unroll
-      for (int m = 0; m < 4; ++m) {
-        const double2 vb = *reinterpret_cast<const double2*>(Bs + kk * BT + tx * 2 + 32 * m);
-        bf[2 * m] = vb.x; bf[2 * m + 1] = vb.y;
-      }
+      for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
 #pragma unroll
       for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fma(af[i], bf[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], bf[j]);
     }
     __syncthreads();
   }
-  // thread (ty, tx): rows ty*8 + i, logical comps cb*128 + tx*8 + 2m + e (slot tx + 16 m holds pair tx*4 + m)
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const int64_t row = row0 + ty * 8 + i;
+    const int64_t row = row0 + wm + i * 8 + gid;
     if (row >= a.n) continue;
-    double* out = a.P + (size_t)row * 2 * a.RP + (size_t)side * a.RP + cb * BT + tx * 8;
+    double* out = a.P + (size_t)row * 2 * a.RP + (size_t)side * a.RP + cb * BT + wn + 2 * tig;
 #pragma unroll
-    for (int m = 0; m < 4; ++m) *reinterpret_cast<double2*>(out + 2 * m) = make_double2(acc[i][2 * m], acc[i][2 * m + 1]);
+    for (int j = 0; j < 4; ++j) *reinterpret_cast<double2*>(out + j * 8) = make_double2(acc[i][j][0], acc[i][j][1]);
   }
 }
 
@@ -161,7 +164,7 @@ struct AccArgs {
   int ld, p2, q2, RP, nbx, nby, ncb;     // column blocks of X / Y (BT wide), comp blocks
 };
 __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
-  extern __shared__ __align__(16) double sm[];    // [2 stages][2 operands][BK][BT]
+  extern __shared__ __align__(16) double sm[];    // [2 stages][2 operands][BK][BP]
   const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block (X blocks, then Y blocks)
   const int side = db >= a.nbx;
   const int col0 = side ? a.p2 + (db - a.nbx) * BT : db * BT;              // first data column of the block
@@ -169,57 +172,57 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
   const double* Bbase = a.MU + (size_t)side * a.RP + (size_t)cb * BT;
   const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_split;
   const int64_t r1 = (r0 + a.rows_per_split < a.n) ? r0 + a.rows_per_split : a.n;
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
+  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;         // this warp's data columns / components of the tile
   const int nst = (r1 > r0) ? (int)((r1 - r0 + BK - 1) / BK) : 0;
 
   auto issue = [&](int s, int buf) {
-    double* As = sm + (size_t)(buf * 2 + 0) * BK * BT;
-    double* Bs = sm + (size_t)(buf * 2 + 1) * BK * BT;
+    double* As = sm + (size_t)(buf * 2 + 0) * BK * BP;
+    double* Bs = sm + (size_t)(buf * 2 + 1) * BK * BP;
 #pragma unroll
     for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {
-      const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63, slot = (pr >> 2) + 16 * (pr & 3);
+      const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63;
       const int64_t grow = r0 + (int64_t)s * BK + kk;
       const bool rok = grow < r1;
       const bool okA = rok && (col0 + pr * 2 < cend);
-      bcp16(As + kk * BT + slot * 2, okA ? a.D + (size_t)grow * a.ld + col0 + pr * 2 : a.D, okA ? 16 : 0);
-      bcp16(Bs + kk * BT + slot * 2, rok ? Bbase + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
+      bcp16(As + kk * BP + pr * 2, okA ? a.D + (size_t)grow * a.ld + col0 + pr * 2 : a.D, okA ? 16 : 0);
+      bcp16(Bs + kk * BP + pr * 2, rok ? Bbase + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
     }
     bcommit();
   };
-  double acc[8][8];
+  double acc[8][4][2];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+    for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
   if (nst > 0) issue(0, 0);
   for (int s = 0; s < nst; ++s) {
     if (s + 1 < nst) { issue(s + 1, (s + 1) & 1); bwait<1>(); } else bwait<0>();
     __syncthreads();
-    const double* As = sm + (size_t)((s & 1) * 2 + 0) * BK * BT;
-    const double* Bs = As + BK * BT;
+    const double* As = sm + (size_t)((s & 1) * 2 + 0) * BK * BP;
+    const double* Bs = As + BK * BP;
 #pragma unroll
-    for (int kk = 0; kk < BK; ++kk) {
-      double af[8], bf[8];
+    for (int k4 = 0; k4 < BK / 4; ++k4) {
+      const double* ar = As + (k4 * 4 + tig) * BP + wm + gid;       // A[m = data column][k = row]
+      const double* br = Bs + (k4 * 4 + tig) * BP + wn + gid;       // B[k = row][n = component]
+      double af[8], bf[4];
 #pragma unroll
-      for (int m = 0; m < 4; ++m) {
-        const double2 va = *reinterpret_cast<const double2*>(As + kk * BT + ty * 2 + 32 * m);
-        const double2 vb = *reinterpret_cast<const double2*>(Bs + kk * BT + tx * 2 + 32 * m);
-        af[2 * m] = va.x; af[2 * m + 1] = va.y; bf[2 * m] = vb.x; bf[2 * m + 1] = vb.y;
-      }
+      for (int i = 0; i < 8; ++i) af[i] = ar[i * 8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
 #pragma unroll
       for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fma(af[i], bf[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], bf[j]);
     }
     __syncthreads();
   }
-  // thread (ty, tx): data columns ty*8 + 2m + e of the block, comps tx*8 + 2m' + e'
   double* out = a.partial + ((size_t)blockIdx.y * gridDim.x + tile) * BT * BT;
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int m = 0; m < 4; ++m)
-      *reinterpret_cast<double2*>(out + (ty * 8 + i) * BT + tx * 8 + 2 * m) = make_double2(acc[i][2 * m], acc[i][2 * m + 1]);
+    for (int j = 0; j < 4; ++j)
+      *reinterpret_cast<double2*>(out + (wm + i * 8 + gid) * BT + wn + j * 8 + 2 * tig) = make_double2(acc[i][j][0], acc[i][j][1]);
 }
 
 // momvec_pack = [G (ld x RP) | Gxx (RP x RP) | Gxy | Gyy]: G summed over the row splits in fixed order, the Gram
@@ -309,7 +312,7 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
   double* P = ws;
   double* partial = P + (size_t)s.n * 2 * p.RP;
   double* gpart = partial + (size_t)p.nsplit * p.ntiles * BT * BT;
-  const size_t smemA = (size_t)2 * (BT * BAP + BK * BT) * sizeof(double), smemB = (size_t)2 * 2 * BK * BT * sizeof(double);
+  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double), smemB = (size_t)2 * 2 * BK * BP * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute((const void*)bproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA);
   if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)baccum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemB);
   if (e != cudaSuccess) return e;

@@ -11,14 +11,21 @@
 namespace ppls {
 
 constexpr int VT = 128;        // Gram tile: VT x VT outputs per CTA
-constexpr int VK = 16;         // rows per pipeline stage
-constexpr int VTHREADS = 256;  // 16 x 16 threads, 8 x 8 outputs each
+constexpr int VK = 32;         // rows per pipeline stage (fewer barriers: +2 %)
+constexpr int VTHREADS = 256;  // 8 warps: 2 x 4, each a 64 x 32 block of the tile = 8 x 4 DMMA tiles of 8 x 8
+constexpr int VP = VT + 4;     // smem pitch: the 4 k-rows of a DMMA fragment fall into disjoint banks
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(src_bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// D (8x8) += A (8x4, row) * B (4x8, col) on the FP64 tensor path.  Lane l: A[l>>2][l&3], B[l&3][l>>2], C[l>>2][2(l&3) + {0,1}].
+// Measured on B200 (tools/dmma_probe.cu): 37.0 TFLOP/s at 8 warps/SM; the same loop with DFMA tops out at 33 with ideal
+// operand reuse and at 25 inside a shared-memory-fed 8x8 register tile (register bandwidth: 3 operands per FMA).
+__device__ __forceinline__ void dmma884(double (&c)[2], double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
+}
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -36,72 +43,71 @@ struct GramArgs {
 
 // partial[split][tile (bi<=bj)] = sum over the split's rows of side[:, bi-block]' side[:, bj-block]
 __global__ void __launch_bounds__(VTHREADS, 1) var_gram_kernel(const GramArgs a) {
-  extern __shared__ __align__(16) double sm[];          // [2 stages][2 operands][VK][VT]
+  extern __shared__ __align__(16) double sm[];          // [2 stages][2 operands][VK][VP]
   int bi = 0, rem = blockIdx.x;
   while (rem >= a.nb - bi) { rem -= a.nb - bi; ++bi; }
   const int bj = bi + rem;
   const bool diag = (bi == bj);
   const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_split;
   const int64_t r1 = (r0 + a.rows_per_split < a.n) ? r0 + a.rows_per_split : a.n;
-  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
+  const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;         // this warp's block of the tile
   const int nst = (r1 > r0) ? (int)((r1 - r0 + VK - 1) / VK) : 0;
   const double* baseA = a.D + a.base + (size_t)bi * a.block_stride;
   const double* baseB = a.D + a.base + (size_t)bj * a.block_stride;
 
   auto issue = [&](int s, int buf) {
-    double* dstA = sm + (size_t)(buf * 2 + 0) * VK * VT;
-    double* dstB = sm + (size_t)(buf * 2 + 1) * VK * VT;
+    double* dstA = sm + (size_t)(buf * 2 + 0) * VK * VP;
+    double* dstB = sm + (size_t)(buf * 2 + 1) * VK * VP;
 #pragma unroll
     for (int c = 0; c < (VK * VT / 2) / VTHREADS; ++c) {
       const int chunk = tid + c * VTHREADS, row = chunk >> 6, col = (chunk & 63) * 2;
       const int64_t grow = r0 + (int64_t)s * VK + row;
       const bool rok = grow < r1;
       const bool okA = rok && (!a.masked || bi * VT + col < a.w2);
-      cp_async16(dstA + row * VT + col, okA ? baseA + (size_t)grow * a.pitch + col : a.D, okA ? 16 : 0);
+      cp_async16(dstA + row * VP + col, okA ? baseA + (size_t)grow * a.pitch + col : a.D, okA ? 16 : 0);
       if (!diag) {
         const bool okB = rok && (!a.masked || bj * VT + col < a.w2);
-        cp_async16(dstB + row * VT + col, okB ? baseB + (size_t)grow * a.pitch + col : a.D, okB ? 16 : 0);
+        cp_async16(dstB + row * VP + col, okB ? baseB + (size_t)grow * a.pitch + col : a.D, okB ? 16 : 0);
       }
     }
     cp_async_commit();
   };
 
-  double acc[8][8];
+  double acc[8][4][2];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[i][j] = 0.0;
+    for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
 
   if (nst > 0) issue(0, 0);
   for (int s = 0; s < nst; ++s) {
     if (s + 1 < nst) { issue(s + 1, (s + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
     __syncthreads();
-    const double* As = sm + (size_t)((s & 1) * 2 + 0) * VK * VT;
-    const double* Bs = diag ? As : As + VK * VT;
+    const double* As = sm + (size_t)((s & 1) * 2 + 0) * VK * VP;
+    const double* Bs = diag ? As : As + VK * VP;
 #pragma unroll
-    for (int kk = 0; kk < VK; ++kk) {
-      double af[8], bf[8];
+    for (int k4 = 0; k4 < VK / 4; ++k4) {
+      const double* ar = As + (k4 * 4 + tig) * VP + wm + gid;
+      const double* br = Bs + (k4 * 4 + tig) * VP + wn + gid;
+      double af[8], bf[4];
 #pragma unroll
-      for (int m = 0; m < 4; ++m) {
-        const double2 va = *reinterpret_cast<const double2*>(As + kk * VT + ty * 2 + 32 * m);
-        const double2 vb = *reinterpret_cast<const double2*>(Bs + kk * VT + tx * 2 + 32 * m);
-        af[2 * m] = va.x; af[2 * m + 1] = va.y; bf[2 * m] = vb.x; bf[2 * m + 1] = vb.y;
-      }
+      for (int i = 0; i < 8; ++i) af[i] = ar[i * 8];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
 #pragma unroll
       for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = fma(af[i], bf[j], acc[i][j]);
+        for (int j = 0; j < 4; ++j) dmma884(acc[i][j], af[i], bf[j]);
     }
     __syncthreads();
   }
   double* out = a.partial + ((size_t)blockIdx.y * a.ntiles + blockIdx.x) * VT * VT;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int row = ty * 2 + 32 * (i >> 1) + (i & 1);
+  for (int i = 0; i < 8; ++i)
 #pragma unroll
-    for (int m = 0; m < 4; ++m)
-      *reinterpret_cast<double2*>(out + row * VT + tx * 2 + 32 * m) = make_double2(acc[i][2 * m], acc[i][2 * m + 1]);
-  }
+    for (int j = 0; j < 4; ++j)
+      *reinterpret_cast<double2*>(out + (wm + i * 8 + gid) * VT + wn + j * 8 + 2 * tig) = make_double2(acc[i][j][0], acc[i][j][1]);
 }
 
 // S[j][l] = S[l][j] = sum over splits (fixed order) of the tile partials, for j <= l < w
@@ -342,7 +348,7 @@ static GramArgs gram_args(const VarPlan& p, const DataShape& s, const double* D,
 cudaError_t launch_var_gram(const VarPlan& p, const DataShape& s, const double* D, double* partial, double* S, cudaStream_t stream) {
   GramArgs a = gram_args(p, s, D, p.c0 != 0);
   a.rows_per_split = p.rows_per_split; a.partial = partial;
-  const size_t smem = (size_t)2 * 2 * VK * VT * sizeof(double);
+  const size_t smem = (size_t)2 * 2 * VK * VP * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute((const void*)var_gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   var_gram_kernel<<<dim3(p.ntiles, p.nsplit), VTHREADS, smem, stream>>>(a);
