@@ -307,7 +307,7 @@ def run_c5(args):
            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
            "config": {"workload": f"c5: {C5_STARTS} starts x N={N} p={p} q={q} r={r}, all {C5_STARTS * r} components per data pass (two FP64 GEMMs, em_batch.cu)",
                       "wall_ms_per_step_incl_setup": wall_ms / K}, "clocks": clocks, "gpu_launches": int(tm["kernel_launches"]),
-           "roofline": {"bound": "fp64 (vector FMA; SURVEY.md 8d config 5)", "achieved": flops / (loop_ms * 1e-3) / 1e12,
+           "roofline": {"bound": "fp64 (tensor DMMA / FMA pipe, same peak; SURVEY.md 8d config 5)", "achieved": flops / (loop_ms * 1e-3) / 1e12,
                         "peak": 37.0, "unit": "TFLOP/s", "frac": flops / (loop_ms * 1e-3) / 1e12 / 37.0, "traffic": None,
                         "peak_source": "nominal B200 FP64 (148 SMs x 64 FMA/clk x 1.965 GHz); not in MEASURED_PEAKS.json",
                         "hbm_gbs_algorithmic": tm["bytes_per_pass"] * tm["stream_launches"] / (loop_ms * 1e-3) / 1e9},

@@ -133,7 +133,7 @@ int update_grid_blocks(int ld);
 // batched multi-start as two FP64 GEMMs per pass (em_batch.cu)
 struct BGemmPlan {
   int RP, R, nstart;            // components of the group (multiple of 128), per start, starts in the group
-  int ncb, nbx, nby, ntiles, rowtiles;
+  int ncb, nbx, nby, ntiles, rowtiles, unified;
   int nsplit; int64_t rows_per_split;
   int nchunk; int64_t rows_per_chunk;
 };

@@ -162,14 +162,26 @@ struct AccArgs {
   const double* D; const double* MU; double* partial;
   int64_t n, rows_per_split;
   int ld, p2, q2, RP, nbx, nby, ncb;     // column blocks of X / Y (BT wide), comp blocks
+  int unified;                           // 1: blocks run over the whole row [0, ld); a block may straddle the X|Y boundary
 };
 __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
-  extern __shared__ __align__(16) double sm[];    // [2 stages][2 operands][BK][BP]
-  const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block (X blocks, then Y blocks)
-  const int side = db >= a.nbx;
-  const int col0 = side ? a.p2 + (db - a.nbx) * BT : db * BT;              // first data column of the block
-  const int cend = side ? a.ld : a.p2;                                    // columns of the side end here
-  const double* Bbase = a.MU + (size_t)side * a.RP + (size_t)cb * BT;
+  extern __shared__ __align__(16) double sm[];    // [2 stages][2 operands][BK][BP] (+ [2 stages][BK][BP] of mu_U for a mixed block)
+  const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block
+  // separate mode: X blocks, then Y blocks, each side padded to the tile.  unified mode (p2 % 8 == 0): blocks over
+  // the whole row; in the block that straddles the X|Y boundary every 8-column DMMA tile still lies on one side,
+  // so it takes its B fragment from mu_T or from mu_U (both staged) -- C5: 250 -> 256 columns instead of 384.
+  int side, col0, cend;
+  bool mixed = false;
+  if (a.unified) {
+    col0 = db * BT; cend = a.ld;
+    side = col0 >= a.p2;
+    mixed = (col0 < a.p2) && (col0 + BT > a.p2);
+  } else {
+    side = db >= a.nbx;
+    col0 = side ? a.p2 + (db - a.nbx) * BT : db * BT;
+    cend = side ? a.ld : a.p2;
+  }
+  const double* Bbase = a.MU + (size_t)side * a.RP + (size_t)cb * BT;       // mixed: side = 0 here, mu_U = Bbase + RP
   const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_split;
   const int64_t r1 = (r0 + a.rows_per_split < a.n) ? r0 + a.rows_per_split : a.n;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
@@ -187,9 +199,14 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
       const bool okA = rok && (col0 + pr * 2 < cend);
       bcp16(As + kk * BP + pr * 2, okA ? a.D + (size_t)grow * a.ld + col0 + pr * 2 : a.D, okA ? 16 : 0);
       bcp16(Bs + kk * BP + pr * 2, rok ? Bbase + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
+      if (mixed) bcp16(sm + (size_t)(4 + buf) * BK * BP + kk * BP + pr * 2, rok ? Bbase + a.RP + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
     }
     bcommit();
   };
+  // per DMMA tile of this warp: does it take mu_U?  (bit i: data columns col0 + wm + 8 i .. + 7)
+  unsigned ymask = 0;
+  if (mixed)
+    for (int i = 0; i < 8; ++i) if (col0 + wm + i * 8 >= a.p2) ymask |= 1u << i;
   double acc[8][4][2];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
@@ -210,10 +227,23 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
       for (int i = 0; i < 8; ++i) af[i] = ar[i * 8];
 #pragma unroll
       for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
+      if (!mixed) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < 8; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], bf[j]);
+          for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], bf[j]);
+      } else {
+        const double* bu = sm + (size_t)(4 + (s & 1)) * BK * BP + (k4 * 4 + tig) * BP + wn + gid;
+        double bg[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) bg[j] = bu[j * 8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const bool y = (ymask >> i) & 1u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], y ? bg[j] : bf[j]);
+        }
+      }
     }
     __syncthreads();
   }
@@ -229,7 +259,7 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
 // blocks of every start summed over the row chunks and written on the block diagonal (nothing else is read).
 struct FinArgs {
   const double* partial; const double* gpart; double* momvec;
-  int nsplit, ntiles, ncb, nbx, ld, p2, RP, R, nstart, nchunk;
+  int nsplit, ntiles, ncb, nbx, ld, p2, RP, R, nstart, nchunk, unified;
 };
 __global__ void __launch_bounds__(256) bfinal_kernel(const FinArgs a) {
   __shared__ double sh[8][33];
@@ -241,8 +271,8 @@ __global__ void __launch_bounds__(256) bfinal_kernel(const FinArgs a) {
   size_t dst = 0;
   if (e < ng) {
     const int j = (int)(e / a.RP), c = (int)(e % a.RP);
-    const int side = j >= a.p2, jj = side ? j - a.p2 : j;
-    const int db = (side ? a.nbx : 0) + jj / BT, cb = c / BT, tile = db * a.ncb + cb;
+    const int side = j >= a.p2, jj = a.unified ? j : (side ? j - a.p2 : j);
+    const int db = (a.unified ? 0 : (side ? a.nbx : 0)) + jj / BT, cb = c / BT, tile = db * a.ncb + cb;
     const size_t off = (size_t)tile * BT * BT + (size_t)(jj % BT) * BT + (c % BT);
     for (int sp = threadIdx.y; sp < a.nsplit; sp += 8) s0 += a.partial[(size_t)sp * a.ntiles * BT * BT + off];
     dst = e;
@@ -267,7 +297,8 @@ void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGe
   p->RP = RP; p->R = R; p->nstart = nstart;
   p->ncb = RP / BT;
   p->nbx = (s.p2 + BT - 1) / BT; p->nby = (s.q2 + BT - 1) / BT;
-  p->ntiles = (p->nbx + p->nby) * p->ncb;
+  p->unified = (s.p2 % 8 == 0) && ((s.ld + BT - 1) / BT < p->nbx + p->nby);
+  p->ntiles = (p->unified ? (s.ld + BT - 1) / BT : p->nbx + p->nby) * p->ncb;
   p->rowtiles = (int)((s.n + BT - 1) / BT);
   // accumulate GEMM: row splits so that tiles x splits fills whole waves of one CTA per SM
   const int64_t max_ns = (s.n + 8 * BK - 1) / (8 * BK);
@@ -312,7 +343,7 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
   double* P = ws;
   double* partial = P + (size_t)s.n * 2 * p.RP;
   double* gpart = partial + (size_t)p.nsplit * p.ntiles * BT * BT;
-  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double), smemB = (size_t)2 * 2 * BK * BP * sizeof(double);
+  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double), smemB = (size_t)2 * 3 * BK * BP * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute((const void*)bproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA);
   if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)baccum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemB);
   if (e != cudaSuccess) return e;
@@ -334,11 +365,11 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
   }
   AccArgs aa{};
   aa.D = D; aa.MU = P; aa.partial = partial; aa.n = s.n; aa.rows_per_split = p.rows_per_split;
-  aa.ld = s.ld; aa.p2 = s.p2; aa.q2 = s.q2; aa.RP = p.RP; aa.nbx = p.nbx; aa.nby = p.nby; aa.ncb = p.ncb;
+  aa.ld = s.ld; aa.p2 = s.p2; aa.q2 = s.q2; aa.RP = p.RP; aa.nbx = p.nbx; aa.nby = p.nby; aa.ncb = p.ncb; aa.unified = p.unified;
   baccum_kernel<<<dim3(p.ntiles, p.nsplit), BTHREADS, smemB, stream>>>(aa);
   FinArgs f{};
   f.partial = partial; f.gpart = gpart; f.momvec = momvec_pack; f.nsplit = p.nsplit; f.ntiles = p.ntiles; f.ncb = p.ncb;
-  f.nbx = p.nbx; f.ld = s.ld; f.p2 = s.p2; f.RP = p.RP; f.R = p.R; f.nstart = p.nstart; f.nchunk = p.nchunk;
+  f.nbx = p.nbx; f.ld = s.ld; f.p2 = s.p2; f.RP = p.RP; f.R = p.R; f.nstart = p.nstart; f.nchunk = p.nchunk; f.unified = p.unified;
   const size_t ne = (size_t)s.ld * p.RP + (size_t)p.nstart * 3 * p.R * p.R;
   bfinal_kernel<<<(unsigned)((ne + 31) / 32), dim3(32, 8), 0, stream>>>(f);
   return cudaGetLastError();

@@ -172,7 +172,9 @@ def test_wide_shapes_vs_fused_oracle(ctx, oracle_lib, shape, steps):
                                             # S*r >= 64: the two-GEMM path (em_batch.cu) -- one group, padded group,
                                             # r not dividing 128, several groups, rows not a multiple of the tile
                                             ((3001, 200, 50, 2), 64, 6), ((1500, 131, 37, 3), 25, 5),
-                                            ((999, 60, 22, 2), 70, 4), ((700, 300, 140, 8), 20, 3), ((2000, 50, 20, 1), 80, 5)])
+                                            ((999, 60, 22, 2), 70, 4), ((700, 300, 140, 8), 20, 3), ((2000, 50, 20, 1), 80, 5),
+                                            # column blocks that straddle the X|Y boundary (p2 % 8 == 0)
+                                            ((1200, 72, 40, 2), 40, 4), ((900, 136, 100, 4), 16, 3)])
 def test_batched_multistart_matches_single_runs(ctx, oracle_lib, shape, S, steps):
     """ppls_simult_run_batched (starts packed into the streaming kernel's component dimension) ==
     one ordinary run per start, and == the oracle for the first start."""
