@@ -105,6 +105,52 @@ class ClockSampler:
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def host_budget_bytes():
+    """Host memory this process may still take: MemAvailable, capped by the cgroup limit when there is one."""
+    avail = 0
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                avail = int(line.split()[1]) * 1024
+                break
+    except Exception:
+        return 0
+    for lim, cur in (("/sys/fs/cgroup/memory.max", "/sys/fs/cgroup/memory.current"),
+                     ("/sys/fs/cgroup/memory/memory.limit_in_bytes", "/sys/fs/cgroup/memory/memory.usage_in_bytes")):
+        try:
+            v = open(lim).read().strip()
+            if v != "max":
+                avail = min(avail, int(v) - int(open(cur).read().strip()))
+            break
+        except Exception:
+            continue
+    return max(avail, 0)
+
+
+class PinnedPair:
+    """Column-major host X (n x p) and Y (n x q), page-locked with cudaHostRegister (torch's pinned allocator
+    rounds sizes up to a power of two, too much at 96 GB)."""
+
+    def __init__(self, n, p, q):
+        import torch
+        self.rt = torch.cuda.cudart()
+        self.X = np.empty((n, p), order="F")
+        self.Y = np.empty((n, q), order="F")
+        self.reg = []
+        for a in (self.X, self.Y):
+            rc = self.rt.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+            if int(rc) != 0:
+                self.close()
+                raise RuntimeError(f"cudaHostRegister of {a.nbytes} bytes failed: {rc}")
+            self.reg.append(a.ctypes.data)
+
+    def close(self):
+        for ptr in self.reg:
+            self.rt.cudaHostUnregister(ptr)
+        self.reg = []
+        self.X = self.Y = None
+
+
 def shard_rows(N, rank, world):
     lo, hi = N * rank // world, N * (rank + 1) // world
     return lo, hi - lo
@@ -191,16 +237,35 @@ def run_ours(args):
         loop_ms, k1_ms, wall_ms = (float(x) for x in t.cpu()[:3])
     fit.close()
 
-    # ---- e2e: the public call with HOST buffers (upload + K steps + download), on a row sample ----
+    # ---- e2e: the public call with HOST buffers (upload + K steps + download) ----
+    # Full shard when the host can hold it pinned (the device copy is freed first: two copies of C3 exceed
+    # the HBM), else a row sample scaled to the shard; `e2e.sample` says which.
     e2e = None
     if not args.no_e2e:
-        ns = min(n_local, args.e2e_rows)
-        Xh, Yh = data.export(0, ns)                      # product API; gives the host-side inputs
-        Xp = torch.empty((Xh.shape[1], ns), dtype=torch.float64, pin_memory=True)
-        Yp = torch.empty((Yh.shape[1], ns), dtype=torch.float64, pin_memory=True)
-        Xn, Yn = Xp.numpy().T, Yp.numpy().T               # column-major views (R layout), pinned
-        Xn[...] = Xh; Yn[...] = Yh
-        del Xh, Yh
+        shard_bytes = 8 * n_local * (data.p + data.q)
+        full = (not colmode and args.e2e_rows == 0 and shard_bytes > 8 * 1_000_000 * (data.p + data.q)
+                and shard_bytes * world <= 0.55 * host_budget_bytes())
+        if world > 1:                                    # every rank takes the same branch
+            t = torch.tensor([1.0 if full else 0.0], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            full = bool(t.cpu()[0] > 0.5)
+        ns = n_local if full else min(n_local, args.e2e_rows or 1_000_000)
+        pinned = None
+        if full:
+            try:
+                pinned = PinnedPair(ns, data.p, data.q)
+            except Exception as ex:                      # cannot pin that much here: fall back to the sample
+                print(f"[bench] full-size pinned buffers unavailable ({ex}); using a row sample", file=sys.stderr)
+                full, ns = False, min(n_local, 1_000_000)
+        if pinned is not None:
+            Xn, Yn = pinned.X, pinned.Y
+            data.export(0, ns, out=(Xn, Yn))             # product API; fills the host-side inputs
+            data.close()                                 # the e2e call allocates its own device copy
+        else:
+            Xp = torch.empty((data.p, ns), dtype=torch.float64, pin_memory=True)
+            Yp = torch.empty((data.q, ns), dtype=torch.float64, pin_memory=True)
+            Xn, Yn = Xp.numpy().T, Yp.numpy().T           # column-major views (R layout), pinned
+            data.export(0, ns, out=(Xn, Yn))
         barrier()
         e0 = time.perf_counter()
         d2 = Data.from_host_cols(ctx, Xn, Yn) if colmode else Data.from_host(ctx, Xn, Yn)
@@ -216,13 +281,18 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e_s = float(t.cpu()[0])
         scale = n_local / ns
+        what = (f"the full shard, {ns} rows/GPU" if ns == n_local else f"{ns} rows/GPU")
         e2e = {"value": K / (e_s * scale), "unit": UNIT, "h2d_bytes_per_step": int(8 * ns * (data.p + data.q) * scale / K),
                "d2h_bytes_per_step": int(8 * ((p + q) * r + 2 * r + 3 + K) / K),
-               "sample": f"one PPLS_simult-style call (upload {ns} rows/GPU from pinned host memory, {K} EM steps, "
-                         f"download estimates+loglik), time scaled x{scale:.1f} to the full shard",
+               "sample": f"one PPLS_simult-style call (upload {what} from pinned host memory, {K} EM steps, "
+                         f"download estimates+loglik)" + ("" if ns == n_local else f", time scaled x{scale:.1f} to the full shard"),
+               "full_size": ns == n_local,
                "seconds_sample": e_s, "upload_seconds_sample": up_s,
                "upload_gbs": 8 * ns * (data.p + data.q) / up_s / 1e9, "loglik_last": float(res["loglik"][-1])}
-        del Xp, Yp
+        if pinned is not None:
+            pinned.close()
+        else:
+            del Xp, Yp
     data.close()
     # orderly teardown on EVERY rank (communicators are collective objects), then leave without
     # running interpreter-exit destructors: a rank that lingers in them hangs torchrun
@@ -388,7 +458,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--rows", type=int, default=0, help="override N (debugging)")
-    ap.add_argument("--e2e-rows", type=int, default=1_000_000)
+    ap.add_argument("--e2e-rows", type=int, default=0, help="rows per GPU of the e2e call; 0 = the full shard when the host can pin it, else 1e6")
     ap.add_argument("--cpu-rows", type=int, default=100_000)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

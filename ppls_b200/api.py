@@ -168,9 +168,17 @@ class Data:
                                                  C.byref(pb.struct), C.byref(h)))
         return cls(ctx, h)
 
-    def export(self, row0: int = 0, n: Optional[int] = None):
+    def export(self, row0: int = 0, n: Optional[int] = None, out=None):
+        """Rows [row0, row0+n) back to the host, column-major.  `out=(X, Y)`: caller-owned column-major
+        float64 arrays (e.g. pinned) of shape (n, p) and (n, q) to fill instead of fresh ones."""
         n = self.n - row0 if n is None else n
-        X = np.empty((n, self.p), order="F"); Y = np.empty((n, self.q), order="F")
+        if out is not None:
+            X, Y = out
+            if X.shape != (n, self.p) or Y.shape != (n, self.q) or not (X.flags.f_contiguous and Y.flags.f_contiguous) \
+                    or X.dtype != np.float64 or Y.dtype != np.float64:
+                raise ValueError("out must be column-major float64 arrays of shape (n, p) and (n, q)")
+        else:
+            X = np.empty((n, self.p), order="F"); Y = np.empty((n, self.q), order="F")
         L.check(L.lib().ppls_data_export(self.ctx._h, self._h, row0, n, X.ctypes.data, max(n, 1), Y.ctypes.data, max(n, 1)))
         return X, Y
 

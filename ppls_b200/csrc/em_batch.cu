@@ -12,12 +12,14 @@
 // sustains 37 TFLOP/s where a shared-memory-fed DFMA register tile stops at 25 (3 operand reads per FMA).
 #include "common.cuh"
 #include <math.h>
+#include <stdlib.h>
 
 namespace ppls {
 
 constexpr int BT = 128;         // tile edge
 constexpr int BK = 16;          // K per stage
 constexpr int BTHREADS = 256;
+constexpr int BACC_STAGES_DEFAULT = 3;   // cp.async stages of the accumulate GEMM (PPLS_BACC_STAGES=2..4 overrides)
 constexpr int BAP = BK + 4;     // pitch of the row-major A tile of bproj: 4 consecutive rows -> disjoint banks
 constexpr int BP = BT + 4;      // pitch of the k-major tiles: 4 consecutive k-rows -> disjoint banks
 
@@ -157,6 +159,160 @@ __global__ void __launch_bounds__(256) bmu_kernel(const MuArgs a) {
   }
 }
 
+// ---- fused projection + posterior means + Gram blocks (R divides 8) ---------------------------------------------
+// One CTA = 128 rows x 64 components, BOTH sides: the K loop runs over the X columns into accx, then over the Y
+// columns into accy (one continuous cp.async pipeline, FSTAGES deep), so a thread ends up holding Xw and Yc of the
+// same (row, component) and the epilogue writes mu_T / mu_U straight from registers -- P never makes the round trip
+// through HBM that bproj_kernel + bmu_kernel cost (n x 2RP doubles written, read and written again).  The r x r Gram
+// blocks of a start come from the same registers: R <= 2 keeps a start inside one thread (components 2 tig, 2 tig + 1
+// of a DMMA tile), R = 4, 8 fetch the start's other components from the neighbouring lanes of the quad.
+constexpr int FT_N = 64;          // components per CTA
+constexpr int FSTAGES = 4;
+constexpr int FBP = FT_N + 4;     // pitch of the k-major loadings tile
+constexpr int FSTAGE = BT * BAP + BK * FBP;
+struct ProjMuArgs {
+  const double* D; const double* L; const double* coef; double* P; double* gpart;
+  int64_t n;
+  int ld, p2, q2, RP, nstart;
+};
+template <int R>
+__global__ void __launch_bounds__(BTHREADS, 1) bprojmu_kernel(const ProjMuArgs a) {
+  static_assert(8 % R == 0, "a start must not straddle a DMMA tile");
+  extern __shared__ __align__(16) double sm[];    // [FSTAGES][ A: BT x BAP | B: BK x FBP ]; reused by the Gram fold
+  const int ncb2 = a.RP / FT_N;
+  const int cb = blockIdx.x % ncb2;               // component block (fastest: the CTAs sharing a row tile run together)
+  const int64_t rt = blockIdx.x / ncb2, row0 = rt * BT;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
+  const int wr = warp >> 1, wm = wr * 32, wn = (warp & 1) * 32;  // this warp's rows / components of the tile
+  const int nsX = (a.p2 + BK - 1) / BK, nsY = (a.q2 + BK - 1) / BK, nst = nsX + nsY;
+
+  auto issue = [&](int s, int buf) {
+    double* As = sm + (size_t)buf * FSTAGE;
+    double* Bs = As + BT * BAP;
+    const bool sideY = s >= nsX;
+    const int c0 = sideY ? a.p2 : 0, K = sideY ? a.q2 : a.p2, k0 = (sideY ? s - nsX : s) * BK;
+#pragma unroll
+    for (int c = 0; c < (BT * BK / 2) / BTHREADS; ++c) {          // A: 128 rows x 8 chunks of 2 columns
+      const int chunk = tid + c * BTHREADS, r = chunk >> 3, kc = (chunk & 7) * 2;
+      const bool ok = (row0 + r < a.n) && (k0 + kc < K);
+      bcp16(As + r * BAP + kc, ok ? a.D + (size_t)(row0 + r) * a.ld + c0 + k0 + kc : a.D, ok ? 16 : 0);
+    }
+#pragma unroll
+    for (int c = 0; c < (BK * FT_N / 2) / BTHREADS; ++c) {        // B: 16 k x 32 pairs of components
+      const int chunk = tid + c * BTHREADS, kk = chunk >> 5, pr = chunk & 31;
+      const bool ok = k0 + kk < K;
+      bcp16(Bs + kk * FBP + pr * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * FT_N + pr * 2 : a.L, ok ? 16 : 0);
+    }
+  };
+
+  double accx[4][4][2], accy[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { accx[i][j][0] = 0.0; accx[i][j][1] = 0.0; accy[i][j][0] = 0.0; accy[i][j][1] = 0.0; }
+#pragma unroll
+  for (int s = 0; s < FSTAGES - 1; ++s) { if (s < nst) issue(s, s); bcommit(); }
+  for (int s = 0; s < nst; ++s) {
+    bwait<FSTAGES - 2>();                      // stage s has landed (one group is committed per stage slot)
+    __syncthreads();                           // ... for every thread; and everyone is done with stage s-1's buffer
+    if (s + FSTAGES - 1 < nst) issue(s + FSTAGES - 1, (s + FSTAGES - 1) % FSTAGES);
+    bcommit();
+    const double* As = sm + (size_t)(s % FSTAGES) * FSTAGE;
+    const double* Bs = As + BT * BAP;
+    const bool sideY = s >= nsX;
+#pragma unroll
+    for (int k4 = 0; k4 < BK / 4; ++k4) {
+      const double* ar = As + (wm + gid) * BAP + k4 * 4 + tig;      // A[m = row][k = data column]
+      const double* br = Bs + (k4 * 4 + tig) * FBP + wn + gid;      // B[k][n = component]
+      double af[4], bf[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) af[i] = ar[i * 8 * BAP];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
+      if (!sideY) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bdmma(accx[i][j], af[i], bf[j]);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bdmma(accy[i][j], af[i], bf[j]);
+      }
+    }
+  }
+  bwait<0>();
+  __syncthreads();                             // the pipeline buffers are free: the Gram fold reuses them
+
+  // ---- Gram blocks: entry (component c, which, l) = sum over the tile's rows of v_c * w_{start(c), l} --------------
+  // rows past n were zero-filled, so they add nothing
+  double* gsh = sm;                            // [4 row warps][FT_N components][3 R]
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      double g[3][R];
+#pragma unroll
+      for (int l = 0; l < R; ++l) { g[0][l] = 0.0; g[1][l] = 0.0; g[2][l] = 0.0; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const double xw = accx[i][j][e], yc = accy[i][j][e];
+#pragma unroll
+        for (int l = 0; l < R; ++l) {
+          double xl, yl;
+          if constexpr (R == 1) { xl = xw; yl = yc; }
+          else if constexpr (R == 2) { xl = accx[i][j][l]; yl = accy[i][j][l]; }
+          else {
+            const int c8 = 2 * tig + e, cl = c8 - (c8 % R) + l, src = (lane & ~3) | (cl >> 1);
+            const double x0 = __shfl_sync(0xffffffffu, accx[i][j][0], src), x1 = __shfl_sync(0xffffffffu, accx[i][j][1], src);
+            const double y0 = __shfl_sync(0xffffffffu, accy[i][j][0], src), y1 = __shfl_sync(0xffffffffu, accy[i][j][1], src);
+            xl = (cl & 1) ? x1 : x0; yl = (cl & 1) ? y1 : y0;
+          }
+          g[0][l] = fma(xw, xl, g[0][l]); g[1][l] = fma(xw, yl, g[1][l]); g[2][l] = fma(yc, yl, g[2][l]);
+        }
+      }
+#pragma unroll
+      for (int w = 0; w < 3; ++w)
+#pragma unroll
+        for (int l = 0; l < R; ++l) {
+          double v = g[w][l];
+          v += __shfl_xor_sync(0xffffffffu, v, 4);
+          v += __shfl_xor_sync(0xffffffffu, v, 8);
+          v += __shfl_xor_sync(0xffffffffu, v, 16);
+          if (gid == 0) gsh[((size_t)wr * FT_N + wn + j * 8 + 2 * tig + e) * 3 * R + w * R + l] = v;
+        }
+    }
+
+  // ---- mu_T, mu_U of the tile, straight from the accumulators --------------------------------------------------
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int c = cb * FT_N + wn + j * 8 + 2 * tig;
+    const double2 aT = *reinterpret_cast<const double2*>(a.coef + c), bT = *reinterpret_cast<const double2*>(a.coef + a.RP + c);
+    const double2 aU = *reinterpret_cast<const double2*>(a.coef + 2 * a.RP + c), bU = *reinterpret_cast<const double2*>(a.coef + 3 * a.RP + c);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t row = row0 + wm + i * 8 + gid;
+      if (row >= a.n) continue;
+      double* out = a.P + (size_t)row * 2 * a.RP + c;
+      const double x0 = accx[i][j][0], x1 = accx[i][j][1], y0 = accy[i][j][0], y1 = accy[i][j][1];
+      *reinterpret_cast<double2*>(out) = make_double2(aT.x * x0 + bT.x * y0, aT.y * x1 + bT.y * y1);
+      *reinterpret_cast<double2*>(out + a.RP) = make_double2(aU.x * x0 + bU.x * y0, aU.y * x1 + bU.y * y1);
+    }
+  }
+  __syncthreads();
+  // fold the 4 row warps in fixed order -> gpart[row tile][start][3][R*R]
+  for (int e = tid; e < FT_N * 3 * R; e += BTHREADS) {
+    const int cl = e / (3 * R), wl = e - cl * 3 * R, w = wl / R, l = wl - w * R;
+    const int c = cb * FT_N + cl, s = c / R, k = c - s * R;
+    if (s >= a.nstart) continue;
+    double t = 0.0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) t += gsh[((size_t)q * FT_N + cl) * 3 * R + wl];
+    a.gpart[((size_t)rt * a.nstart + s) * 3 * R * R + w * R * R + k * R + l] = t;
+  }
+}
+
 // ---- partial[split][tile] = D[:, col block]' mu_side[:, comp block] over the split's rows ----------------------
 struct AccArgs {
   const double* D; const double* MU; double* partial;
@@ -164,8 +320,9 @@ struct AccArgs {
   int ld, p2, q2, RP, nbx, nby, ncb;     // column blocks of X / Y (BT wide), comp blocks
   int unified;                           // 1: blocks run over the whole row [0, ld); a block may straddle the X|Y boundary
 };
+template <int NST>
 __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
-  extern __shared__ __align__(16) double sm[];    // [2 stages][2 operands][BK][BP] (+ [2 stages][BK][BP] of mu_U for a mixed block)
+  extern __shared__ __align__(16) double sm[];    // [NST stages][3 operands: D, mu, mu_U (mixed block only)][BK][BP]
   const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block
   // separate mode: X blocks, then Y blocks, each side padded to the tile.  unified mode (p2 % 8 == 0): blocks over
   // the whole row; in the block that straddles the X|Y boundary every 8-column DMMA tile still lies on one side,
@@ -189,8 +346,8 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
   const int nst = (r1 > r0) ? (int)((r1 - r0 + BK - 1) / BK) : 0;
 
   auto issue = [&](int s, int buf) {
-    double* As = sm + (size_t)(buf * 2 + 0) * BK * BP;
-    double* Bs = sm + (size_t)(buf * 2 + 1) * BK * BP;
+    double* As = sm + (size_t)(buf * 3 + 0) * BK * BP;
+    double* Bs = As + BK * BP;
 #pragma unroll
     for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {
       const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63;
@@ -199,9 +356,8 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
       const bool okA = rok && (col0 + pr * 2 < cend);
       bcp16(As + kk * BP + pr * 2, okA ? a.D + (size_t)grow * a.ld + col0 + pr * 2 : a.D, okA ? 16 : 0);
       bcp16(Bs + kk * BP + pr * 2, rok ? Bbase + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
-      if (mixed) bcp16(sm + (size_t)(4 + buf) * BK * BP + kk * BP + pr * 2, rok ? Bbase + a.RP + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
+      if (mixed) bcp16(Bs + BK * BP + kk * BP + pr * 2, rok ? Bbase + a.RP + (size_t)grow * 2 * a.RP + pr * 2 : a.D, rok ? 16 : 0);
     }
-    bcommit();
   };
   // per DMMA tile of this warp: does it take mu_U?  (bit i: data columns col0 + wm + 8 i .. + 7)
   unsigned ymask = 0;
@@ -212,11 +368,14 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
   for (int i = 0; i < 8; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
-  if (nst > 0) issue(0, 0);
+#pragma unroll
+  for (int s = 0; s < NST - 1; ++s) { if (s < nst) issue(s, s); bcommit(); }
   for (int s = 0; s < nst; ++s) {
-    if (s + 1 < nst) { issue(s + 1, (s + 1) & 1); bwait<1>(); } else bwait<0>();
-    __syncthreads();
-    const double* As = sm + (size_t)((s & 1) * 2 + 0) * BK * BP;
+    bwait<NST - 2>();                          // stage s has landed (one group is committed per stage slot)
+    __syncthreads();                           // ... for every thread; and everyone is done with stage s-1's buffer
+    if (s + NST - 1 < nst) issue(s + NST - 1, (s + NST - 1) % NST);
+    bcommit();
+    const double* As = sm + (size_t)((s % NST) * 3 + 0) * BK * BP;
     const double* Bs = As + BK * BP;
 #pragma unroll
     for (int k4 = 0; k4 < BK / 4; ++k4) {
@@ -233,7 +392,7 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], bf[j]);
       } else {
-        const double* bu = sm + (size_t)(4 + (s & 1)) * BK * BP + (k4 * 4 + tig) * BP + wn + gid;
+        const double* bu = Bs + BK * BP + (k4 * 4 + tig) * BP + wn + gid;
         double bg[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) bg[j] = bu[j * 8];
@@ -245,7 +404,6 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
         }
       }
     }
-    __syncthreads();
   }
   double* out = a.partial + ((size_t)blockIdx.y * gridDim.x + tile) * BT * BT;
 #pragma unroll
@@ -325,6 +483,10 @@ void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGe
   int64_t rpc = (s.n + nc - 1) / nc;
   p->nchunk = (int)((s.n + rpc - 1) / rpc);
   p->rows_per_chunk = rpc;
+  // fused projection + mu kernel (R divides 8): one Gram partial per row tile
+  const char* ef = getenv("PPLS_BATCH_FUSED");
+  p->fused = (8 % R == 0) && !(ef && *ef && atoi(ef) == 0);
+  if (p->fused) { p->nchunk = p->rowtiles; p->rows_per_chunk = BT; }
 }
 size_t bgemm_workspace_doubles(const DataShape& s, const BGemmPlan& p) {
   return (size_t)s.n * 2 * p.RP                                   // P / mu
@@ -338,15 +500,44 @@ static void launch_bmu(const MuArgs& m, const BGemmPlan& p, cudaStream_t stream)
   bmu_kernel<R><<<dim3((p.nstart + SW - 1) / SW, p.nchunk), 256, 0, stream>>>(m);
 }
 
+template <int R>
+static cudaError_t launch_bprojmu_r(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
+  const size_t smem = (size_t)FSTAGES * FSTAGE * sizeof(double);
+  cudaError_t e = cudaFuncSetAttribute((const void*)bprojmu_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  bprojmu_kernel<R><<<(unsigned)((size_t)(p.RP / FT_N) * p.rowtiles), BTHREADS, smem, stream>>>(fa);
+  return cudaGetLastError();
+}
+static cudaError_t launch_bprojmu(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
+  switch (p.R) {
+    case 1: return launch_bprojmu_r<1>(fa, p, stream);
+    case 2: return launch_bprojmu_r<2>(fa, p, stream);
+    case 4: return launch_bprojmu_r<4>(fa, p, stream);
+    case 8: return launch_bprojmu_r<8>(fa, p, stream);
+    default: return cudaErrorInvalidValue;
+  }
+}
+
 cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const double* D, const double* Lpack, const double* coef,
                               double* ws, double* momvec_pack, cudaStream_t stream) {
   double* P = ws;
   double* partial = P + (size_t)s.n * 2 * p.RP;
   double* gpart = partial + (size_t)p.nsplit * p.ntiles * BT * BT;
-  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double), smemB = (size_t)2 * 3 * BK * BP * sizeof(double);
+  const char* es = getenv("PPLS_BACC_STAGES");
+  const int nstg = (es && *es) ? atoi(es) : BACC_STAGES_DEFAULT;
+  if (nstg < 2 || nstg > 4) return cudaErrorInvalidValue;
+  const void* bacc = nstg == 2 ? (const void*)baccum_kernel<2> : nstg == 3 ? (const void*)baccum_kernel<3> : (const void*)baccum_kernel<4>;
+  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double), smemB = (size_t)nstg * 3 * BK * BP * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute((const void*)bproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute((const void*)baccum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemB);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(bacc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemB);
   if (e != cudaSuccess) return e;
+  if (p.fused) {
+    ProjMuArgs fa{};
+    fa.D = D; fa.L = Lpack; fa.coef = coef; fa.P = P; fa.gpart = gpart; fa.n = s.n;
+    fa.ld = s.ld; fa.p2 = s.p2; fa.q2 = s.q2; fa.RP = p.RP; fa.nstart = p.nstart;
+    e = launch_bprojmu(fa, p, stream);
+    if (e != cudaSuccess) return e;
+  } else {
   ProjArgs pa{};
   pa.D = D; pa.L = Lpack; pa.P = P; pa.n = s.n; pa.ld = s.ld; pa.p2 = s.p2; pa.q2 = s.q2; pa.RP = p.RP;
   bproj_kernel<<<dim3(p.rowtiles, p.ncb, 2), BTHREADS, smemA, stream>>>(pa);
@@ -363,10 +554,15 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
     case 8: launch_bmu<8>(m, p, stream); break;
     default: return cudaErrorInvalidValue;
   }
+  }
   AccArgs aa{};
   aa.D = D; aa.MU = P; aa.partial = partial; aa.n = s.n; aa.rows_per_split = p.rows_per_split;
   aa.ld = s.ld; aa.p2 = s.p2; aa.q2 = s.q2; aa.RP = p.RP; aa.nbx = p.nbx; aa.nby = p.nby; aa.ncb = p.ncb; aa.unified = p.unified;
-  baccum_kernel<<<dim3(p.ntiles, p.nsplit), BTHREADS, smemB, stream>>>(aa);
+  {
+    void* kargs[] = {(void*)&aa};
+    e = cudaLaunchKernel(bacc, dim3(p.ntiles, p.nsplit), dim3(BTHREADS), kargs, smemB, stream);
+    if (e != cudaSuccess) return e;
+  }
   FinArgs f{};
   f.partial = partial; f.gpart = gpart; f.momvec = momvec_pack; f.nsplit = p.nsplit; f.ntiles = p.ntiles; f.ncb = p.ncb;
   f.nbx = p.nbx; f.ld = s.ld; f.p2 = s.p2; f.RP = p.RP; f.R = p.R; f.nstart = p.nstart; f.nchunk = p.nchunk; f.unified = p.unified;

@@ -205,6 +205,39 @@ def test_batched_multistart_matches_single_runs(ctx, oracle_lib, shape, S, steps
     d.close()
 
 
+@pytest.mark.parametrize("shape,S", [((3001, 200, 50, 2), 64), ((1111, 50, 20, 1), 80), ((900, 136, 100, 4), 20), ((700, 300, 140, 8), 20)])
+@pytest.mark.parametrize("stages", ["2", "3", "4"])
+def test_batched_fused_projection_matches_unfused(ctx, shape, S, stages):
+    """em_batch.cu: the fused projection + posterior-mean + Gram kernel (r divides 8) against the separate
+    bproj/bmu kernels, for every cp.async depth of the accumulate GEMM: same EM trajectory up to rounding."""
+    import os
+    from ppls_b200 import Data, PPLS_simult_batched, synth
+    N, p, q, r = shape
+    truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
+    d = Data.synthetic(ctx, N, p, q, truth, seed=77)
+    inits = [synth.start_params(truth, seed=300 + s, noise=0.4 + 0.05 * s) for s in range(S)]
+    outs = {}
+    old = {k: os.environ.get(k) for k in ("PPLS_BATCH_FUSED", "PPLS_BACC_STAGES")}
+    try:
+        for fused in ("0", "1"):
+            os.environ["PPLS_BATCH_FUSED"] = fused
+            os.environ["PPLS_BACC_STAGES"] = stages if fused == "1" else "2"
+            outs[fused] = PPLS_simult_batched(None, None, r, inits, EMsteps=5, atol=-np.inf, data=d)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    for a, b in zip(outs["0"], outs["1"]):
+        assert a["steps"] == b["steps"]
+        assert relmax(b["loglik"], a["loglik"]) < 1e-12
+        for k in ("W", "C"):
+            assert relmax(b["loop_state"][k], a["loop_state"][k]) < 1e-10, k
+        assert relmax(np.diag(b["loop_state"]["B"]), np.diag(a["loop_state"]["B"])) < 1e-10
+    d.close()
+
+
 def test_column_sharded_two_gpus():
     """Column-sharded wide path over 2 ranks (one process per GPU, NCCL inside the library) vs the oracle;
     skipped on a 1-GPU box (tests/mgpu_colshard.py is the torchrun entry)."""
