@@ -137,6 +137,7 @@ struct BGemmPlan {
   int nsplit; int64_t rows_per_split;
   int nchunk; int64_t rows_per_chunk;
   int fused;                    // projection + mu + Gram blocks in one kernel (R divides 8): nchunk = rowtiles
+  int sm_count;
 };
 void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGemmPlan* p);
 size_t bgemm_workspace_doubles(const DataShape& s, const BGemmPlan& p);

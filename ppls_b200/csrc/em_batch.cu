@@ -19,6 +19,7 @@ namespace ppls {
 constexpr int BT = 128;         // tile edge
 constexpr int BK = 16;          // K per stage
 constexpr int BTHREADS = 256;
+constexpr int BACC_WAVES_DEFAULT = 1;     // least number of waves (one CTA per SM) the accumulate GEMM's row splits fill (PPLS_BACC_WAVES)
 constexpr int BACC_STAGES_DEFAULT = 3;   // cp.async stages of the accumulate GEMM (PPLS_BACC_STAGES=2..4 overrides)
 constexpr int BAP = BK + 4;     // pitch of the row-major A tile of bproj: 4 consecutive rows -> disjoint banks
 constexpr int BP = BT + 4;      // pitch of the k-major tiles: 4 consecutive k-rows -> disjoint banks
@@ -31,8 +32,49 @@ __device__ __forceinline__ void bcommit() { asm volatile("cp.async.commit_group;
 __device__ __forceinline__ void bdmma(double (&c)[2], double a, double b) {   // lane l: A[l>>2][l&3], B[l&3][l>>2], C[l>>2][2(l&3)+{0,1}]
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c[0]), "+d"(c[1]) : "d"(a), "d"(b));
 }
+// m16n8k16: rows {gid, gid+8} x k {tig, tig+4, tig+8, tig+12} -- the same lane mapping as eight m8n8k4 (two row tiles x four
+// k-steps); one statement per K = 16 stage (ptxas for sm_100a expands it to eight DMMA.8x8x4, the only FP64 tensor
+// instruction of the part, so the rate is the same).  a[v]: row gid + 8 (v & 1), k = tig + 4 (v >> 1);
+// b[v]: k = tig + 4 v, n = gid; c: {row gid: cols 2 tig, 2 tig + 1; row gid + 8: the same}.
+__device__ __forceinline__ void bdmma16(double (&c0)[2], double (&c1)[2], const double (&a)[8], const double (&b)[4]) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7,%8,%9,%10,%11}, {%12,%13,%14,%15}, {%0,%1,%2,%3};"
+               : "+d"(c0[0]), "+d"(c0[1]), "+d"(c1[0]), "+d"(c1[1])
+               : "d"(a[0]), "d"(a[1]), "d"(a[2]), "d"(a[3]), "d"(a[4]), "d"(a[5]), "d"(a[6]), "d"(a[7]),
+                 "d"(b[0]), "d"(b[1]), "d"(b[2]), "d"(b[3]));
+}
 template <int N>
 __device__ __forceinline__ void bwait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Warp-specialised form of the two GEMM kernels (WS = true): 8 consumer warps (fragments + DMMA only) and a
+// PRODUCER warpgroup (4 warps) that issues every cp.async of a stage; hand-offs through mbarriers -- full[slot] completes when the
+// producer lanes' copies have landed (cp.async.mbarrier.arrive.noinc, one arrival per lane), empty[slot] when the 8
+// consumer warps have multiplied the stage.  No CTA-wide barrier and no address arithmetic in the consumers' loop:
+// ncu of the __syncthreads form showed the DMMA pipe 60-74 % busy, every warp doing the copies' integer work at the
+// same time right after each barrier.
+constexpr int WS_THREADS = BTHREADS + 128;   // consumers = warpgroups 0, 1; producers = warpgroup 2
+// register budget per warpgroup (setmaxnreg works on whole warpgroups): 256 x 224 + 128 x 56 = 64512 <= 65536
+__device__ __forceinline__ void breg_consumer() { asm volatile("setmaxnreg.inc.sync.aligned.u32 224;" ::: "memory"); }
+__device__ __forceinline__ void breg_producer() { asm volatile("setmaxnreg.dec.sync.aligned.u32 56;" ::: "memory"); }
+__device__ __forceinline__ uint32_t bsm32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bbar_arrive_cpasync(uint32_t bar) {      // arrives when this thread's earlier cp.async have landed
+  asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void bbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  } while (!ok);
+}
 
 // ---- P[row][side*RP + c] = sum_j D[row][c0 + j] * L[c0 + j][c]   (side 0: X columns, side 1: Y columns) -------
 struct ProjArgs {
@@ -173,143 +215,176 @@ constexpr int FSTAGE = BT * BAP + BK * FBP;
 struct ProjMuArgs {
   const double* D; const double* L; const double* coef; double* P; double* gpart;
   int64_t n;
-  int ld, p2, q2, RP, nstart;
+  int ld, p2, q2, RP, nstart, rowtiles;
+  int dbg;                       // timing experiments only (PPLS_BGEMM_DBG): 1 = no copies, 2 = no DMMA
 };
 template <int R>
-__global__ void __launch_bounds__(BTHREADS, 1) bprojmu_kernel(const ProjMuArgs a) {
+__global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs a) {
   static_assert(8 % R == 0, "a start must not straddle a DMMA tile");
-  extern __shared__ __align__(16) double sm[];    // [FSTAGES][ A: BT x BAP | B: BK x FBP ]; reused by the Gram fold
+  static_assert(BK == 16, "one m16n8k16 step per stage");
+  static_assert(4 * FT_N == BTHREADS, "one coefficient per consumer thread");
+  extern __shared__ __align__(16) double sm[];    // [FSTAGES][ A: BT x BAP | B: BK x FBP ] | gsh [4][FT_N][3 R] | coef [4][FT_N] | mbarriers
   const int ncb2 = a.RP / FT_N;
-  const int cb = blockIdx.x % ncb2;               // component block (fastest: the CTAs sharing a row tile run together)
-  const int64_t rt = blockIdx.x / ncb2, row0 = rt * BT;
+  const int64_t ntile = (int64_t)ncb2 * a.rowtiles;               // tile t = (row tile t / ncb2, component block t % ncb2)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
   const int wr = warp >> 1, wm = wr * 32, wn = (warp & 1) * 32;  // this warp's rows / components of the tile
   const int nsX = (a.p2 + BK - 1) / BK, nsY = (a.q2 + BK - 1) / BK, nst = nsX + nsY;
-
-  auto issue = [&](int s, int buf) {
-    double* As = sm + (size_t)buf * FSTAGE;
-    double* Bs = As + BT * BAP;
-    const bool sideY = s >= nsX;
-    const int c0 = sideY ? a.p2 : 0, K = sideY ? a.q2 : a.p2, k0 = (sideY ? s - nsX : s) * BK;
-#pragma unroll
-    for (int c = 0; c < (BT * BK / 2) / BTHREADS; ++c) {          // A: 128 rows x 8 chunks of 2 columns
-      const int chunk = tid + c * BTHREADS, r = chunk >> 3, kc = (chunk & 7) * 2;
-      const bool ok = (row0 + r < a.n) && (k0 + kc < K);
-      bcp16(As + r * BAP + kc, ok ? a.D + (size_t)(row0 + r) * a.ld + c0 + k0 + kc : a.D, ok ? 16 : 0);
-    }
-#pragma unroll
-    for (int c = 0; c < (BK * FT_N / 2) / BTHREADS; ++c) {        // B: 16 k x 32 pairs of components
-      const int chunk = tid + c * BTHREADS, kk = chunk >> 5, pr = chunk & 31;
-      const bool ok = k0 + kk < K;
-      bcp16(Bs + kk * FBP + pr * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * FT_N + pr * 2 : a.L, ok ? 16 : 0);
-    }
-  };
-
-  double accx[4][4][2], accy[4][4][2];
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-#pragma unroll
-    for (int j = 0; j < 4; ++j) { accx[i][j][0] = 0.0; accx[i][j][1] = 0.0; accy[i][j][0] = 0.0; accy[i][j][1] = 0.0; }
-#pragma unroll
-  for (int s = 0; s < FSTAGES - 1; ++s) { if (s < nst) issue(s, s); bcommit(); }
-  for (int s = 0; s < nst; ++s) {
-    bwait<FSTAGES - 2>();                      // stage s has landed (one group is committed per stage slot)
-    __syncthreads();                           // ... for every thread; and everyone is done with stage s-1's buffer
-    if (s + FSTAGES - 1 < nst) issue(s + FSTAGES - 1, (s + FSTAGES - 1) % FSTAGES);
-    bcommit();
-    const double* As = sm + (size_t)(s % FSTAGES) * FSTAGE;
-    const double* Bs = As + BT * BAP;
-    const bool sideY = s >= nsX;
-#pragma unroll
-    for (int k4 = 0; k4 < BK / 4; ++k4) {
-      const double* ar = As + (wm + gid) * BAP + k4 * 4 + tig;      // A[m = row][k = data column]
-      const double* br = Bs + (k4 * 4 + tig) * FBP + wn + gid;      // B[k][n = component]
-      double af[4], bf[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) af[i] = ar[i * 8 * BAP];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
-      if (!sideY) {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) bdmma(accx[i][j], af[i], bf[j]);
-      } else {
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int j = 0; j < 4; ++j) bdmma(accy[i][j], af[i], bf[j]);
-      }
-    }
-  }
-  bwait<0>();
-  __syncthreads();                             // the pipeline buffers are free: the Gram fold reuses them
-
-  // ---- Gram blocks: entry (component c, which, l) = sum over the tile's rows of v_c * w_{start(c), l} --------------
-  // rows past n were zero-filled, so they add nothing
-  double* gsh = sm;                            // [4 row warps][FT_N components][3 R]
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      double g[3][R];
-#pragma unroll
-      for (int l = 0; l < R; ++l) { g[0][l] = 0.0; g[1][l] = 0.0; g[2][l] = 0.0; }
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const double xw = accx[i][j][e], yc = accy[i][j][e];
-#pragma unroll
-        for (int l = 0; l < R; ++l) {
-          double xl, yl;
-          if constexpr (R == 1) { xl = xw; yl = yc; }
-          else if constexpr (R == 2) { xl = accx[i][j][l]; yl = accy[i][j][l]; }
-          else {
-            const int c8 = 2 * tig + e, cl = c8 - (c8 % R) + l, src = (lane & ~3) | (cl >> 1);
-            const double x0 = __shfl_sync(0xffffffffu, accx[i][j][0], src), x1 = __shfl_sync(0xffffffffu, accx[i][j][1], src);
-            const double y0 = __shfl_sync(0xffffffffu, accy[i][j][0], src), y1 = __shfl_sync(0xffffffffu, accy[i][j][1], src);
-            xl = (cl & 1) ? x1 : x0; yl = (cl & 1) ? y1 : y0;
-          }
-          g[0][l] = fma(xw, xl, g[0][l]); g[1][l] = fma(xw, yl, g[1][l]); g[2][l] = fma(yc, yl, g[2][l]);
-        }
-      }
-#pragma unroll
-      for (int w = 0; w < 3; ++w)
-#pragma unroll
-        for (int l = 0; l < R; ++l) {
-          double v = g[w][l];
-          v += __shfl_xor_sync(0xffffffffu, v, 4);
-          v += __shfl_xor_sync(0xffffffffu, v, 8);
-          v += __shfl_xor_sync(0xffffffffu, v, 16);
-          if (gid == 0) gsh[((size_t)wr * FT_N + wn + j * 8 + 2 * tig + e) * 3 * R + w * R + l] = v;
-        }
-    }
-
-  // ---- mu_T, mu_U of the tile, straight from the accumulators --------------------------------------------------
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const int c = cb * FT_N + wn + j * 8 + 2 * tig;
-    const double2 aT = *reinterpret_cast<const double2*>(a.coef + c), bT = *reinterpret_cast<const double2*>(a.coef + a.RP + c);
-    const double2 aU = *reinterpret_cast<const double2*>(a.coef + 2 * a.RP + c), bU = *reinterpret_cast<const double2*>(a.coef + 3 * a.RP + c);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int64_t row = row0 + wm + i * 8 + gid;
-      if (row >= a.n) continue;
-      double* out = a.P + (size_t)row * 2 * a.RP + c;
-      const double x0 = accx[i][j][0], x1 = accx[i][j][1], y0 = accy[i][j][0], y1 = accy[i][j][1];
-      *reinterpret_cast<double2*>(out) = make_double2(aT.x * x0 + bT.x * y0, aT.y * x1 + bT.y * y1);
-      *reinterpret_cast<double2*>(out + a.RP) = make_double2(aU.x * x0 + bU.x * y0, aU.y * x1 + bU.y * y1);
-    }
+  double* gsh = sm + (size_t)FSTAGES * FSTAGE;                    // Gram fold buffer (not the ring: the producer runs ahead)
+  double* csh = gsh + 4 * FT_N * 3 * R;                           // coefficients aT, bT, aU, bU of the tile's components
+  const uint32_t bars = bsm32(csh + 4 * FT_N);                    // full[FSTAGES], empty[FSTAGES]
+  if (tid == 0) {
+    for (int b = 0; b < FSTAGES; ++b) { bbar_init(bars + 8u * b, 128); bbar_init(bars + 8u * (FSTAGES + b), BTHREADS / 32); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  // fold the 4 row warps in fixed order -> gpart[row tile][start][3][R*R]
-  for (int e = tid; e < FT_N * 3 * R; e += BTHREADS) {
-    const int cl = e / (3 * R), wl = e - cl * 3 * R, w = wl / R, l = wl - w * R;
-    const int c = cb * FT_N + cl, s = c / R, k = c - s * R;
-    if (s >= a.nstart) continue;
-    double t = 0.0;
+
+  if (warp >= BTHREADS / 32) {
+    // ================================ producer warpgroup (warps 8..11) ================================
+    // One continuous stream of stages over all of this CTA's tiles: the copies of the next tile are in flight while
+    // the consumers run the epilogue of the current one.
+    breg_producer();
+    const int ctid = tid - BTHREADS;
+    uint32_t g = 0;                                               // stages issued so far
+    for (int64_t t = blockIdx.x; t < ntile; t += gridDim.x) {
+      const int cb = (int)(t % ncb2);
+      const int64_t row0 = (t / ncb2) * BT;
+      for (int s = 0; s < nst; ++s, ++g) {
+        const uint32_t slot = g % FSTAGES;
+        if (g >= FSTAGES) bbar_wait(bars + 8u * (FSTAGES + slot), (g / FSTAGES - 1u) & 1u);
+        double* As = sm + (size_t)slot * FSTAGE;
+        double* Bs = As + BT * BAP;
+        const bool sideY = s >= nsX;
+        const int c0 = sideY ? a.p2 : 0, K = sideY ? a.q2 : a.p2, k0 = (sideY ? s - nsX : s) * BK;
+        if (a.dbg != 1) {
+#pragma unroll 4
+        for (int c = 0; c < (BT * BK / 2) / 128; ++c) {           // A: 128 rows x 8 chunks of 2 columns
+          const int chunk = ctid + c * 128, r = chunk >> 3, kc = (chunk & 7) * 2;
+          const bool ok = (row0 + r < a.n) && (k0 + kc < K);
+          bcp16(As + r * BAP + kc, ok ? a.D + (size_t)(row0 + r) * a.ld + c0 + k0 + kc : a.D, ok ? 16 : 0);
+        }
+#pragma unroll 4
+        for (int c = 0; c < (BK * FT_N / 2) / 128; ++c) {         // B: 16 k x 32 pairs of components
+          const int chunk = ctid + c * 128, kk = chunk >> 5, pr = chunk & 31;
+          const bool ok = k0 + kk < K;
+          bcp16(Bs + kk * FBP + pr * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * FT_N + pr * 2 : a.L, ok ? 16 : 0);
+        }
+        }
+        bbar_arrive_cpasync(bars + 8u * slot);
+      }
+    }
+    bwait<0>();
+    return;
+  }
+
+  // ==================================== consumer warps 0..7 ========================================
+  breg_consumer();
+  auto csync = [&]() { asm volatile("bar.sync 1, 256;" ::: "memory"); };   // the 256 consumer threads
+  uint32_t g = 0;                                                 // stages consumed so far
+  for (int64_t t = blockIdx.x; t < ntile; t += gridDim.x) {
+    const int cb = (int)(t % ncb2);
+    const int64_t rt = t / ncb2, row0 = rt * BT;
+    // (read after the barrier that follows the K loop; the previous tile's readers are past its second barrier)
+    csh[tid] = a.coef[(size_t)(tid / FT_N) * a.RP + cb * FT_N + (tid % FT_N)];
+    double accx[4][4][2], accy[4][4][2];
 #pragma unroll
-    for (int q = 0; q < 4; ++q) t += gsh[((size_t)q * FT_N + cl) * 3 * R + wl];
-    a.gpart[((size_t)rt * a.nstart + s) * 3 * R * R + w * R * R + k * R + l] = t;
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { accx[i][j][0] = 0.0; accx[i][j][1] = 0.0; accy[i][j][0] = 0.0; accy[i][j][1] = 0.0; }
+    for (int s = 0; s < nst; ++s, ++g) {
+      const uint32_t slot = g % FSTAGES;
+      bbar_wait(bars + 8u * slot, (g / FSTAGES) & 1u);
+      const double* As = sm + (size_t)slot * FSTAGE;
+      const double* ar = As + (wm + gid) * BAP + tig;               // A[m = row][k = data column]
+      const double* br = As + BT * BAP + tig * FBP + wn + gid;      // B[k][n = component]
+      double bf[4][4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int v = 0; v < 4; ++v) bf[j][v] = br[v * 4 * FBP + j * 8];
+      if (a.dbg != 2)
+#pragma unroll
+      for (int ip = 0; ip < 2; ++ip) {                              // row tiles 2 ip, 2 ip + 1
+        double af[8];
+#pragma unroll
+        for (int v = 0; v < 8; ++v) af[v] = ar[(2 * ip + (v & 1)) * 8 * BAP + (v >> 1) * 4];
+        if (s < nsX) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bdmma16(accx[2 * ip][j], accx[2 * ip + 1][j], af, bf[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bdmma16(accy[2 * ip][j], accy[2 * ip + 1][j], af, bf[j]);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) bbar_arrive(bars + 8u * (FSTAGES + slot));
+    }
+    csync();                                   // the fold of the previous tile has read gsh
+
+    // ---- Gram blocks: entry (component c, which, l) = sum over the tile's rows of v_c * w_{start(c), l} ------------
+    // rows past n were zero-filled, so they add nothing
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        double gg[3][R];
+#pragma unroll
+        for (int l = 0; l < R; ++l) { gg[0][l] = 0.0; gg[1][l] = 0.0; gg[2][l] = 0.0; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const double xw = accx[i][j][e], yc = accy[i][j][e];
+#pragma unroll
+          for (int l = 0; l < R; ++l) {
+            double xl, yl;
+            if constexpr (R == 1) { xl = xw; yl = yc; }
+            else if constexpr (R == 2) { xl = accx[i][j][l]; yl = accy[i][j][l]; }
+            else {
+              const int c8 = 2 * tig + e, cl = c8 - (c8 % R) + l, src = (lane & ~3) | (cl >> 1);
+              const double x0 = __shfl_sync(0xffffffffu, accx[i][j][0], src), x1 = __shfl_sync(0xffffffffu, accx[i][j][1], src);
+              const double y0 = __shfl_sync(0xffffffffu, accy[i][j][0], src), y1 = __shfl_sync(0xffffffffu, accy[i][j][1], src);
+              xl = (cl & 1) ? x1 : x0; yl = (cl & 1) ? y1 : y0;
+            }
+            gg[0][l] = fma(xw, xl, gg[0][l]); gg[1][l] = fma(xw, yl, gg[1][l]); gg[2][l] = fma(yc, yl, gg[2][l]);
+          }
+        }
+#pragma unroll
+        for (int w = 0; w < 3; ++w)
+#pragma unroll
+          for (int l = 0; l < R; ++l) {
+            double v = gg[w][l];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (gid == 0) gsh[((size_t)wr * FT_N + wn + j * 8 + 2 * tig + e) * 3 * R + w * R + l] = v;
+          }
+      }
+
+    // ---- mu_T, mu_U of the tile, straight from the accumulators ------------------------------------------------
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int cl = wn + j * 8 + 2 * tig, c = cb * FT_N + cl;
+      const double2 aT = *reinterpret_cast<const double2*>(csh + cl), bT = *reinterpret_cast<const double2*>(csh + FT_N + cl);
+      const double2 aU = *reinterpret_cast<const double2*>(csh + 2 * FT_N + cl), bU = *reinterpret_cast<const double2*>(csh + 3 * FT_N + cl);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t row = row0 + wm + i * 8 + gid;
+        if (row >= a.n) continue;
+        double* out = a.P + (size_t)row * 2 * a.RP + c;
+        const double x0 = accx[i][j][0], x1 = accx[i][j][1], y0 = accy[i][j][0], y1 = accy[i][j][1];
+        *reinterpret_cast<double2*>(out) = make_double2(aT.x * x0 + bT.x * y0, aT.y * x1 + bT.y * y1);
+        *reinterpret_cast<double2*>(out + a.RP) = make_double2(aU.x * x0 + bU.x * y0, aU.y * x1 + bU.y * y1);
+      }
+    }
+    csync();
+    // fold the 4 row warps in fixed order -> gpart[row tile][start][3][R*R]
+    for (int e = tid; e < FT_N * 3 * R; e += BTHREADS) {
+      const int cl = e / (3 * R), wl = e - cl * 3 * R, w = wl / R, l = wl - w * R;
+      const int c = cb * FT_N + cl, st = c / R, k = c - st * R;
+      if (st >= a.nstart) continue;
+      double tsum = 0.0;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) tsum += gsh[((size_t)q * FT_N + cl) * 3 * R + wl];
+      a.gpart[((size_t)rt * a.nstart + st) * 3 * R * R + w * R * R + k * R + l] = tsum;
+    }
   }
 }
 
@@ -319,9 +394,10 @@ struct AccArgs {
   int64_t n, rows_per_split;
   int ld, p2, q2, RP, nbx, nby, ncb;     // column blocks of X / Y (BT wide), comp blocks
   int unified;                           // 1: blocks run over the whole row [0, ld); a block may straddle the X|Y boundary
+  int dbg;                               // timing experiments only (PPLS_BGEMM_DBG): 1 = no copies, 2 = no DMMA
 };
-template <int NST>
-__global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
+template <int NST, bool WS>
+__global__ void __launch_bounds__(WS ? WS_THREADS : BTHREADS, 1) baccum_kernel(const AccArgs a) {
   extern __shared__ __align__(16) double sm[];    // [NST stages][3 operands: D, mu, mu_U (mixed block only)][BK][BP]
   const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block
   // separate mode: X blocks, then Y blocks, each side padded to the tile.  unified mode (p2 % 8 == 0): blocks over
@@ -345,12 +421,14 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
   const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;         // this warp's data columns / components of the tile
   const int nst = (r1 > r0) ? (int)((r1 - r0 + BK - 1) / BK) : 0;
 
+  constexpr int NCOPY = WS ? 128 : BTHREADS;        // threads that issue the copies of a stage
+  const int ctid = WS ? tid - BTHREADS : tid;
   auto issue = [&](int s, int buf) {
     double* As = sm + (size_t)(buf * 3 + 0) * BK * BP;
     double* Bs = As + BK * BP;
-#pragma unroll
-    for (int c = 0; c < (BK * BT / 2) / BTHREADS; ++c) {
-      const int chunk = tid + c * BTHREADS, kk = chunk >> 6, pr = chunk & 63;
+#pragma unroll 4
+    for (int c = 0; c < (BK * BT / 2) / NCOPY; ++c) {
+      const int chunk = ctid + c * NCOPY, kk = chunk >> 6, pr = chunk & 63;
       const int64_t grow = r0 + (int64_t)s * BK + kk;
       const bool rok = grow < r1;
       const bool okA = rok && (col0 + pr * 2 < cend);
@@ -363,46 +441,108 @@ __global__ void __launch_bounds__(BTHREADS, 1) baccum_kernel(const AccArgs a) {
   unsigned ymask = 0;
   if (mixed)
     for (int i = 0; i < 8; ++i) if (col0 + wm + i * 8 >= a.p2) ymask |= 1u << i;
+  [[maybe_unused]] uint32_t bars = 0;                                // WS: full[NST], empty[NST]
+  if constexpr (WS) {
+    bars = bsm32(sm + (size_t)NST * 3 * BK * BP);
+    if (tid == 0) {
+      for (int b = 0; b < NST; ++b) { bbar_init(bars + 8u * b, 128); bbar_init(bars + 8u * (NST + b), BTHREADS / 32); }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp >= BTHREADS / 32) {                                    // ---- producer warpgroup (warps 8..11)
+      breg_producer();
+      for (int s = 0; s < nst; ++s) {
+        const int slot = s % NST;
+        if (s >= NST) bbar_wait(bars + 8u * (NST + slot), (uint32_t)(s / NST - 1) & 1u);
+        if (a.dbg != 1) issue(s, slot);
+        bbar_arrive_cpasync(bars + 8u * slot);
+      }
+      bwait<0>();
+      return;
+    }
+    breg_consumer();
+  }
   double acc[8][4][2];
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
-#pragma unroll
-  for (int s = 0; s < NST - 1; ++s) { if (s < nst) issue(s, s); bcommit(); }
-  for (int s = 0; s < nst; ++s) {
-    bwait<NST - 2>();                          // stage s has landed (one group is committed per stage slot)
-    __syncthreads();                           // ... for every thread; and everyone is done with stage s-1's buffer
-    if (s + NST - 1 < nst) issue(s + NST - 1, (s + NST - 1) % NST);
-    bcommit();
+  auto multiply = [&](int s) {
+    static_assert(BK == 16, "one m16n8k16 step per stage");
     const double* As = sm + (size_t)((s % NST) * 3 + 0) * BK * BP;
-    const double* Bs = As + BK * BP;
+    const double* ar = As + tig * BP + wm + gid;                    // A[m = data column][k = row]
+    const double* br = As + BK * BP + tig * BP + wn + gid;          // B[k = row][n = component]
+    const bool uniform = (ymask == 0u || ymask == 0xffu);           // all of this warp's columns on one side
+    if (ymask == 0xffu) br += BK * BP;
+    double bf[4][4];
 #pragma unroll
-    for (int k4 = 0; k4 < BK / 4; ++k4) {
-      const double* ar = As + (k4 * 4 + tig) * BP + wm + gid;       // A[m = data column][k = row]
-      const double* br = Bs + (k4 * 4 + tig) * BP + wn + gid;       // B[k = row][n = component]
-      double af[8], bf[4];
+    for (int j = 0; j < 4; ++j)
 #pragma unroll
-      for (int i = 0; i < 8; ++i) af[i] = ar[i * 8];
+      for (int v = 0; v < 4; ++v) bf[j][v] = br[v * 4 * BP + j * 8];
+    if (uniform) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) bf[j] = br[j * 8];
-      if (!mixed) {
+      for (int ip = 0; ip < 4; ++ip) {                              // column tiles 2 ip, 2 ip + 1
+        double af[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int v = 0; v < 8; ++v) af[v] = ar[(v >> 1) * 4 * BP + (2 * ip + (v & 1)) * 8];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], bf[j]);
-      } else {
-        const double* bu = Bs + BK * BP + (k4 * 4 + tig) * BP + wn + gid;
-        double bg[4];
+        for (int j = 0; j < 4; ++j) bdmma16(acc[2 * ip][j], acc[2 * ip + 1][j], af, bf[j]);
+      }
+    } else {
+      // the X|Y boundary runs through this warp's columns: every 8-column tile still lies on one side; a tile on the
+      // other side than its partner gets zeros in the partner's A rows of the other product
 #pragma unroll
-        for (int j = 0; j < 4; ++j) bg[j] = bu[j * 8];
+      for (int ip = 0; ip < 4; ++ip) {
+        const bool y0 = (ymask >> (2 * ip)) & 1u, y1 = (ymask >> (2 * ip + 1)) & 1u;
+        double af[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const bool y = (ymask >> i) & 1u;
+        for (int v = 0; v < 8; ++v) af[v] = ar[(v >> 1) * 4 * BP + (2 * ip + (v & 1)) * 8];
+        if (y0 == y1) {
+          if (!y0) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) bdmma(acc[i][j], af[i], y ? bg[j] : bf[j]);
+            for (int j = 0; j < 4; ++j) bdmma16(acc[2 * ip][j], acc[2 * ip + 1][j], af, bf[j]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              double bg[4];
+#pragma unroll
+              for (int v = 0; v < 4; ++v) bg[v] = br[BK * BP + v * 4 * BP + j * 8];
+              bdmma16(acc[2 * ip][j], acc[2 * ip + 1][j], af, bg);
+            }
+          }
+        } else {                                                    // (ymask is monotone: tile 2 ip on X, 2 ip + 1 on Y)
+          double ax[8], ay[8];
+#pragma unroll
+          for (int v = 0; v < 8; ++v) { ax[v] = (v & 1) ? 0.0 : af[v]; ay[v] = (v & 1) ? af[v] : 0.0; }
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            double bg[4];
+#pragma unroll
+            for (int v = 0; v < 4; ++v) bg[v] = br[BK * BP + v * 4 * BP + j * 8];
+            bdmma16(acc[2 * ip][j], acc[2 * ip + 1][j], ax, bf[j]);
+            bdmma16(acc[2 * ip][j], acc[2 * ip + 1][j], ay, bg);
+          }
         }
       }
+    }
+  };
+  if constexpr (WS) {
+    for (int s = 0; s < nst; ++s) {
+      const int slot = s % NST;
+      bbar_wait(bars + 8u * slot, (uint32_t)(s / NST) & 1u);
+      if (a.dbg != 2) multiply(s);
+      __syncwarp();
+      if (lane == 0) bbar_arrive(bars + 8u * (NST + slot));
+    }
+  } else {
+#pragma unroll
+    for (int s = 0; s < NST - 1; ++s) { if (s < nst) issue(s, s); bcommit(); }
+    for (int s = 0; s < nst; ++s) {
+      bwait<NST - 2>();                        // stage s has landed (one group is committed per stage slot)
+      __syncthreads();                         // ... for every thread; and everyone is done with stage s-1's buffer
+      if (s + NST - 1 < nst) issue(s + NST - 1, (s + NST - 1) % NST);
+      bcommit();
+      multiply(s);
     }
   }
   double* out = a.partial + ((size_t)blockIdx.y * gridDim.x + tile) * BT * BT;
@@ -452,7 +592,7 @@ __global__ void __launch_bounds__(256) bfinal_kernel(const FinArgs a) {
 
 // ---- host side ---------------------------------------------------------------------------------------------------
 void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGemmPlan* p) {
-  p->RP = RP; p->R = R; p->nstart = nstart;
+  p->RP = RP; p->R = R; p->nstart = nstart; p->sm_count = sm_count;
   p->ncb = RP / BT;
   p->nbx = (s.p2 + BT - 1) / BT; p->nby = (s.q2 + BT - 1) / BT;
   p->unified = (s.p2 % 8 == 0) && ((s.ld + BT - 1) / BT < p->nbx + p->nby);
@@ -460,7 +600,9 @@ void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGe
   p->rowtiles = (int)((s.n + BT - 1) / BT);
   // accumulate GEMM: row splits so that tiles x splits fills whole waves of one CTA per SM
   const int64_t max_ns = (s.n + 8 * BK - 1) / (8 * BK);
-  int64_t lo = (4 * (int64_t)sm_count + p->ntiles - 1) / p->ntiles, ns = 1;
+  const char* ew = getenv("PPLS_BACC_WAVES");
+  const int waves_min = (ew && *ew && atoi(ew) > 0) ? atoi(ew) : BACC_WAVES_DEFAULT;
+  int64_t lo = (waves_min * (int64_t)sm_count + p->ntiles - 1) / p->ntiles, ns = 1;
   double best = -1.0;
   for (int64_t c = lo < 1 ? 1 : lo; c < lo + 64; ++c) {
     const int64_t cc = c > max_ns ? max_ns : c;
@@ -500,12 +642,22 @@ static void launch_bmu(const MuArgs& m, const BGemmPlan& p, cudaStream_t stream)
   bmu_kernel<R><<<dim3((p.nstart + SW - 1) / SW, p.nchunk), 256, 0, stream>>>(m);
 }
 
+// PPLS_BGEMM_WS=0: the __syncthreads form of the two GEMM kernels (kept for comparison); default: warp-specialised
+static int bgemm_ws() {
+  const char* e = getenv("PPLS_BGEMM_WS");
+  return (e && *e) ? (atoi(e) != 0) : 1;
+}
 template <int R>
 static cudaError_t launch_bprojmu_r(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
-  const size_t smem = (size_t)FSTAGES * FSTAGE * sizeof(double);
+  const size_t smem = ((size_t)FSTAGES * FSTAGE + 4 * FT_N * 3 * R + 4 * FT_N + 2 * FSTAGES) * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute((const void*)bprojmu_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  bprojmu_kernel<R><<<(unsigned)((size_t)(p.RP / FT_N) * p.rowtiles), BTHREADS, smem, stream>>>(fa);
+  // persistent: one CTA per SM walks the (row tile, component block) tiles; PPLS_BPROJ_PERSIST=0: one CTA per tile
+  const char* ep = getenv("PPLS_BPROJ_PERSIST");
+  const size_t ntile = (size_t)(p.RP / FT_N) * p.rowtiles;
+  size_t grid = ntile;
+  if (!(ep && *ep && atoi(ep) == 0) && p.sm_count > 0 && grid > (size_t)p.sm_count) grid = (size_t)p.sm_count;
+  bprojmu_kernel<R><<<(unsigned)grid, WS_THREADS, smem, stream>>>(fa);
   return cudaGetLastError();
 }
 static cudaError_t launch_bprojmu(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
@@ -526,15 +678,21 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
   const char* es = getenv("PPLS_BACC_STAGES");
   const int nstg = (es && *es) ? atoi(es) : BACC_STAGES_DEFAULT;
   if (nstg < 2 || nstg > 4) return cudaErrorInvalidValue;
-  const void* bacc = nstg == 2 ? (const void*)baccum_kernel<2> : nstg == 3 ? (const void*)baccum_kernel<3> : (const void*)baccum_kernel<4>;
-  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double), smemB = (size_t)nstg * 3 * BK * BP * sizeof(double);
+  const int wsp = bgemm_ws();
+  const void* bacc_tab[3][2] = {{(const void*)baccum_kernel<2, false>, (const void*)baccum_kernel<2, true>},
+                                {(const void*)baccum_kernel<3, false>, (const void*)baccum_kernel<3, true>},
+                                {(const void*)baccum_kernel<4, false>, (const void*)baccum_kernel<4, true>}};
+  const void* bacc = bacc_tab[nstg - 2][wsp];
+  const size_t smemA = (size_t)2 * (BT * BAP + BK * BP) * sizeof(double);
+  const size_t smemB = (size_t)nstg * 3 * BK * BP * sizeof(double) + (wsp ? 2 * nstg * 8 : 0);
   cudaError_t e = cudaFuncSetAttribute((const void*)bproj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemA);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(bacc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemB);
   if (e != cudaSuccess) return e;
   if (p.fused) {
     ProjMuArgs fa{};
     fa.D = D; fa.L = Lpack; fa.coef = coef; fa.P = P; fa.gpart = gpart; fa.n = s.n;
-    fa.ld = s.ld; fa.p2 = s.p2; fa.q2 = s.q2; fa.RP = p.RP; fa.nstart = p.nstart;
+    fa.ld = s.ld; fa.p2 = s.p2; fa.q2 = s.q2; fa.RP = p.RP; fa.nstart = p.nstart; fa.rowtiles = p.rowtiles;
+    { const char* ed = getenv("PPLS_BGEMM_DBG"); fa.dbg = (ed && *ed) ? atoi(ed) : 0; }
     e = launch_bprojmu(fa, p, stream);
     if (e != cudaSuccess) return e;
   } else {
@@ -558,9 +716,10 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
   AccArgs aa{};
   aa.D = D; aa.MU = P; aa.partial = partial; aa.n = s.n; aa.rows_per_split = p.rows_per_split;
   aa.ld = s.ld; aa.p2 = s.p2; aa.q2 = s.q2; aa.RP = p.RP; aa.nbx = p.nbx; aa.nby = p.nby; aa.ncb = p.ncb; aa.unified = p.unified;
+  { const char* ed = getenv("PPLS_BGEMM_DBG"); aa.dbg = (ed && *ed) ? atoi(ed) : 0; }
   {
     void* kargs[] = {(void*)&aa};
-    e = cudaLaunchKernel(bacc, dim3(p.ntiles, p.nsplit), dim3(BTHREADS), kargs, smemB, stream);
+    e = cudaLaunchKernel(bacc, dim3(p.ntiles, p.nsplit), dim3(wsp ? WS_THREADS : BTHREADS), kargs, smemB, stream);
     if (e != cudaSuccess) return e;
   }
   FinArgs f{};
