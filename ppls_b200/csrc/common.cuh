@@ -83,6 +83,7 @@ struct WidePlan {            // two-pass wide-row path (em_wide.cu)
   int R, NCH, nstage;
   int scX, scY, nslabX, nslabY;      // slab widths (columns) and counts
   int nrg, rows_per_rg, nblk_mu;
+  int slots;                         // CTAs resident at once = grid of the persistent wide kernel (0: one CTA per work item)
 };
 struct WideOffsets { size_t ppart, proj, mu, gpart, gram; };   // offsets (doubles) into the wide workspace
 cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, const char** why);

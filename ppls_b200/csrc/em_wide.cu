@@ -56,27 +56,26 @@ __device__ __forceinline__ void warp_reduce_scatter(double* v, int lane) {
 __host__ __device__ constexpr int pow2_ceil(int x) { return x <= 1 ? 1 : x <= 2 ? 2 : x <= 4 ? 4 : x <= 8 ? 8 : 16; }
 __host__ __device__ constexpr int ilog2(int x) { return x <= 1 ? 0 : 1 + ilog2(x / 2); }
 
+// Register cap: 9 warps per CTA land 5 + 4 on the SM's four schedulers when two CTAs are resident, and a scheduler's
+// 16384 registers hold 5 warps only up to 102 per thread -- at 104+ the second CTA does not fit (measured: pass time
+// 155 -> 219 us).  Narrow slabs stay below the cap anyway.
 template <int R, int NCH, int MODE>
-__global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const WideArgs a) {
+__global__ void __maxnreg__(NCH * R <= 10 ? 96 : 255) wide_kernel(const WideArgs a) {
   if (a.st->done) return;
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int slab = blockIdx.x, rg = blockIdx.y;
-  const bool isY = slab >= a.nslabX;
-  const int sc = isY ? a.scY : a.scX;
-  const int cbeg = isY ? a.p2 + (slab - a.nslabX) * a.scY : slab * a.scX;     // first global column
-  const int cend_type = isY ? a.p2 + a.q2 : a.p2;
-  const int width = (cend_type - cbeg < sc) ? (cend_type - cbeg) : sc;        // even, >= 2
-  const int64_t rbeg = (int64_t)rg * a.rows_per_rg;
-  const int64_t rend = (rbeg + a.rows_per_rg < a.n) ? rbeg + a.rows_per_rg : a.n;
-  const int ntile = (int)((rend - rbeg + WIDE_TR - 1) / WIDE_TR);
-  const uint32_t segbytes = a.panel ? PANEL_W * 8u : (uint32_t)width * 8u;   // a panel is stored whole (zero-padded)
+  // Persistent: the grid is the number of CTAs resident at once; CTA b walks the work items b, b + grid, ...
+  // (item = (column slab, row group)) through ONE continuous ring -- the copies of the next item are in flight while
+  // the compute warps finish the current one, and the ring / barriers are set up once per launch.
+  const int nslab = a.nslabX + a.nslabY;
+  const int nitem = nslab * a.nrg;
   const uint32_t pitch = (uint32_t)NCH * 64u * 8u;                            // smem row pitch (bytes)
   const uint32_t mubytes = (MODE == MODE_ACCUM) ? WIDE_TR * R * 8u : 0u;
   const uint32_t stage_bytes = WIDE_TR * pitch + mubytes;
   const uint32_t sbase = smem_u32(smem);
-  const uint32_t bars = sbase + stage_bytes * a.nstage;                       // full[ns], empty[ns]
-  // zero the ring once: lanes beyond `width` read (and multiply by zero loadings) whatever is there
+  const uint32_t gs_off = stage_bytes * a.nstage;                             // ACCUM: warp-sum buffer [NCH*64*2... cols][R]
+  const uint32_t bars = sbase + gs_off + ((MODE == MODE_ACCUM) ? (uint32_t)NCH * 64u * R * 8u : 0u);   // full[ns], empty[ns]
+  // zero the ring once: lanes beyond a slab's width read (and multiply by zero loadings) whatever is there
   for (uint32_t e = tid; e < stage_bytes * a.nstage / 8u; e += blockDim.x) reinterpret_cast<double*>(smem)[e] = 0.0;
   if (tid == 0) {
     for (int s = 0; s < a.nstage; ++s) { mbar_init(bars + 8u * s, 1); mbar_init(bars + 8u * (a.nstage + s), WIDE_WARPS); }
@@ -85,29 +84,55 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
   fence_proxy_async();
   __syncthreads();
 
+  struct Item { int slab, width, cbeg, ntile; bool isY; int64_t rbeg, rend; int rg; };
+  auto item_of = [&](int it) {
+    Item q;
+    q.slab = it % nslab; q.rg = it / nslab;
+    q.isY = q.slab >= a.nslabX;
+    const int sc = q.isY ? a.scY : a.scX;
+    q.cbeg = q.isY ? a.p2 + (q.slab - a.nslabX) * a.scY : q.slab * a.scX;     // first global column
+    const int cend_type = q.isY ? a.p2 + a.q2 : a.p2;
+    q.width = (cend_type - q.cbeg < sc) ? (cend_type - q.cbeg) : sc;          // even, >= 2
+    q.rbeg = (int64_t)q.rg * a.rows_per_rg;
+    q.rend = (q.rbeg + a.rows_per_rg < a.n) ? q.rbeg + a.rows_per_rg : a.n;
+    q.ntile = (int)((q.rend - q.rbeg + WIDE_TR - 1) / WIDE_TR);
+    return q;
+  };
+
   if (warp == WIDE_WARPS) {
     // ------------------------------------ producer ------------------------------------------
     if (lane == 0) {
       uint32_t s = 0, par = 1;
-      for (int t = 0; t < ntile; ++t) {
-        if (t >= a.nstage) mbar_wait(bars + 8u * (a.nstage + s), par);
-        const int64_t row0 = rbeg + (int64_t)t * WIDE_TR;
-        const int rows = (int)((rend - row0 < WIDE_TR) ? (rend - row0) : WIDE_TR);
-        const uint32_t full = bars + 8u * s, dst = sbase + s * stage_bytes;
-        mbar_expect_tx(full, (uint32_t)rows * segbytes + mubytes);
-        if (a.panel) {
-          bulk_g2s(dst, a.D + ((size_t)slab * a.n + row0) * PANEL_W, (uint32_t)rows * segbytes, full);
-        } else {
-          for (int i = 0; i < rows; ++i)
-            bulk_g2s(dst + (uint32_t)i * pitch, a.D + (size_t)(row0 + i) * a.ld + cbeg, segbytes, full);
+      int64_t gt = 0;                                                          // tiles issued so far (all items)
+      for (int it = blockIdx.x; it < nitem; it += gridDim.x) {
+        const Item q = item_of(it);
+        const uint32_t segbytes = a.panel ? PANEL_W * 8u : (uint32_t)q.width * 8u;   // a panel is stored whole (zero-padded)
+        for (int t = 0; t < q.ntile; ++t, ++gt) {
+          if (gt >= a.nstage) mbar_wait(bars + 8u * (a.nstage + s), par);
+          const int64_t row0 = q.rbeg + (int64_t)(MODE == MODE_ACCUM ? q.ntile - 1 - t : t) * WIDE_TR;   // pass 2 walks back
+          const int rows = (int)((q.rend - row0 < WIDE_TR) ? (q.rend - row0) : WIDE_TR);
+          const uint32_t full = bars + 8u * s, dst = sbase + s * stage_bytes;
+          mbar_expect_tx(full, (uint32_t)rows * segbytes + mubytes);
+          if (a.panel) {
+            bulk_g2s(dst, a.D + ((size_t)q.slab * a.n + row0) * PANEL_W, (uint32_t)rows * segbytes, full);
+          } else {
+            for (int i = 0; i < rows; ++i)
+              bulk_g2s(dst + (uint32_t)i * pitch, a.D + (size_t)(row0 + i) * a.ld + q.cbeg, segbytes, full);
+          }
+          if (MODE == MODE_ACCUM)
+            bulk_g2s(dst + WIDE_TR * pitch, a.mu + (q.isY ? (size_t)a.npad * R : 0) + (size_t)row0 * R, mubytes, full);   // whole tile: the arrays are padded
+          if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
         }
-        if (MODE == MODE_ACCUM)
-          bulk_g2s(dst + WIDE_TR * pitch, a.mu + (isY ? (size_t)a.npad * R : 0) + (size_t)row0 * R, mubytes, full);   // whole tile: the arrays are padded
-        if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
       }
     }
   } else {
     // ------------------------------------ compute warps --------------------------------------
+    const uint32_t xoff = (uint32_t)lane * 16u;
+    uint32_t s = 0, par = 0;
+    for (int it = blockIdx.x; it < nitem; it += gridDim.x) {
+    const Item q = item_of(it);
+    const int slab = q.slab, rg = q.rg, width = q.width, cbeg = q.cbeg, ntile = q.ntile;
+    const int64_t rbeg = q.rbeg, rend = q.rend;
     double wv[NCH][2][R];            // MODE_PROJECT: loadings of my columns; MODE_ACCUM: G accumulators
 #pragma unroll
     for (int j = 0; j < NCH; ++j) {
@@ -118,10 +143,8 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
         for (int k = 0; k < R; ++k)
           wv[j][h][k] = (MODE == MODE_PROJECT && c < width) ? a.L[(size_t)(cbeg + c + h) * R + k] : 0.0;
     }
-    const uint32_t xoff = (uint32_t)lane * 16u;
-    uint32_t s = 0, par = 0;
     for (int t = 0; t < ntile; ++t) {
-      const int64_t row0 = rbeg + (int64_t)t * WIDE_TR;
+      const int64_t row0 = rbeg + (int64_t)(MODE == MODE_ACCUM ? ntile - 1 - t : t) * WIDE_TR;   // pass 2 walks back
       const int rows = (int)((rend - row0 < WIDE_TR) ? (rend - row0) : WIDE_TR);
       mbar_wait(bars + 8u * s, par);
       const uint32_t tile = sbase + s * stage_bytes;
@@ -179,10 +202,10 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
       if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
     }
     if (MODE == MODE_ACCUM) {
-      // this CTA's partial G: add the 8 warps' accumulators in warp order through shared memory
-      // (the ring is free: every tile has been consumed by every warp once all warps are here)
+      // this item's partial G: add the 8 warps' accumulators in warp order through shared memory (a buffer of
+      // its own: the producer is already filling the ring for the next item)
       asm volatile("bar.sync 1, %0;" ::"n"(WIDE_WARPS * 32) : "memory");
-      double* gs = reinterpret_cast<double*>(smem);        // [NCH*64][R]
+      double* gs = reinterpret_cast<double*>(smem + gs_off);        // [NCH*64][R]
       for (int w = 0; w < WIDE_WARPS; ++w) {
         if (warp == w) {
 #pragma unroll
@@ -199,6 +222,7 @@ __global__ void __launch_bounds__((WIDE_WARPS + 1) * 32, 1) wide_kernel(const Wi
       }
       double* out = a.gpart + ((size_t)rg * a.ld + cbeg) * R;
       for (int e = tid; e < width * R; e += WIDE_WARPS * 32) out[e] = gs[e];
+    }
     }
   }
 }
@@ -305,7 +329,7 @@ static wide_kernel_t wide_lookup(int R, int NCH, int mode) {
 
 static size_t wide_smem(int R, int NCH, int nstage, int mode) {
   const size_t stage = (size_t)WIDE_TR * NCH * 64 * 8 + (mode == MODE_ACCUM ? (size_t)WIDE_TR * R * 8 : 0);
-  return stage * nstage + 2 * (size_t)nstage * 8;
+  return stage * nstage + (mode == MODE_ACCUM ? (size_t)NCH * 64 * R * 8 : 0) + 2 * (size_t)nstage * 8;
 }
 
 cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, const char** why) {
@@ -339,6 +363,25 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
     w->NCH = 8;
     for (int i = 5; i >= 0; --i) if (allowed[i] * 64 >= scm) w->NCH = allowed[i];
   }
+  w->R = R;
+  w->nstage = 4;
+  while (w->nstage > 2 && wide_smem(R, w->NCH, w->nstage, MODE_ACCUM) > 200 * 1024) --w->nstage;
+  // CTAs resident at once, as the runtime sees it for these kernels (registers and shared memory)
+  int occ_min = 1 << 30;
+  for (int mode = MODE_PROJECT; mode <= MODE_ACCUM; ++mode) {
+    wide_kernel_t k = wide_lookup(R, w->NCH, mode);
+    if (!k) { *why = "wide path: no kernel for this (nr_comp, slab width)"; return cudaErrorInvalidValue; }
+    const size_t smem = wide_smem(R, w->NCH, w->nstage, mode);
+    cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) { *why = "cudaFuncSetAttribute failed (wide path)"; return e; }
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k, (WIDE_WARPS + 1) * 32, smem);
+    if (e != cudaSuccess || occ < 1) { *why = "wide path: the kernel does not fit an SM"; return e != cudaSuccess ? e : cudaErrorInvalidValue; }
+    if (occ < occ_min) occ_min = occ;
+  }
+  if (occ_min > 2) occ_min = 2;                                       // two rings per SM already keep > 128 KB in flight
+  if (!s.panel) occ_min = 1;                                          // the slab split above is sized for one CTA per SM
+  slots = occ_min * sm_count;
   // row groups: fill the resident-CTA slots in whole waves (each group keeps >= 4 tiles of rows)
   const int nslab = w->nslabX + w->nslabY;
   const int64_t max_rg = (s.n + 4 * WIDE_TR - 1) / (4 * WIDE_TR);
@@ -350,20 +393,11 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
   }
   w->rows_per_rg = (int)(((s.n + nrg - 1) / nrg + WIDE_TR - 1) / WIDE_TR * WIDE_TR);
   w->nrg = (int)((s.n + w->rows_per_rg - 1) / w->rows_per_rg);
-  w->R = R;
-  w->nstage = 4;
-  while (w->nstage > 2 && wide_smem(R, w->NCH, w->nstage, MODE_ACCUM) > 200 * 1024) --w->nstage;
+  { const char* ep = getenv("PPLS_WIDE_PERSIST"); w->slots = (ep && *ep && atoi(ep) == 0) ? 0 : slots; }   // 0: one CTA per work item
   w->nblk_mu = (int)((s.n + WMU_ROWS - 1) / WMU_ROWS);
-  for (int mode = MODE_PROJECT; mode <= MODE_ACCUM; ++mode) {
-    wide_kernel_t k = wide_lookup(R, w->NCH, mode);
-    if (!k) { *why = "wide path: no kernel for this (nr_comp, slab width)"; return cudaErrorInvalidValue; }
-    cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)wide_smem(R, w->NCH, w->nstage, mode));
-    if (e != cudaSuccess) { *why = "cudaFuncSetAttribute failed (wide path)"; return e; }
-  }
   if (getenv("PPLS_K1_VERBOSE") && atoi(getenv("PPLS_K1_VERBOSE")))
-    fprintf(stderr, "[ppls] wide plan: R=%d slabs X %d x %d cols, Y %d x %d cols, NCH=%d, row groups %d x %d rows, stages=%d\n",
-            R, w->nslabX, w->scX, w->nslabY, w->scY, w->NCH, w->nrg, w->rows_per_rg, w->nstage);
+    fprintf(stderr, "[ppls] wide plan: R=%d slabs X %d x %d cols, Y %d x %d cols, NCH=%d, row groups %d x %d rows, stages=%d, resident CTAs %d\n",
+            R, w->nslabX, w->scX, w->nslabY, w->scY, w->NCH, w->nrg, w->rows_per_rg, w->nstage, slots);
   return cudaSuccess;
 }
 
@@ -387,7 +421,8 @@ cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const dou
   a.D = D; a.L = L; a.st = st; a.ppart = ws + o.ppart; a.mu = ws + o.mu; a.gpart = ws + o.gpart;
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.q2 = s.q2; a.scX = w.scX; a.scY = w.scY; a.nslabX = w.nslabX;
   a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage; a.panel = s.panel;
-  dim3 grid(w.nslabX + w.nslabY, w.nrg);
+  const int nitem = (w.nslabX + w.nslabY) * w.nrg;
+  const int grid = (w.slots > 0 && w.slots < nitem) ? w.slots : nitem;
   wide_lookup(w.R, w.NCH, MODE_PROJECT)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_PROJECT), stream>>>(a);
   const int64_t ne = s.n * w.R;
   wide_proj_sum_kernel<<<(unsigned)((ne + 31) / 32), dim3(32, 8), 0, stream>>>(ws + o.ppart, s.n, w.R, w.nslabX, w.nslabY, ws + o.proj, st);
@@ -403,7 +438,8 @@ cudaError_t launch_wide_accum(const WidePlan& w, const DataShape& s, const doubl
   a.D = D; a.L = L; a.st = st; a.ppart = ws + o.ppart; a.mu = ws + o.mu; a.gpart = ws + o.gpart;
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.q2 = s.q2; a.scX = w.scX; a.scY = w.scY; a.nslabX = w.nslabX;
   a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage; a.panel = s.panel;
-  dim3 grid(w.nslabX + w.nslabY, w.nrg);
+  const int nitem = (w.nslabX + w.nslabY) * w.nrg;
+  const int grid = (w.slots > 0 && w.slots < nitem) ? w.slots : nitem;
   wide_lookup(w.R, w.NCH, MODE_ACCUM)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_ACCUM), stream>>>(a);
   const int64_t glen = (int64_t)s.ld * w.R; const int glen2 = 3 * w.R * w.R;
   wide_finalize_kernel<<<(unsigned)((glen + glen2 + 255) / 256), 256, 0, stream>>>(ws + o.gpart, w.nrg, glen, ws + o.gram, w.nblk_mu,
