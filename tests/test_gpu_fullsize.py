@@ -76,3 +76,35 @@ def test_prefix_of_the_big_sample_is_the_small_problem(oracle_lib):
                      atol=-np.inf)
     assert relmax(res["loglik"], o["loglik"]) < 1e-10
     assert relmax(res["W"], o["W"]) < 1e-8 and relmax(res["C"], o["C"]) < 1e-8 and relmax(res["B"], o["B"]) < 1e-8
+
+
+def test_c5_full_size_batched_against_single_runs_and_oracle(oracle_lib):
+    """BASELINE config 5 at full size (64 starts of N=1e5, p=200, q=50, r=2 over one resident dataset): the batched
+    GEMM path (em_batch.cu) against ordinary runs of the streaming kernel for three of the starts, and against the
+    fused CPU oracle for the first one; every start's log-likelihood trace is monotone."""
+    from oracle import cbind, ppls_fused as F
+    from helpers import relmax
+    from ppls_b200 import Data, Fit, PPLS_simult_batched, default_context, normalise, synth
+    N, p, q, r, S, steps = 100_000, 200, 50, 2, 64, 6
+    truth = synth.truth_params(p, q, r)
+    ctx = default_context()
+    d = Data.synthetic(ctx, N, p, q, truth, seed=20260105)
+    inits = [synth.start_params(truth, seed=1000 + s) for s in range(S)]
+    out = PPLS_simult_batched(None, None, r, inits, EMsteps=steps, atol=-np.inf, data=d)
+    assert len(out) == S
+    for o in out:
+        ll = o["loglik"]
+        assert o["steps"] == steps and np.all(np.diff(ll) > -1e-9 * np.abs(ll[:-1]))
+    for s in (0, 31, 63):
+        W0, C0, B0, T0 = normalise(inits[s]["W"], inits[s]["C"], inits[s]["B"], inits[s]["sigT"])
+        f = Fit(d, dict(inits[s], W=W0, C=C0, B=B0, sigT=T0), r, steps, -np.inf, "SVD")
+        f.run(); one = f.result(want_mu=False); f.close()
+        assert relmax(out[s]["loglik"], one["loglik"]) < 1e-12
+        assert relmax(out[s]["loop_state"]["W"], one["W"]) < 1e-10 and relmax(out[s]["loop_state"]["C"], one["C"]) < 1e-10
+    d.close()
+    X, Y = cbind.gen_data(oracle_lib, 20260105, 0, N, truth)
+    W0, C0, B0, T0 = normalise(inits[0]["W"], inits[0]["C"], inits[0]["B"], inits[0]["sigT"])
+    o = F.fused_loop(oracle_lib, X, Y, W0, C0, B0, inits[0]["sigE"], inits[0]["sigF"], inits[0]["sigH"], T0,
+                     EMsteps=steps, atol=-np.inf, want_mu=False)
+    assert relmax(out[0]["loglik"], o["loglik"]) < 1e-10
+    assert relmax(out[0]["loop_state"]["W"], o["W"]) < 1e-8 and relmax(out[0]["loop_state"]["C"], o["C"]) < 1e-8
