@@ -994,7 +994,7 @@ extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const 
     rc = allreduce_sum(ctx, B.mp, (size_t)groups * veclenP);
     if (rc) return rc;
     CU(launch_em_update_batch(sh, R, RP, g, S, tracelen, 0, B.mp, B.Lp, B.pst, B.st, B.ms, B.Ls, B.Lsc, B.tr, st, B.coef));
-    launches += (gemm ? (bplan.fused ? 3 : 4) : 2) * groups + 2; passes += 1;
+    launches += (gemm ? (bplan.fused ? 3 : 4) : 2) * groups + (gemm ? 1 : 2); passes += 1;
     if ((pass + 1) % check_every == 0 && pass < opts->max_steps) {
       CU(cudaMemcpyAsync(hst.data(), B.st, (size_t)S * sizeof(FitState), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));

@@ -83,10 +83,28 @@ __global__ void ssq_partial_kernel(const double* __restrict__ D, const DataShape
                                    double* __restrict__ scratch /*[grid][2]*/) {
   const int64_t n = s.n; const int ld = s.ld, p2 = s.p2;
   double sx = 0.0, sy = 0.0;
-  for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
-    for (int j = threadIdx.x; j < ld; j += blockDim.x) {
-      const double v = D[data_index(s, i, j)];
-      if (j < p2) sx += v * v; else sy += v * v;
+  if (!s.panel) {
+    // row-major: 16-byte loads (p2 is even, so a pair never straddles the X|Y boundary), 4 rows in flight per thread
+    const int np = ld >> 1, px = p2 >> 1;
+    const double2* D2 = reinterpret_cast<const double2*>(D);
+    for (int64_t i = (int64_t)blockIdx.x * 4; i < n; i += (int64_t)gridDim.x * 4) {
+      const int rows = (n - i < 4) ? (int)(n - i) : 4;
+      for (int j = threadIdx.x; j < np; j += blockDim.x) {
+        double2 v[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) v[r] = (r < rows) ? D2[(size_t)(i + r) * np + j] : make_double2(0.0, 0.0);
+        double t = 0.0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) t += v[r].x * v[r].x + v[r].y * v[r].y;
+        if (j < px) sx += t; else sy += t;
+      }
+    }
+  } else {
+    for (int64_t i = blockIdx.x; i < n; i += gridDim.x) {
+      for (int j = threadIdx.x; j < ld; j += blockDim.x) {
+        const double v = D[data_index(s, i, j)];
+        if (j < p2) sx += v * v; else sy += v * v;
+      }
     }
   }
   __shared__ double shx[8], shy[8];

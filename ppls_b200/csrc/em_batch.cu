@@ -231,7 +231,9 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs
   const int nsX = (a.p2 + BK - 1) / BK, nsY = (a.q2 + BK - 1) / BK, nst = nsX + nsY;
   double* gsh = sm + (size_t)FSTAGES * FSTAGE;                    // Gram fold buffer (not the ring: the producer runs ahead)
   double* csh = gsh + 4 * FT_N * 3 * R;                           // coefficients aT, bT, aU, bU of the tile's components
-  const uint32_t bars = bsm32(csh + 4 * FT_N);                    // full[FSTAGES], empty[FSTAGES]
+  double* gacc = csh + 4 * FT_N;                                  // [ncb2][FT_N][3 R]: this CTA's Gram sums over all its tiles
+  const uint32_t bars = bsm32(gacc + (size_t)ncb2 * FT_N * 3 * R);   // full[FSTAGES], empty[FSTAGES]
+  for (int e = tid; e < ncb2 * FT_N * 3 * R; e += WS_THREADS) gacc[e] = 0.0;
   if (tid == 0) {
     for (int b = 0; b < FSTAGES; ++b) { bbar_init(bars + 8u * b, 128); bbar_init(bars + 8u * (FSTAGES + b), BTHREADS / 32); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs
   uint32_t g = 0;                                                 // stages consumed so far
   for (int64_t t = blockIdx.x; t < ntile; t += gridDim.x) {
     const int cb = (int)(t % ncb2);
-    const int64_t rt = t / ncb2, row0 = rt * BT;
+    const int64_t row0 = (t / ncb2) * BT;
     // (read after the barrier that follows the K loop; the previous tile's readers are past its second barrier)
     csh[tid] = a.coef[(size_t)(tid / FT_N) * a.RP + cb * FT_N + (tid % FT_N)];
     double accx[4][4][2], accy[4][4][2];
@@ -375,16 +377,20 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs
       }
     }
     csync();
-    // fold the 4 row warps in fixed order -> gpart[row tile][start][3][R*R]
+    // fold the 4 row warps in fixed order and add to this CTA's running sums (element e always belongs to the same thread)
     for (int e = tid; e < FT_N * 3 * R; e += BTHREADS) {
-      const int cl = e / (3 * R), wl = e - cl * 3 * R, w = wl / R, l = wl - w * R;
-      const int c = cb * FT_N + cl, st = c / R, k = c - st * R;
-      if (st >= a.nstart) continue;
       double tsum = 0.0;
 #pragma unroll
-      for (int q = 0; q < 4; ++q) tsum += gsh[((size_t)q * FT_N + cl) * 3 * R + wl];
-      a.gpart[((size_t)rt * a.nstart + st) * 3 * R * R + w * R * R + k * R + l] = tsum;
+      for (int q = 0; q < 4; ++q) tsum += gsh[(size_t)q * FT_N * 3 * R + e];
+      gacc[(size_t)cb * FT_N * 3 * R + e] += tsum;
     }
+  }
+  // this CTA's Gram partial -> gpart[CTA][start][3][R*R] (tiles were added in the order the CTA walked them)
+  csync();
+  for (int e = tid; e < ncb2 * FT_N * 3 * R; e += BTHREADS) {
+    const int c = e / (3 * R), wl = e - c * 3 * R, w = wl / R, l = wl - w * R;
+    const int st = c / R, k = c - st * R;
+    if (st < a.nstart) a.gpart[((size_t)blockIdx.x * a.nstart + st) * 3 * R * R + w * R * R + k * R + l] = gacc[e];
   }
 }
 
@@ -628,7 +634,14 @@ void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGe
   // fused projection + mu kernel (R divides 8): one Gram partial per row tile
   const char* ef = getenv("PPLS_BATCH_FUSED");
   p->fused = (8 % R == 0) && !(ef && *ef && atoi(ef) == 0);
-  if (p->fused) { p->nchunk = p->rowtiles; p->rows_per_chunk = BT; }
+  if (p->fused) {
+    // persistent: one CTA per SM walks the (row tile, component block) tiles (PPLS_BPROJ_PERSIST=0: one CTA per tile);
+    // every CTA leaves ONE Gram partial, so nchunk = the grid of bprojmu_kernel
+    const char* ep = getenv("PPLS_BPROJ_PERSIST");
+    int64_t grid = (int64_t)(RP / FT_N) * p->rowtiles;
+    if (!(ep && *ep && atoi(ep) == 0) && sm_count > 0 && grid > sm_count) grid = sm_count;
+    p->nchunk = (int)grid; p->rows_per_chunk = BT;
+  }
 }
 size_t bgemm_workspace_doubles(const DataShape& s, const BGemmPlan& p) {
   return (size_t)s.n * 2 * p.RP                                   // P / mu
@@ -649,14 +662,10 @@ static int bgemm_ws() {
 }
 template <int R>
 static cudaError_t launch_bprojmu_r(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
-  const size_t smem = ((size_t)FSTAGES * FSTAGE + 4 * FT_N * 3 * R + 4 * FT_N + 2 * FSTAGES) * sizeof(double);
+  const size_t smem = ((size_t)FSTAGES * FSTAGE + 4 * FT_N * 3 * R + 4 * FT_N + (size_t)(p.RP / FT_N) * FT_N * 3 * R + 2 * FSTAGES) * sizeof(double);
   cudaError_t e = cudaFuncSetAttribute((const void*)bprojmu_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  // persistent: one CTA per SM walks the (row tile, component block) tiles; PPLS_BPROJ_PERSIST=0: one CTA per tile
-  const char* ep = getenv("PPLS_BPROJ_PERSIST");
-  const size_t ntile = (size_t)(p.RP / FT_N) * p.rowtiles;
-  size_t grid = ntile;
-  if (!(ep && *ep && atoi(ep) == 0) && p.sm_count > 0 && grid > (size_t)p.sm_count) grid = (size_t)p.sm_count;
+  const size_t grid = (size_t)p.nchunk;            // = CTAs of this kernel (plan_bgemm): one Gram partial per CTA
   bprojmu_kernel<R><<<(unsigned)grid, WS_THREADS, smem, stream>>>(fa);
   return cudaGetLastError();
 }

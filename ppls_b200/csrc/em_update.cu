@@ -864,7 +864,8 @@ cudaError_t launch_em_update_batch(const DataShape& s, int R, int RP, int g, int
     case 8: launch_batch_R<8>(b, stream); break;
     default: return cudaErrorInvalidValue;
   }
-  if (!prepare) batch_done_kernel<<<(S / g + 64) / 64, 64, 0, stream>>>(pack_st, st, g, S);
+  // (the GEMM path, coef != null, never reads a pack's done flag: every start checks its own in the update block)
+  if (!prepare && !coef) batch_done_kernel<<<(S / g + 64) / 64, 64, 0, stream>>>(pack_st, st, g, S);
   return cudaGetLastError();
 }
 

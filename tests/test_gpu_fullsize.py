@@ -83,8 +83,10 @@ def test_c5_full_size_batched_against_single_runs_and_oracle(oracle_lib):
     GEMM path (em_batch.cu) against ordinary runs of the streaming kernel for three of the starts, and against the
     fused CPU oracle for the first one; every start's log-likelihood trace is monotone."""
     from oracle import cbind, ppls_fused as F
-    from helpers import relmax
+    from helpers import TOL_LOGLIK_ILLCOND, TOL_PARAM, relmax
     from ppls_b200 import Data, Fit, PPLS_simult_batched, default_context, normalise, synth
+    # the bench's generating parameters (sigma = 0.05): the ill-conditioned workload of helpers.py, where a 1-ulp change
+    # of the data moves the reference's own log-likelihood by up to 3e-10 -- two summation orders agree to 2e-9, not 1e-12
     N, p, q, r, S, steps = 100_000, 200, 50, 2, 64, 6
     truth = synth.truth_params(p, q, r)
     ctx = default_context()
@@ -99,12 +101,12 @@ def test_c5_full_size_batched_against_single_runs_and_oracle(oracle_lib):
         W0, C0, B0, T0 = normalise(inits[s]["W"], inits[s]["C"], inits[s]["B"], inits[s]["sigT"])
         f = Fit(d, dict(inits[s], W=W0, C=C0, B=B0, sigT=T0), r, steps, -np.inf, "SVD")
         f.run(); one = f.result(want_mu=False); f.close()
-        assert relmax(out[s]["loglik"], one["loglik"]) < 1e-12
-        assert relmax(out[s]["loop_state"]["W"], one["W"]) < 1e-10 and relmax(out[s]["loop_state"]["C"], one["C"]) < 1e-10
+        assert relmax(out[s]["loglik"], one["loglik"]) < TOL_LOGLIK_ILLCOND
+        assert relmax(out[s]["loop_state"]["W"], one["W"]) < TOL_PARAM and relmax(out[s]["loop_state"]["C"], one["C"]) < TOL_PARAM
     d.close()
     X, Y = cbind.gen_data(oracle_lib, 20260105, 0, N, truth)
     W0, C0, B0, T0 = normalise(inits[0]["W"], inits[0]["C"], inits[0]["B"], inits[0]["sigT"])
     o = F.fused_loop(oracle_lib, X, Y, W0, C0, B0, inits[0]["sigE"], inits[0]["sigF"], inits[0]["sigH"], T0,
                      EMsteps=steps, atol=-np.inf, want_mu=False)
-    assert relmax(out[0]["loglik"], o["loglik"]) < 1e-10
-    assert relmax(out[0]["loop_state"]["W"], o["W"]) < 1e-8 and relmax(out[0]["loop_state"]["C"], o["C"]) < 1e-8
+    assert relmax(out[0]["loglik"], o["loglik"]) < TOL_LOGLIK_ILLCOND
+    assert relmax(out[0]["loop_state"]["W"], o["W"]) < TOL_PARAM and relmax(out[0]["loop_state"]["C"], o["C"]) < TOL_PARAM
