@@ -354,28 +354,48 @@ static int data_from_host_impl(ppls_ctx* ctx, const double* X, int64_t ldX, cons
   cudaError_t e = cudaMalloc(&d->D, bytes);
   if (e == cudaSuccess && d->s.panel) e = cudaMemsetAsync(d->D, 0, bytes, ctx->stream);
   if (e != cudaSuccess) { delete d; return fail(PPLS_E_OOM, std::string("device allocation of the data shard: ") + cudaGetErrorString(e)); }
-  // staging: chunks of rows, column-major as they lie in the caller's arrays
-  const size_t stage_budget = (size_t)256 << 20;
+  // staging: chunks of rows, column-major as they lie in the caller's arrays.  Two staging buffers and a copy
+  // stream of its own: the host->device copy of chunk k+1 runs while chunk k is re-tiled into the row-major shard.
+  const size_t stage_budget = (size_t)128 << 20;
   int64_t cr = (int64_t)(stage_budget / (sizeof(double) * (size_t)(p + q)));
   if (cr > n) cr = n;
   if (cr < 32) cr = (n < 32) ? n : 32;
+  const size_t stg_elems = (size_t)cr * (size_t)(p + q);
   double* stg = nullptr;
-  e = cudaMalloc(&stg, sizeof(double) * (size_t)cr * (size_t)(p + q));
-  if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_OOM, "device allocation of the staging buffer"); }
-  double* stgX = stg;
-  double* stgY = stg + (size_t)cr * p;
-  for (int64_t i0 = 0; i0 < n && e == cudaSuccess; i0 += cr) {
+  e = cudaMalloc(&stg, 2 * sizeof(double) * stg_elems);
+  if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_OOM, "device allocation of the staging buffers"); }
+  cudaStream_t cs = nullptr;
+  cudaEvent_t copied[2] = {nullptr, nullptr}, tiled[2] = {nullptr, nullptr};
+  e = cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking);
+  for (int b = 0; b < 2 && e == cudaSuccess; ++b) {
+    e = cudaEventCreateWithFlags(&copied[b], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&tiled[b], cudaEventDisableTiming);
+  }
+  int64_t k = 0;
+  for (int64_t i0 = 0; i0 < n && e == cudaSuccess; i0 += cr, ++k) {
+    const int b = (int)(k & 1);
     const int64_t rows = (n - i0 < cr) ? (n - i0) : cr;
-    e = cudaMemcpy2DAsync(stgX, rows * sizeof(double), X + i0, ldX * sizeof(double), rows * sizeof(double), (size_t)p,
-                          cudaMemcpyHostToDevice, ctx->stream);
+    double* stgX = stg + (size_t)b * stg_elems;
+    double* stgY = stgX + (size_t)cr * p;
+    if (k >= 2) e = cudaStreamWaitEvent(cs, tiled[b], 0);          // the re-tile of chunk k-2 has read this buffer
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(stgX, rows * sizeof(double), X + i0, ldX * sizeof(double), rows * sizeof(double), (size_t)p,
+                            cudaMemcpyHostToDevice, cs);
     if (e == cudaSuccess)
       e = cudaMemcpy2DAsync(stgY, rows * sizeof(double), Y + i0, ldY * sizeof(double), rows * sizeof(double), (size_t)q,
-                            cudaMemcpyHostToDevice, ctx->stream);
+                            cudaMemcpyHostToDevice, cs);
+    if (e == cudaSuccess) e = cudaEventRecord(copied[b], cs);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, copied[b], 0);
     if (e == cudaSuccess) e = launch_retile(stgX, rows, rows, (int)p, d->D, d->s, 0, i0, ctx->stream);
     if (e == cudaSuccess) e = launch_retile(stgY, rows, rows, (int)q, d->D, d->s, d->s.p2, i0, ctx->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(tiled[b], ctx->stream);
   }
   if (e == cudaSuccess) e = launch_zero_pad(d->D, d->s, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaError_t e2 = cs ? cudaStreamSynchronize(cs) : cudaSuccess;
+  if (e == cudaSuccess) e = e2;
+  for (int b = 0; b < 2; ++b) { if (copied[b]) cudaEventDestroy(copied[b]); if (tiled[b]) cudaEventDestroy(tiled[b]); }
+  if (cs) cudaStreamDestroy(cs);
   cudaFree(stg);
   if (e != cudaSuccess) { cudaFree(d->D); delete d; return fail(PPLS_E_CUDA, std::string("upload: ") + cudaGetErrorString(e)); }
   rc = data_finalize(ctx, d);
