@@ -128,41 +128,56 @@ __device__ void block_gram(const double* A, int n, double* S, double* scratch) {
 
 // Cyclic Jacobi eigen-decomposition of a symmetric R x R matrix (one thread).
 // On exit A is (numerically) diagonal and the columns of V are the eigenvectors.
-template <int R>
-__device__ void jacobi_eig(double* A, double* V) {
-  for (int i = 0; i < R; ++i)
-    for (int j = 0; j < R; ++j) V[i * R + j] = (i == j) ? 1.0 : 0.0;
-  for (int sweep = 0; sweep < 40; ++sweep) {
-    double off = 0.0, diag = 0.0;
-    for (int i = 0; i < R; ++i) {
-      diag += A[i * R + i] * A[i * R + i];
-      for (int j = i + 1; j < R; ++j) off += A[i * R + j] * A[i * R + j];
-    }
-    if (off <= 1e-40 * diag || off == 0.0) break;
-    for (int p = 0; p < R - 1; ++p)
-      for (int q = p + 1; q < R; ++q) {
-        const double apq = A[p * R + q];
-        if (apq == 0.0) continue;
-        const double theta = (A[q * R + q] - A[p * R + p]) / (2.0 * apq);
-        const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
-        const double c = 1.0 / sqrt(tt * tt + 1.0), s = tt * c;
-        for (int k = 0; k < R; ++k) {  // A <- A J
-          const double akp = A[k * R + p], akq = A[k * R + q];
-          A[k * R + p] = c * akp - s * akq;
-          A[k * R + q] = s * akp + c * akq;
-        }
-        for (int k = 0; k < R; ++k) {  // A <- J' A
-          const double apk = A[p * R + k], aqk = A[q * R + k];
-          A[p * R + k] = c * apk - s * aqk;
-          A[q * R + k] = s * apk + c * aqk;
-        }
-        for (int k = 0; k < R; ++k) {
-          const double vkp = V[k * R + p], vkq = V[k * R + q];
-          V[k * R + p] = c * vkp - s * vkq;
-          V[k * R + q] = s * vkp + c * vkq;
-        }
-      }
+// Mat[m] = S[m]^{-1/2} for NM symmetric positive definite R x R matrices in shared memory, by the WHOLE block
+// (every thread must call it; blockDim.x >= 64 NM).  Coupled Newton-Schulz iteration on Y0 = S / trace(S), Z0 = I:
+//   T = (3 I - Z Y) / 2,  Y <- Y T,  Z <- T Z;   Y -> (S/c)^{1/2},  Z -> (S/c)^{-1/2}   (eigenvalues of S/c lie in (0, 1])
+// One thread per matrix element, three block barriers per step; quadratic convergence once |I - Z Y| < 1, about
+// log_2.25(cond) steps before that.  Replaces the one-thread Jacobi eigen-decomposition (R = 5: ~30 us of serial
+// rotations with the matrices in local memory) by ~2 us; the Newton-Schulz polish that follows in the callers is
+// unchanged.  A matrix that does not converge (singular Gram: rank-deficient G) yields NaN, which the callers'
+// finiteness checks turn into PPLS_E_NONFINITE exactly as 1/sqrt(0) did.
+template <int R, int NM>
+__device__ void block_inv_sqrt(const double* S /*[NM][R*R]*/, double* Mat /*[NM][R*R]*/, double* work /*[NM][3][R*R]*/) {
+  static_assert(R * R <= 64, "one thread per element, 64 threads per matrix");
+  const int m = threadIdx.x >> 6, e = threadIdx.x & 63;
+  const bool act = (m < NM) && (e < R * R);
+  const int i = act ? e / R : 0, j = act ? e - i * R : 0;
+  double* Y = work + (size_t)(act ? m : 0) * 3 * R * R;
+  double* Z = Y + R * R;
+  double* T = Z + R * R;
+  double c = 0.0;
+  if (act) {
+    const double* Sm = S + (size_t)m * R * R;
+#pragma unroll
+    for (int k = 0; k < R; ++k) c += Sm[k * R + k];
+    Y[e] = Sm[e] / c;
+    Z[e] = (i == j) ? 1.0 : 0.0;
   }
+  __syncthreads();
+  bool converged = false;
+  for (int it = 0; it < 100; ++it) {
+    double err = 0.0;
+    if (act) {
+      double zy = 0.0;
+#pragma unroll
+      for (int k = 0; k < R; ++k) zy = fma(Z[i * R + k], Y[k * R + j], zy);
+      const double d = (i == j) ? 1.0 : 0.0;
+      err = fabs(d - zy);
+      T[e] = 0.5 * (3.0 * d - zy);
+    }
+    const int go = __syncthreads_or(!(err < 1e-13));      // (NaN counts as not converged)
+    double yn = 0.0, zn = 0.0;
+    if (act) {
+#pragma unroll
+      for (int k = 0; k < R; ++k) { yn = fma(Y[i * R + k], T[k * R + j], yn); zn = fma(T[i * R + k], Z[k * R + j], zn); }
+    }
+    __syncthreads();
+    if (act) { Y[e] = yn; Z[e] = zn; }
+    __syncthreads();
+    if (!go) { converged = true; break; }                  // the step just taken started from |I - Z Y| < 1e-13
+  }
+  if (act) Mat[(size_t)m * R * R + e] = converged ? Z[e] / sqrt(c) : __longlong_as_double(0x7ff8000000000000ll);
+  __syncthreads();
 }
 
 // out[j][:] = A[j][:] * Mat (R x R, shared) for all rows j.
@@ -192,18 +207,11 @@ template <int R>
 __device__ void orth_polar(const double* G, int n, double* out, double* S, double* Mat,
                            double* scratch) {
   block_gram<R>(G, n, S, scratch);
-  if (threadIdx.x == 0) {
-    double A[R * R], V[R * R];
-    for (int e = 0; e < R * R; ++e) A[e] = S[e];
-    jacobi_eig<R>(A, V);
-    for (int i = 0; i < R; ++i)
-      for (int j = 0; j < R; ++j) {
-        double s = 0.0;
-        for (int k = 0; k < R; ++k) s += V[i * R + k] * (1.0 / sqrt(A[k * R + k])) * V[j * R + k];
-        Mat[i * R + j] = s;
-      }
-  }
   __syncthreads();
+  {
+    __shared__ double nswork[3 * R * R];
+    block_inv_sqrt<R, 1>(S, Mat, nswork);
+  }
   rows_times<R>(G, n, Mat, out);
   block_gram<R>(out, n, S, scratch);
   if (threadIdx.x == 0)
@@ -658,7 +666,6 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   const int nb = gridDim.x - 1, rb = (int)blockIdx.x - 1;
   double* ph0 = a.gscratch;
   double* ph1 = ph0 + (size_t)nb * 2 * R * R;
-  double* ph2 = ph1 + (size_t)nb * 2 * R * R;
   const double* G = a.momvec;
   // ---- phase 0 (multi-GPU peer exchange): wait for the world's vectors, sum them in rank order ------
   if (a.use_x) {
@@ -702,19 +709,10 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
     grid_sum_gram<R>(ph0, nb, 0, S[0]);
     grid_sum_gram<R>(ph0, nb, 1, S[1]);
     __syncthreads();
-    if (threadIdx.x == 0 || threadIdx.x == 32) {
-      const int w = threadIdx.x >> 5;
-      double A[R * R], V[R * R];
-      for (int e = 0; e < R * R; ++e) A[e] = S[w][e];
-      jacobi_eig<R>(A, V);
-      for (int i = 0; i < R; ++i)
-        for (int j = 0; j < R; ++j) {
-          double sacc = 0.0;
-          for (int k = 0; k < R; ++k) sacc += V[i * R + k] * (1.0 / sqrt(A[k * R + k])) * V[j * R + k];
-          Mat[w][i * R + j] = sacc;
-        }
+    {
+      __shared__ double nswork[2 * 3 * R * R];
+      block_inv_sqrt<R, 2>(&S[0][0], &Mat[0][0], nswork);     // (G1'G1)^{-1/2} and (G2'G2)^{-1/2}, every row block its own copy
     }
-    __syncthreads();
     for (int j = rb * GT + threadIdx.x; j < a.ld; j += nb * GT) {
       const double* M = Mat[j >= a.p2 ? 1 : 0];
       double row[R];
