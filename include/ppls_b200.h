@@ -184,6 +184,12 @@ int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int3
  * for r components: one streaming pass over the resident data. */
 int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out);
 
+/* ---- orth(G, type): OmicsPLS::orth as the M-step calls it (EM_W_multi.R:732-733; historical in-tree copy
+ * Package/functions.R:252-260).  G: n x r column-major host matrix (r <= n); type PPLS_ORTH_SVD: the polar factor
+ * U V' of the thin SVD; PPLS_ORTH_QR: qr.Q(qr(G)) times sign(e[,1]' G[,1]).  out: n x r column-major host. ---- */
+int ppls_orth(ppls_ctx* ctx, const double* G, int64_t ldG, int64_t n, int32_t r, int32_t orth_type,
+              double* out, int64_t ldOut);
+
 /* ---- standard errors of the loadings: variances.PPLS_simult(fit, data, XorY) (EM_W_multi.R:830-860) ---- */
 /* which = 0: data = X, mu = fit$Expectations$mu_T (n x r column-major, host, this rank's rows), Cdiag =
  * diag(fit$Expectations$Ctt); which = 1: data = Y, mu = mu_U, Cdiag = diag(Cuu).  sigE = fit$estimates$sigE

@@ -17,7 +17,7 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "normalise", "default_init",
+__all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "orth", "normalise", "default_init",
            "sequential_init", "default_context", "variances", "simulC", "meta_PPLSi"]
 
 
@@ -474,6 +474,22 @@ def logl_W(X, Y, W, C_, B_T, sigX, sigY, sigH, sigT, ctx: Optional[Context] = No
         if own:
             data.close()
     return float(out.value)
+
+
+def orth(G, type="SVD", ctx: Optional[Context] = None):
+    """OmicsPLS::orth(G, type) as the M-step calls it (EM_W_multi.R:732-733; in-tree copy Package/functions.R:252-260):
+    type "SVD" -> the polar factor U V' of the thin SVD of G; "QR" -> qr.Q(qr(G)) * sign(e[,1]' G[,1])."""
+    if type not in ("SVD", "QR"):
+        raise ValueError("'arg' should be one of 'SVD', 'QR'")
+    Gf = _f64(np.asarray(G))
+    if Gf.ndim != 2:
+        raise ValueError("G must be a matrix")
+    n, r = Gf.shape
+    ctx = ctx or default_context()
+    out = np.empty((n, r), order="F")
+    L.check(L.lib().ppls_orth(ctx._h, Gf.ctypes.data, max(n, 1), n, r, L.PPLS_ORTH_SVD if type == "SVD" else L.PPLS_ORTH_QR,
+                              out.ctypes.data, max(n, 1)))
+    return out
 
 
 def variances(fit, data, XorY="X", ctx: Optional[Context] = None, dev_data: Optional[Data] = None, matrices: bool = True):

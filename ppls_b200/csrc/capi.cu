@@ -1121,6 +1121,31 @@ extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr
 
 // ---- log-likelihood of a parameter set: logl_W (EM_W_multi.R:296-326) -> loglC_fast (loglC.cpp:318-338) ------
 // One streaming pass (the same kernels as an EM iteration; the moments it needs are the Gram of (XW, YC)).
+// orth(G, type): OmicsPLS::orth as PPLS_simult calls it (EM_W_multi.R:732-733).  Host in, host out.
+extern "C" int ppls_orth(ppls_ctx* ctx, const double* G, int64_t ldG, int64_t n, int32_t r, int32_t orth_type,
+                         double* out, int64_t ldOut) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!G || !out) return fail(PPLS_E_INVALID, "null G or out");
+  if (r < 1 || r > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
+  if (n < r || n > 0x7fffffff / MAXR) return fail(PPLS_E_INVALID, "orth: need r <= nrow(G) < 2^31 / 8");
+  if (ldG < n || ldOut < n) return fail(PPLS_E_INVALID, "leading dimension smaller than the row count");
+  if (orth_type != PPLS_ORTH_SVD && orth_type != PPLS_ORTH_QR) return fail(PPLS_E_INVALID, "'arg' should be one of 'SVD', 'QR'");
+  std::vector<double> h((size_t)n * r);
+  for (int k = 0; k < r; ++k)
+    for (int64_t j = 0; j < n; ++j) h[(size_t)j * r + k] = G[j + (size_t)k * ldG];
+  struct Bufs { double *g = nullptr, *o = nullptr, *w = nullptr; ~Bufs() { cudaFree(g); cudaFree(o); cudaFree(w); } } B;
+  const size_t bytes = h.size() * sizeof(double);
+  CU(cudaMalloc(&B.g, bytes)); CU(cudaMalloc(&B.o, bytes)); CU(cudaMalloc(&B.w, bytes));
+  CU(cudaMemcpyAsync(B.g, h.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
+  CU(launch_orth(r, B.g, (int)n, B.o, orth_type, B.w, ctx->stream));
+  CU(cudaMemcpyAsync(h.data(), B.o, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  for (int k = 0; k < r; ++k)
+    for (int64_t j = 0; j < n; ++j) out[j + (size_t)k * ldOut] = h[(size_t)j * r + k];
+  return PPLS_OK;
+}
+
 extern "C" int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   ppls_opts opts{};

@@ -149,6 +149,7 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
 cudaError_t launch_meta_update(const DataShape& s, int J, const double* momvecs, double* L, FitState* sts, double* trace,
                                int prepare, cudaStream_t stream);
 cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream);
+cudaError_t launch_orth(int R, const double* G, int n, double* out, int orth_type, double* work, cudaStream_t stream);
 
 // ---- standard errors of the loadings (em_var.cu; variances.PPLS_simult, EM_W_multi.R:830-860) -----------
 struct VarPlan {

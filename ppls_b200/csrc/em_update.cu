@@ -128,14 +128,55 @@ __device__ void block_gram(const double* A, int n, double* S, double* scratch) {
 
 // Cyclic Jacobi eigen-decomposition of a symmetric R x R matrix (one thread).
 // On exit A is (numerically) diagonal and the columns of V are the eigenvectors.
+// Cyclic Jacobi eigen-decomposition of a symmetric R x R matrix by ONE thread: A -> diagonal, V = eigenvectors.
+// Slow (serial rotations) and robust: the fallback of block_inv_sqrt for ill-conditioned Gram matrices.
+template <int R>
+__device__ void jacobi_eig(double* A, double* V) {
+  for (int i = 0; i < R; ++i)
+    for (int j = 0; j < R; ++j) V[i * R + j] = (i == j) ? 1.0 : 0.0;
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    double off = 0.0, diag = 0.0;
+    for (int i = 0; i < R; ++i) {
+      diag += A[i * R + i] * A[i * R + i];
+      for (int j = i + 1; j < R; ++j) off += A[i * R + j] * A[i * R + j];
+    }
+    if (off <= 1e-40 * diag || off == 0.0) break;
+    for (int p = 0; p < R - 1; ++p)
+      for (int q = p + 1; q < R; ++q) {
+        const double apq = A[p * R + q];
+        if (apq == 0.0) continue;
+        const double theta = (A[q * R + q] - A[p * R + p]) / (2.0 * apq);
+        const double tt = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+        const double c = 1.0 / sqrt(tt * tt + 1.0), s = tt * c;
+        for (int k = 0; k < R; ++k) {  // A <- A J
+          const double akp = A[k * R + p], akq = A[k * R + q];
+          A[k * R + p] = c * akp - s * akq;
+          A[k * R + q] = s * akp + c * akq;
+        }
+        for (int k = 0; k < R; ++k) {  // A <- J' A
+          const double apk = A[p * R + k], aqk = A[q * R + k];
+          A[p * R + k] = c * apk - s * aqk;
+          A[q * R + k] = s * apk + c * aqk;
+        }
+        for (int k = 0; k < R; ++k) {
+          const double vkp = V[k * R + p], vkq = V[k * R + q];
+          V[k * R + p] = c * vkp - s * vkq;
+          V[k * R + q] = s * vkp + c * vkq;
+        }
+      }
+  }
+}
+
 // Mat[m] = S[m]^{-1/2} for NM symmetric positive definite R x R matrices in shared memory, by the WHOLE block
 // (every thread must call it; blockDim.x >= 64 NM).  Coupled Newton-Schulz iteration on Y0 = S / trace(S), Z0 = I:
 //   T = (3 I - Z Y) / 2,  Y <- Y T,  Z <- T Z;   Y -> (S/c)^{1/2},  Z -> (S/c)^{-1/2}   (eigenvalues of S/c lie in (0, 1])
 // One thread per matrix element, three block barriers per step; quadratic convergence once |I - Z Y| < 1, about
 // log_2.25(cond) steps before that.  Replaces the one-thread Jacobi eigen-decomposition (R = 5: ~30 us of serial
 // rotations with the matrices in local memory) by ~2 us; the Newton-Schulz polish that follows in the callers is
-// unchanged.  A matrix that does not converge (singular Gram: rank-deficient G) yields NaN, which the callers'
-// finiteness checks turn into PPLS_E_NONFINITE exactly as 1/sqrt(0) did.
+// unchanged.  The iteration is accurate to ~ cond(S) eps and stalls above cond(S) ~ 1e9, so it is trusted only when
+// it converges within NS_STEPS steps (cond(S) up to ~1e3: error <= 2e-13); otherwise one thread per matrix runs the
+// Jacobi eigen-decomposition (S^{-1/2} = V diag(lambda^{-1/2}) V'), which handles anything short of a singular
+// Gram matrix -- and that one yields inf/NaN, which the callers' finiteness checks turn into PPLS_E_NONFINITE.
 template <int R, int NM>
 __device__ void block_inv_sqrt(const double* S /*[NM][R*R]*/, double* Mat /*[NM][R*R]*/, double* work /*[NM][3][R*R]*/) {
   static_assert(R * R <= 64, "one thread per element, 64 threads per matrix");
@@ -155,7 +196,8 @@ __device__ void block_inv_sqrt(const double* S /*[NM][R*R]*/, double* Mat /*[NM]
   }
   __syncthreads();
   bool converged = false;
-  for (int it = 0; it < 100; ++it) {
+  constexpr int NS_STEPS = 16;
+  for (int it = 0; it < NS_STEPS; ++it) {
     double err = 0.0;
     if (act) {
       double zy = 0.0;
@@ -176,7 +218,19 @@ __device__ void block_inv_sqrt(const double* S /*[NM][R*R]*/, double* Mat /*[NM]
     __syncthreads();
     if (!go) { converged = true; break; }                  // the step just taken started from |I - Z Y| < 1e-13
   }
-  if (act) Mat[(size_t)m * R * R + e] = converged ? Z[e] / sqrt(c) : __longlong_as_double(0x7ff8000000000000ll);
+  if (converged) {
+    if (act) Mat[(size_t)m * R * R + e] = Z[e] / sqrt(c);
+  } else if (m < NM && e == 0) {                           // (block-uniform branch; one thread per matrix)
+    double A[R * R], V[R * R];
+    for (int x = 0; x < R * R; ++x) A[x] = S[(size_t)m * R * R + x];
+    jacobi_eig<R>(A, V);
+    for (int x = 0; x < R; ++x)
+      for (int y = 0; y < R; ++y) {
+        double sacc = 0.0;
+        for (int k = 0; k < R; ++k) sacc += V[x * R + k] * (1.0 / sqrt(A[k * R + k])) * V[y * R + k];
+        Mat[(size_t)m * R * R + x * R + y] = sacc;
+      }
+  }
   __syncthreads();
 }
 
@@ -788,25 +842,36 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   }
 }
 
-// orth(G, "SVD") alone (variances.PPLS_simult, EM_W_multi.R:831-832): out = polar factor of G [n][R].
+// orth(G, type) alone (OmicsPLS::orth as called at EM_W_multi.R:732-733 and by variances.PPLS_simult, :831-832):
+// out = polar factor of G [n][R] (SVD) or qr.Q(qr(G)) with the sign of column 1 (QR; `work` = scratch copy of G).
 template <int R>
-__global__ void __launch_bounds__(UPD_THREADS, 1) orth_only_kernel(const double* G, int n, double* out) {
+__global__ void __launch_bounds__(UPD_THREADS, 1) orth_only_kernel(const double* G, int n, double* out, int orth_type, double* work) {
   __shared__ double scratch[UPD_WARPS * 36], S[R * R], Mat[R * R];
-  orth_polar<R>(G, n, out, S, Mat, scratch);
+  if (orth_type == PPLS_ORTH_QR) {
+    for (size_t e = threadIdx.x; e < (size_t)n * R; e += UPD_THREADS) work[e] = G[e];
+    __syncthreads();
+    orth_qr<R>(work, n, out, scratch);
+  } else {
+    orth_polar<R>(G, n, out, S, Mat, scratch);
+  }
 }
-cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream) {
+cudaError_t launch_orth(int R, const double* G, int n, double* out, int orth_type, double* work, cudaStream_t stream) {
+  if (orth_type == PPLS_ORTH_QR && !work) return cudaErrorInvalidValue;
   switch (R) {
-    case 1: orth_only_kernel<1><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 2: orth_only_kernel<2><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 3: orth_only_kernel<3><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 4: orth_only_kernel<4><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 5: orth_only_kernel<5><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 6: orth_only_kernel<6><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 7: orth_only_kernel<7><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
-    case 8: orth_only_kernel<8><<<1, UPD_THREADS, 0, stream>>>(G, n, out); break;
+    case 1: orth_only_kernel<1><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 2: orth_only_kernel<2><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 3: orth_only_kernel<3><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 4: orth_only_kernel<4><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 5: orth_only_kernel<5><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 6: orth_only_kernel<6><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 7: orth_only_kernel<7><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
+    case 8: orth_only_kernel<8><<<1, UPD_THREADS, 0, stream>>>(G, n, out, orth_type, work); break;
     default: return cudaErrorInvalidValue;
   }
   return cudaGetLastError();
+}
+cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream) {
+  return launch_orth(R, G, n, out, PPLS_ORTH_SVD, nullptr, stream);
 }
 
 int update_grid_blocks(int ld) {

@@ -266,3 +266,39 @@ def test_row_sharded_two_gpus_peer_exchange():
                         "127.0.0.1", "--master-port", "29543", os.path.join(root, "tests", "mgpu_rowshard.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ROWSHARD OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("n,r", [(37, 1), (500, 2), (1201, 3), (50001, 5), (900, 8)])
+@pytest.mark.parametrize("cond", [1.0, 30.0, 1e3, 1e5])
+def test_orth_matches_the_oracle(ctx, n, r, cond):
+    """ppls_orth == OmicsPLS::orth as restated in oracle/ppls_ref.py (EM_W_multi.R:732-733), both types, for singular
+    value spreads from orthonormal to cond(G) = 1e5 (cond(G'G) = 1e10): the Newton-Schulz inverse square root of the
+    polar factor (cond(G'G) <= ~1e3) and its Jacobi fallback (beyond).  The polar factor is unique, so no sign freedom.
+    The engine forms it as G (G'G)^{-1/2}, so its forward error grows like cond(G)^2 eps (the reference's SVD: cond(G)
+    eps) -- stated in DESIGN.md; EM iterates have cond(G) of order 1-30."""
+    from oracle import ppls_ref as R
+    from ppls_b200 import orth
+    rng = np.random.default_rng(7 * n + r)
+    Q, _ = np.linalg.qr(rng.standard_normal((n, r)))
+    V, _ = np.linalg.qr(rng.standard_normal((r, r)))
+    sv = np.geomspace(1.0, 1.0 / cond, r) if r > 1 else np.array([3.0])
+    G = (Q * sv) @ V.T * 1e3
+    out = orth(G, "SVD", ctx=ctx)
+    ref = R.orth(G, "SVD")
+    tol = max(1e-12, 50 * cond * cond * 2.2e-16)
+    assert np.max(np.abs(out - ref)) < tol, (cond, np.max(np.abs(out - ref)))
+    assert np.max(np.abs(out.T @ out - np.eye(r))) < 1e-12
+    outq = orth(G, "QR", ctx=ctx)
+    refq = R.orth(G, "QR")
+    assert np.max(np.abs(outq.T @ outq - np.eye(r))) < 1e-12
+    assert np.max(np.abs(outq - refq)) < max(1e-11, 50 * cond * 2.2e-16)
+
+
+def test_orth_rejects_bad_arguments(ctx):
+    from ppls_b200 import PPLSError, orth
+    with pytest.raises(ValueError):
+        orth(np.eye(3), "LU", ctx=ctx)
+    with pytest.raises(PPLSError):
+        orth(np.ones((2, 3)), "SVD", ctx=ctx)          # more columns than rows
+    with pytest.raises(PPLSError):
+        orth(np.ones((20, 9)), "SVD", ctx=ctx)         # nr_comp > 8
