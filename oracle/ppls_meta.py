@@ -10,7 +10,8 @@ Rows must be sorted by population (the reference slices (1+Ni[i]):Ni[i+1], :455-
 Cxt, Cyu are divided by ITS OWN N before pooling (so populations weigh equally, :481-482), the sign of both pooled sums
 comes from Cxt (:481-482), and logvalue[1,] holds the FULL-data log-likelihood once per population (:548), so the first
 increment compares sum(logvalue[2,]) with nlevels times that value (:578).
-PARITY UNPINNED (see oracle/ppls_ref.py).  Only tests/, smoke() and bench.py's CPU legs may import this module.
+PARITY: meta_estep / meta_mstep are PINNED to the reference's compiled meta_Estep / meta_Mstep (oracle/_ref,
+tests/test_ref_pin.py); the R driver (meta_EMstep pooling, meta_PPLSi loop) is a restatement, unpinned.  Only tests/, smoke() and bench.py's CPU legs may import this module.
 """
 from __future__ import annotations
 

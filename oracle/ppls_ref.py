@@ -5,13 +5,17 @@ EM estimator (selbouhaddani/PPLS).  Only tests/, __graft_entry__.smoke() and the
 cpu_baseline / --impl reference legs of bench.py may import this module; the
 product path (ppls_b200/) never does.
 
-PARITY UNPINNED: the reference ships no tests, golden vectors or recorded output
-for PPLS_simult, R is not installed in the build container, and
-`orth`/`ssq` live in the un-vendored, un-versioned OmicsPLS package.  This
-restatement is therefore defended by independent cross-checks instead
-(dense `debug=TRUE` E-step, dense Gaussian log-likelihood, closed-form inverse
-identity -- see tests/test_oracle.py) and by golden vectors generated from it
-(tests/golden/, made by tests/golden/make_golden.py).
+PARITY: PARTLY PINNED.  The reference ships no tests, golden vectors or recorded output for
+PPLS_simult and R is not installed here, but its one native file,
+Package/PPLS/src/loglC.cpp, IS compiled unmodified into oracle/_ref/libppls_ref.so (stand-in
+Eigen/Rcpp headers, oracle/ref_shim/; recipe `make -C oracle ref`), and tests/test_ref_pin.py holds
+this module to it: loglc_fast == loglC_fast (1e-13, every golden case, whole traces replayed),
+logl_w == the dense Cholesky log-likelihood of loglC (1e-9), expect_m's moments == the dense
+E-step EMstepC (1e-9, one component).  UNPINNED (R code, no interpreter; `orth`/`ssq` live in the
+un-vendored, un-versioned OmicsPLS package): the R-level expression order of Expect_M / Maximiz_M,
+the normalisation quirk and orth -- defended by independent cross-checks instead (dense `debug=TRUE`
+E-step, dense Gaussian log-likelihood, closed-form inverse identity: tests/test_oracle.py).
+Golden vectors: tests/golden/, made by tests/golden/make_golden.py from this module.
 
 Reference files restated (paths relative to /root/reference/Package/PPLS):
   R/EM_W_multi.R:758-807   PPLS_simult      -> ppls_simult_loop / normalise

@@ -11,7 +11,10 @@ operation for operation, of
   Package/PPLS/R/EM_W_multi.R:229-279  PPLS           -> ppls       (explicit deflation, :270-271)
 
 "random" (:133, runif / rchisq from R's RNG) and "o2m" (OmicsPLS::o2m) start values are not restated:
-R's RNG stream and OmicsPLS are not available here.  PARITY UNPINNED (see oracle/ppls_ref.py).
+R's RNG stream and OmicsPLS are not available here ("random" is restated distributionally in ppls_b200).
+PARITY: emstepc_fast and the log-likelihood are PINNED to the reference's compiled EMstepC_fast / loglC_fast
+(oracle/_ref, tests/test_ref_pin.py: single steps at 1e-12 and the whole golden fits replayed with the reference's
+functions swapped in); the R driver around them (PPLSi / PPLS, deflation, break rule) is a restatement, unpinned.
 Only tests/, smoke() and bench.py's CPU legs may import this module.
 """
 from __future__ import annotations
