@@ -102,6 +102,14 @@ int ppls_ctx_info(const ppls_ctx* ctx, int* device, int* rank, int* world, int* 
 /* Synchronise the context's stream (for callers that time with their own clock). */
 int ppls_ctx_sync(ppls_ctx* ctx);
 
+/* Measured ceilings of the context's GPU, for roofline reporting (no counterpart in the reference; bench.py's
+ * `roofline` object): which = PPLS_PROBE_HBM_READ -> GB/s of a read-only stream over the resident dataset `d`
+ * (or over a scratch buffer of up to 8 GiB when d is NULL); PPLS_PROBE_FP64_DMMA -> TFLOP/s of back-to-back FP64
+ * tensor instructions (mma.sync m8n8k4 f64) from registers, 8 warps per SM. */
+#define PPLS_PROBE_HBM_READ  0
+#define PPLS_PROBE_FP64_DMMA 1
+int ppls_probe(ppls_ctx* ctx, const ppls_data* d, int32_t which, double* value);
+
 /* ---- data ---------------------------------------------------------------------------- */
 /* Copy this rank's rows of X (n x p, leading dimension ldX) and Y (n x q, ldY) to the
  * device and re-tile them into the engine's row-major layout.  Replaces the by-value

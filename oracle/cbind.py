@@ -29,6 +29,8 @@ def declare(L):
                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.ppls_oracle_num_threads.restype = C.c_int
+    L.ppls_oracle_set_threads.restype = None
+    L.ppls_oracle_set_threads.argtypes = [C.c_int]
     return L
 
 

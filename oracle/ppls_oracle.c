@@ -322,3 +322,12 @@ int ppls_oracle_num_threads(void) {
   return 1;
 #endif
 }
+
+/* torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU legs of bench.py restore the core count here */
+void ppls_oracle_set_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}

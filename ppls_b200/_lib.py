@@ -53,6 +53,7 @@ SIGNATURES = {
     "ppls_ctx_destroy": (C.c_int, [_vp]),
     "ppls_ctx_info": (C.c_int, [_vp, _ip, _ip, _ip, _ip]),
     "ppls_ctx_sync": (C.c_int, [_vp]),
+    "ppls_probe": (C.c_int, [_vp, _vp, C.c_int32, c_double_p]),
     "ppls_data_from_host": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _vpp]),
     "ppls_data_synthetic": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_uint64,
                                       C.POINTER(Params), _vpp]),

@@ -76,6 +76,13 @@ class Context:
     def sync(self):
         L.check(L.lib().ppls_ctx_sync(self._h))
 
+    def probe(self, which: str, data: "Optional[Data]" = None) -> float:
+        """Measured ceiling of this GPU (ppls_probe): 'hbm_read' -> GB/s of a read-only stream (over `data` when given),
+        'fp64_dmma' -> TFLOP/s of the FP64 tensor path.  For roofline reporting only."""
+        v = C.c_double(0.0)
+        L.check(L.lib().ppls_probe(self._h, data._h if data is not None else None, {"hbm_read": 0, "fp64_dmma": 1}[which], C.byref(v)))
+        return float(v.value)
+
     def close(self):
         if self._h:
             L.lib().ppls_ctx_destroy(self._h)

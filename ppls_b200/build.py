@@ -21,6 +21,7 @@ UNITS = {
     "em_var.cu": [],
     "em_batch.cu": [],
     "data.cu": ["-fmad=false"],
+    "probe.cu": [],
     "capi.cu": [],
 }
 

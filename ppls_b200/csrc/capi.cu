@@ -258,6 +258,41 @@ extern "C" int ppls_ctx_sync(ppls_ctx* ctx) {
   return PPLS_OK;
 }
 
+extern "C" int ppls_probe(ppls_ctx* ctx, const ppls_data* d, int32_t which, double* value) {
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!value) return fail(PPLS_E_INVALID, "null output pointer");
+  if (d && d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
+  double* scratch = nullptr;
+  CU(cudaMalloc(&scratch, (size_t)ctx->sm_count * 256 * sizeof(double)));
+  cudaError_t e = cudaSuccess;
+  if (which == PPLS_PROBE_FP64_DMMA) {
+    e = probe_dmma(ctx->sm_count, scratch, value, ctx->stream);
+  } else if (which == PPLS_PROBE_HBM_READ) {
+    void* buf = nullptr;
+    size_t bytes = 0;
+    if (d) { bytes = data_elems(d->s) * sizeof(double); }
+    else {
+      size_t fr = 0, tot = 0;
+      e = cudaMemGetInfo(&fr, &tot);
+      bytes = fr / 2 < ((size_t)8 << 30) ? fr / 2 : ((size_t)8 << 30);
+      if (e == cudaSuccess) e = cudaMalloc(&buf, bytes);
+      if (e == cudaSuccess) e = cudaMemsetAsync(buf, 0, bytes, ctx->stream);
+    }
+    if (e == cudaSuccess) {
+      // ~0.2 s of streaming: long enough to see the clocks the power cap allows
+      int launches = (int)(1.4e12 / (double)(bytes ? bytes : 1));
+      if (launches < 3) launches = 3;
+      if (launches > 400) launches = 400;
+      e = probe_read(d ? (const void*)d->D : buf, bytes, ctx->sm_count, launches, scratch, value, ctx->stream);
+    }
+    if (buf) cudaFree(buf);
+  } else { cudaFree(scratch); return fail(PPLS_E_INVALID, "unknown probe"); }
+  cudaFree(scratch);
+  if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("probe: ") + cudaGetErrorString(e));
+  return PPLS_OK;
+}
+
 // sum `count` doubles (device, in place) over all ranks
 static int allreduce_sum(ppls_ctx* ctx, double* dbuf, size_t count) {
   if (ctx->world == 1) return PPLS_OK;
@@ -593,6 +628,7 @@ struct ppls_fit {
   double *L = nullptr, *Lscratch = nullptr, *partials = nullptr, *momvec = nullptr, *trace = nullptr;
   FitState* st = nullptr;        // device
   FitState* st_host = nullptr;   // pinned mirror
+  int32_t* done_host = nullptr;  // pinned, mapped: set by the device when it raises `done` (FitState::done_host)
   bool finished = false;
   int32_t passes = 0;
   // timing
@@ -610,6 +646,7 @@ static void fit_free(ppls_fit* f) {
   cudaFree(f->wide_ws); cudaFree(f->upd_scratch); cudaFree(f->Gglob); cudaFree(f->Lglob); cudaFree(f->Lscratch_g); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
   cudaFree(f->st);
   if (f->st_host) cudaFreeHost(f->st_host);
+  if (f->done_host) cudaFreeHost(f->done_host);
   delete f;
 }
 
@@ -677,7 +714,9 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
   if (e == cudaSuccess) e = cudaMalloc(&f->trace, (size_t)(opts->max_steps + 1) * sizeof(double));
   if (e == cudaSuccess) e = cudaMalloc(&f->st, sizeof(FitState));
   if (e == cudaSuccess) e = cudaMallocHost(&f->st_host, sizeof(FitState));
+  if (e == cudaSuccess) e = cudaHostAlloc(&f->done_host, sizeof(int32_t), cudaHostAllocMapped);
   if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_OOM, std::string("fit workspace: ") + cudaGetErrorString(e)); }
+  *f->done_host = 0;
   std::vector<double> L;
   pack_loadings(d->s, R, init->W, init->C, L);
   FitState* h = f->st_host;
@@ -687,6 +726,10 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
   h->ssqX = ssq_deflated ? ssq_deflated[0] : d->ssq[0]; h->ssqY = ssq_deflated ? ssq_deflated[1] : d->ssq[1];
   h->Ntot = (double)d->n_total;
   h->max_steps = opts->max_steps; h->orth_type = opts->orth_type; h->R = R; h->atol = opts->atol;
+  {
+    void* dp = nullptr;     // device alias of the mapped flag (same address under unified addressing)
+    h->done_host = (cudaHostGetDevicePointer(&dp, f->done_host, 0) == cudaSuccess) ? (int32_t*)dp : nullptr;
+  }
   e = cudaMemcpyAsync(f->L, L.data(), Lbytes, cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemcpyAsync(f->st, h, sizeof(FitState), cudaMemcpyHostToDevice, ctx->stream);
   if (e == cudaSuccess) e = cudaMemsetAsync(f->trace, 0, (size_t)(opts->max_steps + 1) * sizeof(double), ctx->stream);
@@ -753,6 +796,7 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
   // passes the device may still run: it stops by itself (done flag), the host only bounds the queue
   for (int32_t i = 0; i < n_passes && !f->finished; ++i) {
     if (f->passes > f->opts.max_steps) break;
+    if (*reinterpret_cast<volatile int32_t*>(f->done_host)) break;      // the device has ended the run: stop queueing
     cudaEvent_t a = nullptr, b = nullptr;
     if (timing) { a = fit_event(f); b = fit_event(f); cudaEventRecord(a, ctx->stream); }
     cudaError_t e;
@@ -1096,10 +1140,11 @@ extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr
     if (h->status == PPLS_E_DEGENERATE) { fit_free(f); break; }     // :257-262: stop at this component, keep the earlier ones
     const int k = h->steps_done;
     std::vector<double> L(sh.ld), tr((size_t)k + 1);
-    double gram[3];
+    // Gram of the pass that ended the fit, as the update kernel recorded it (NOT momvec: the host may have queued
+    // further passes, which are no-ops on the device but re-run the in-place allreduce of momvec on world > 1)
+    const double gram[3] = {h->gram_last[0], h->gram_last[1], h->gram_last[2]};
     cudaError_t e = cudaMemcpyAsync(L.data(), f->L, sh.ld * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(tr.data(), f->trace, tr.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(gram, f->momvec + sh.ld, sizeof(gram), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(dprev + (size_t)i * sh.ld, f->L, sh.ld * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     fit_free(f);

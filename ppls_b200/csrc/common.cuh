@@ -67,7 +67,18 @@ struct FitState {
   int32_t status;        // PPLS_OK or PPLS_E_NONFINITE
   int32_t max_steps, orth_type, R, pad_;
   double atol;
+  // Gram (xx, xy, yy) of the pass that ENDED a sequential fit: the deflation of the next component reads it from
+  // here (momvec is rewritten / re-reduced by the no-op passes the host may still have queued)
+  double gram_last[3];
+  // host-mapped (pinned, zero-copy) word the device sets when it raises `done`, so that the host stops
+  // queueing passes without a stream synchronisation; 0 = none
+  int32_t* done_host;
 };
+// every kernel raises `done` through this
+__device__ __forceinline__ void raise_done(FitState* st) {
+  st->done = 1;
+  if (st->done_host) { *reinterpret_cast<volatile int32_t*>(st->done_host) = 1; __threadfence_system(); }
+}
 
 // ---- launchers (host functions defined in the .cu files) -------------------------------
 struct StreamPlan {          // how K1 is launched for one shape
@@ -201,5 +212,9 @@ struct SynthOrth {
 cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t colX0, uint32_t colY0, int R, uint64_t seed,
                          const double* Ltruth /*[ld][R]*/, const double* b, const double* t,
                          double sigE, double sigF, double sigH, cudaStream_t stream, const SynthOrth* orth = nullptr);
+
+// probe.cu: measured ceilings for bench.py's roofline lines
+cudaError_t probe_read(const void* x, size_t bytes, int sm_count, int launches, double* scratch, double* gbs, cudaStream_t stream);
+cudaError_t probe_dmma(int sm_count, double* scratch, double* tflops, cudaStream_t stream);
 
 }  // namespace ppls

@@ -151,13 +151,14 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
     if (!done && (sigX < 100 * 2.220446049250313e-16 || sigY < 100 * 2.220446049250313e-16)) {
       st->status = PPLS_E_DEGENERATE; done = true;
     }
-    if (done) { st->done = 1; st->steps_done = k; }
+    st->gram_last[0] = xx; st->gram_last[1] = xy; st->gram_last[2] = yy;
+    if (done) { raise_done(st); st->steps_done = k; }
     s_done = done ? 1 : 0;
     if (!done) {
       seq_em_scalars(st, xx, xy, yy, N, p, q);
       st->pass = k + 1;
       const bool ok = isfinite(st->b[0]) && isfinite(st->sigE) && isfinite(st->sigF) && isfinite(st->sigH) && isfinite(st->t[0]);
-      if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = k; s_done = 1; }
+      if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); st->steps_done = k; s_done = 1; }
       else seq_coefficients(st);
     }
   }

@@ -538,7 +538,7 @@ __device__ void update_body(const UpdateArgs& a) {
   __shared__ ScalarShared ssh;
   FitState* st = a.st;
   if (st->done) return;
-  if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) { s_done = d; if (d) st->done = 1; } }
+  if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) { s_done = d; if (d) raise_done(st); } }
   __syncthreads();
   if (s_done) return;
   // ---- loadings: W = orth(t(X) mu_T), C = orth(t(Y) mu_U)  (:732-733) ----------------------------
@@ -563,7 +563,7 @@ __device__ void update_body(const UpdateArgs& a) {
   if (threadIdx.x == 0) {
     bool ok = true;
     for (int e = 0; e < R * R; ++e) ok = ok && finite_d(st->WtW[e]) && finite_d(S[e]);
-    if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = st->pass - 1; }
+    if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); st->steps_done = st->pass - 1; }
   }
 }
 
@@ -575,7 +575,7 @@ __global__ void __launch_bounds__(UPD_THREADS, 1) em_update_kernel(const UpdateA
     const unsigned long long next = *a.x.epoch + 1;
     if (threadIdx.x < 32) { xchg_wait(a.x, next); if (threadIdx.x == 0) bad = *a.x.failed; }
     __syncthreads();
-    if (bad) { if (threadIdx.x == 0) { a.st->status = PPLS_E_NCCL; a.st->done = 1; } return; }
+    if (bad) { if (threadIdx.x == 0) { a.st->status = PPLS_E_NCCL; raise_done(a.st); } return; }
     double* mv = const_cast<double*>(a.momvec);
     const long long len = (long long)a.ld * R + 3 * R * R;
     for (long long e = threadIdx.x; e < len; e += blockDim.x) mv[e] = xchg_sum(a.x, next, e);
@@ -732,7 +732,7 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
       mv[e] = xchg_sum(a.x, next, e);
     grid.sync();
     if (*a.x.failed) {                                    // same on every block (raised before the sync)
-      if (blockIdx.x == 0 && threadIdx.x == 0) { st->status = PPLS_E_NCCL; st->done = 1; }
+      if (blockIdx.x == 0 && threadIdx.x == 0) { st->status = PPLS_E_NCCL; raise_done(st); }
       return;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) *a.x.epoch = next;
@@ -787,7 +787,7 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   grid.sync();
   if (rb < 0 && threadIdx.x == 0) *rowbar = 0u;             // every row block is past the barrier: arm it for the next launch
   if (*done_now) {                                        // the run ended with this pass: keep theta_k
-    if (rb < 0 && threadIdx.x == 0) st->done = 1;
+    if (rb < 0 && threadIdx.x == 0) raise_done(st);
     return;
   }
   // ---- phase 3: one Newton-Schulz step L <- L M, M = (3I - S)/2 with S = L'L --------------------------
@@ -837,7 +837,7 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
     if (threadIdx.x == 0) {
       bool ok = true;
       for (int e = 0; e < R * R; ++e) ok = ok && finite_d(S[0][e]) && finite_d(S[1][e]);
-      if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; st->steps_done = st->pass - 1; }
+      if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); st->steps_done = st->pass - 1; }
     }
   }
 }
@@ -897,7 +897,7 @@ __device__ void prepare_body(const UpdateArgs& a) {
     st->pass = 0; st->done = 0; st->steps_done = 0; st->status = PPLS_OK;
     bool ok = true;
     for (int k = 0; k < R; ++k) ok = ok && finite_d(st->aT[k]) && finite_d(st->bT[k]) && finite_d(st->aU[k]) && finite_d(st->bU[k]);
-    if (!ok) { st->status = PPLS_E_NONFINITE; st->done = 1; }
+    if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); }
   }
 }
 template <int R>

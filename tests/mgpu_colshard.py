@@ -70,7 +70,7 @@ def main():
     dist.barrier()
     dist.destroy_process_group()
     sys.stdout.flush()
-    os._exit(0 if ok else 1)
+    sys.exit(0 if ok else 1)
 
 
 if __name__ == "__main__":

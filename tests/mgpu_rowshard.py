@@ -9,7 +9,7 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
-from ppls_b200 import Context, Data, Fit, synth   # noqa: E402
+from ppls_b200 import Context, Data, Fit, PPLS, PPLS_simult, synth   # noqa: E402
 
 
 def fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, xchg):
@@ -27,11 +27,18 @@ def fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, xchg):
         f.run()
         out.append(f.result(want_mu=False))
         f.close()
+    seq = None
+    if not xchg:
+        # the sequential fit (start-value path of PPLS_simult, NCCL exchange) with several components: the deflation
+        # of component i+1 reads the Gram of the pass that ended component i, which the host has over-queued
+        seq = PPLS(None, None, 3, 15, 1e-4, "equal", data=d, loglikelihoods=False)
+        sim = PPLS_simult(None, None, 2, EMsteps=6, atol=-np.inf, data=d, want_mu=False)       # init=None: sequential start
+        seq["simult_default_start"] = sim
     d.close()
     dist.barrier()
     ctx.close()
     dist.barrier()
-    return out
+    return out + [seq]
 
 
 def main():
@@ -42,8 +49,8 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
     st = synth.start_params(truth, 3)
-    xa, xb = fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, True)
-    na, _ = fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, False)
+    xa, xb, _ = fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, True)
+    na, _, seq = fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, False)
     # every rank must hold bit-identical parameters (rank-ordered sums on every rank)
     t = torch.from_numpy(np.concatenate([xa["W"].ravel(), xa["C"].ravel(), xa["loglik"]])).to(dev)
     ts = [torch.empty_like(t) for _ in range(world)]
@@ -60,14 +67,27 @@ def main():
         errs = dict(loglik=relmax(xa["loglik"], o["loglik"]), W=relmax(xa["W"], o["W"]), C=relmax(xa["C"], o["C"]),
                     B=relmax(xa["B"], o["B"]), sigT=relmax(xa["sigT"], o["sigT"]), sigE=abs(xa["sigE"] / o["sigE"] - 1),
                     vs_nccl=relmax(xa["W"], na["W"]), repeat=relmax(xa["W"], xb["W"]))
-        ok = (same_ranks and errs["loglik"] < 1e-10 and all(v < 1e-8 for v in errs.values()) and errs["repeat"] == 0.0
-              and (world != 2 or errs["vs_nccl"] == 0.0))
+        from oracle import ppls_ref as R, ppls_seq
+        so = ppls_seq.ppls(X, Y, 3, 15, 1e-4, "equal")
+        errs["seq_steps"] = 0.0 if np.array_equal(seq["Other_output"]["Number_steps"], so["Number_steps"]) else 1.0
+        errs["seq_W"] = relmax(seq["W"], so["W"]); errs["seq_C"] = relmax(seq["C"], so["C"])
+        errs["seq_B"] = relmax(seq["B"], so["B"]); errs["seq_sig"] = float(np.max(np.abs(seq["sig"] / so["sig"] - 1)))
+        errs["seq_loglik"] = max(relmax(t, so["logvalues"][i][:t.size]) for i, t in enumerate(seq["Other_output"]["logvalues"]))
+        # PPLS_simult with its default start: the 20-step, 2-component sequential fit, then the loop
+        s2 = ppls_seq.ppls(X, Y, 2, 20, 1e-4, "equal")
+        W0, C0, B0, T0 = R.normalise(s2["W"], s2["C"], s2["B"], s2["sig"][:, 3])
+        o2 = R.ppls_simult_loop(X, Y, W0, C0, B0, s2["sig"][1, 0], s2["sig"][1, 1], s2["sig"][1, 2], T0, EMsteps=6, atol=-np.inf)
+        sim = seq["simult_default_start"]
+        errs["simult_default_W"] = relmax(sim["estimates"]["W"], o2["estimates"]["W"])
+        errs["simult_default_loglik"] = relmax(sim["loglik"], o2["loglik"])
+        ok = (same_ranks and errs["loglik"] < 1e-10 and errs["seq_loglik"] < 1e-10 and errs["simult_default_loglik"] < 1e-10
+              and all(v < 1e-8 for v in errs.values()) and errs["repeat"] == 0.0 and (world != 2 or errs["vs_nccl"] == 0.0))
         print("ROWSHARD", "OK" if ok else "FAIL", world, "ranks", (N, p, q, r), "same_on_all_ranks", same_ranks,
               {k: float(f"{v:.2e}") for k, v in errs.items()}, flush=True)
     dist.barrier()
     dist.destroy_process_group()
     sys.stdout.flush()
-    os._exit(0 if ok else 1)
+    sys.exit(0 if ok else 1)
 
 
 if __name__ == "__main__":
