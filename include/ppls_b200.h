@@ -84,6 +84,8 @@ typedef struct {
   int64_t bytes_per_pass; /* algorithmic bytes of one pass on this rank: 8*N*(p+q) */
   double  tail_ms;        /* sum over passes of what follows K1: reduce, exchange, update (K2) */
   int64_t peer_exchange;  /* 1: the moment vector travels by the one-shot peer exchange, 0: NCCL / single GPU */
+  double  stream_phase_ms;/* fused launches (one kernel per EM iteration): device-clock time of the streaming phase
+                             alone, summed; tail_ms is then the device-clock time of reduction + exchange + update */
 } ppls_timing;
 
 const char* ppls_version(void);

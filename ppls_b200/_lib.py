@@ -35,7 +35,7 @@ class Params(C.Structure):
 class Timing(C.Structure):
     _fields_ = [("stream_ms", C.c_double), ("stream_launches", C.c_int64), ("loop_ms", C.c_double),
                 ("kernel_launches", C.c_int64), ("passes", C.c_int64), ("bytes_per_pass", C.c_int64),
-                ("tail_ms", C.c_double), ("peer_exchange", C.c_int64)]
+                ("tail_ms", C.c_double), ("peer_exchange", C.c_int64), ("stream_phase_ms", C.c_double)]
 
 
 # every exported symbol of include/ppls_b200.h: name -> (restype, argtypes)

@@ -13,8 +13,10 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xcompiler", "-fno-strict-aliasing"]
 # translation unit -> extra flags.  -fmad=false where bit-exact / reference-order arithmetic matters.
 UNITS = {
-    "em_stream.cu": [],
-    **{f"em_stream_inst.cu@r{r}": [f"-DPPLS_INST_R={r}"] for r in range(1, 9)},
+    "em_stream.cu": ["-fmad=false"],
+    # -fmad=false: the fused tail evaluates the closed-form coefficients (em_update_dev.cuh); the streaming loops
+    # spell their FMAs out (fma()), so nothing hot depends on contraction
+    **{f"em_stream_inst.cu@r{r}": [f"-DPPLS_INST_R={r}", "-fmad=false"] for r in range(1, 9)},
     "em_wide.cu": [],
     "em_update.cu": ["-fmad=false"],
     "em_seq.cu": ["-fmad=false"],
@@ -45,6 +47,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "em_stream_kernel.cuh"),
+               os.path.join(CSRC, "em_update_dev.cuh"), os.path.join(CSRC, "em_tail.cuh"),
                os.path.join(HERE, "..", "include", "ppls_b200.h")]
     objs = []
     procs = []

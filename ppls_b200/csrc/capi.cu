@@ -616,6 +616,9 @@ struct ppls_fit {
   WideOffsets woff{};
   double* wide_ws = nullptr;
   double* upd_scratch = nullptr; // Gram partials of the grid update kernel
+  bool fused = false;            // one launch per EM iteration: the streaming kernel carries the reduction, the exchange and the update (em_tail.cuh)
+  double* tail_scratch = nullptr;
+  unsigned long long* clk_host = nullptr;   // pinned: device clocks of the fused launches (streaming ns, tail ns, launches)
   bool seq = false;              // sequential one-component fit (em_seq.cu) instead of the simultaneous update
   const double* prev = nullptr;  // [nprev][ld] loadings of the earlier components (device, owned by the caller)
   int nprev = 0;
@@ -643,6 +646,8 @@ static void fit_free(ppls_fit* f) {
   for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto& pr : f->ev_tail) cudaEventDestroy(pr.second);
   for (auto e : f->ev_free) cudaEventDestroy(e);
+  if (f->clk_host) cudaFreeHost(f->clk_host);
+  cudaFree(f->tail_scratch);
   cudaFree(f->wide_ws); cudaFree(f->upd_scratch); cudaFree(f->Gglob); cudaFree(f->Lglob); cudaFree(f->Lscratch_g); cudaFree(f->L); cudaFree(f->Lscratch); cudaFree(f->partials); cudaFree(f->momvec); cudaFree(f->trace);
   cudaFree(f->st);
   if (f->st_host) cudaFreeHost(f->st_host);
@@ -695,8 +700,21 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     f->wide = true;
   }
   f->veclen = momvec_len(d->s.ld, R);
+  {
+    const char* ef = getenv("PPLS_FUSE_TAIL");
+    f->fused = !f->wide && !f->cols && !seq && opts->orth_type == PPLS_ORTH_SVD && f->plan.grid >= 32 &&
+               stream_tail_fits(f->plan, d->s) && !(ef && *ef && atoi(ef) == 0) &&
+               (ctx->world == 1 || (ctx->xchg_on && (size_t)f->veclen <= XCHG_SLOT));
+  }
   const size_t Lbytes = (size_t)d->s.ld * R * sizeof(double);
   e = cudaMalloc(&f->L, Lbytes);
+  if (e == cudaSuccess && f->fused) {
+    const size_t tb = stream_tail_scratch_doubles(f->plan) * sizeof(double);
+    e = cudaMalloc(&f->tail_scratch, tb);
+    if (e == cudaSuccess) e = cudaMemsetAsync(f->tail_scratch, 0, tb, ctx->stream);     // barrier words, clocks
+    if (e == cudaSuccess) e = cudaMallocHost(&f->clk_host, 4 * sizeof(unsigned long long));
+    if (e == cudaSuccess) memset(f->clk_host, 0, 4 * sizeof(unsigned long long));
+  }
   if (e == cudaSuccess) e = cudaMalloc(&f->Lscratch, Lbytes);
   if (e == cudaSuccess && !f->wide) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
   if (e == cudaSuccess && f->wide)
@@ -761,7 +779,14 @@ static cudaEvent_t fit_event(ppls_fit* f) {
 static int fit_poll(ppls_fit* f) {
   ppls_ctx* ctx = f->ctx;
   CU(cudaMemcpyAsync(f->st_host, f->st, sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
+  if (f->fused)
+    CU(cudaMemcpyAsync(f->clk_host, f->tail_scratch + stream_tail_clock_offset(f->plan), 3 * sizeof(unsigned long long),
+                       cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
+  if (f->fused) {       // device clocks (globaltimer) of the fused launches: streaming phase | reduction + exchange + update
+    f->tm.stream_phase_ms = (double)f->clk_host[0] * 1e-6;
+    f->tm.tail_ms = (double)f->clk_host[1] * 1e-6;
+  }
   for (auto& pr : f->ev_tail) {       // .first is the K1 end event (owned by ev_k1, recycled below)
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) f->tm.tail_ms += ms;
@@ -800,6 +825,21 @@ extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_d
     cudaEvent_t a = nullptr, b = nullptr;
     if (timing) { a = fit_event(f); b = fit_event(f); cudaEventRecord(a, ctx->stream); }
     cudaError_t e;
+    if (f->fused) {
+      FusedTail ft{f->momvec, f->L, f->st, f->trace, f->tail_scratch, ctx->world > 1 ? &ctx->xdev : nullptr};
+      e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream, &ft);
+      if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+      if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("fused EM iteration: ") + cudaGetErrorString(e));
+      f->tm.peer_exchange = ctx->world > 1 ? 1 : 0;
+      f->tm.kernel_launches += 1;
+      f->passes += 1;
+      if (++since_check >= check_every) {
+        rc = fit_poll(f);
+        if (rc) return rc;
+        since_check = 0;
+      }
+      continue;
+    }
     if (f->wide) {
       e = launch_wide_project(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, ctx->stream);
       if (e == cudaSuccess && f->cols) {      // column-sharded: the N x 2r projection sums are what ranks exchange

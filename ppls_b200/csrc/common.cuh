@@ -108,9 +108,19 @@ cudaError_t launch_wide_accum(const WidePlan& w, const DataShape& s, const doubl
 
 cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* plan, const char** why);
 // One data pass: per-CTA partials -> `partials` [grid][momvec_len].
+struct XchgDev;
+// fused tail (em_tail.cuh): with `ft` the launch also reduces the partials, exchanges them (xchg != null) and runs
+// the whole update of the iteration -- one launch per EM iteration
+struct FusedTail {
+  double* momvec; double* L; FitState* st; double* trace; double* gscratch;
+  const XchgDev* xchg;
+};
+bool stream_tail_fits(const StreamPlan& plan, const DataShape& s);
+size_t stream_tail_scratch_doubles(const StreamPlan& plan);
+size_t stream_tail_clock_offset(const StreamPlan& plan);      // doubles; then u64 x 3: streaming ns, tail ns, launches
 cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const double* D,
                              const double* L, const FitState* st, double* partials,
-                             double* muT, double* muU, int write_mu, cudaStream_t stream);
+                             double* muT, double* muU, int write_mu, cudaStream_t stream, const FusedTail* ft = nullptr);
 // Sum the per-CTA partials in CTA order -> momvec.
 // One-shot peer exchange of the moment vector (multi-GPU, one node): every rank stores its reduced vector
 // straight into every peer's inbox over NVLink (peer-mapped cudaIpc memory), raises a flag there, and the

@@ -2,6 +2,7 @@
 #include "em_stream_kernel.cuh"
 #include <cstdlib>
 #include <cstdio>
+#include <cstring>
 
 namespace ppls {
 
@@ -103,6 +104,11 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
   if (grid > plan->ntiles) grid = plan->ntiles;
   if (grid < 1) grid = 1;
   plan->grid = (int)grid;
+  // the fused tail (em_tail.cuh) reuses the dynamic shared memory from offset 0: make sure it is large enough
+  if (plan->grid >= 2) {
+    const size_t tb = tail_smem_bytes(R, s.ld, plan->grid, plan->threads);
+    if (tb > plan->smem_bytes && tb <= smem_max) plan->smem_bytes = tb;
+  }
   cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)plan->smem_bytes);
   if (e != cudaSuccess) { *why = "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed"; return e; }
@@ -113,16 +119,34 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
   return cudaSuccess;
 }
 
+bool stream_tail_fits(const StreamPlan& plan, const DataShape& s) {
+  return plan.grid >= 2 && tail_smem_bytes(plan.R, s.ld, plan.grid, plan.threads) <= plan.smem_bytes;
+}
+size_t stream_tail_scratch_doubles(const StreamPlan& plan) { return tail_scratch_doubles(plan.grid, plan.R); }
+size_t stream_tail_clock_offset(const StreamPlan& plan) { return tail_clock_offset(plan.grid, plan.R); }
+
 cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const double* D,
                              const double* L, const FitState* st, double* partials,
-                             double* muT, double* muU, int write_mu, cudaStream_t stream) {
+                             double* muT, double* muU, int write_mu, cudaStream_t stream, const FusedTail* ft) {
   stream_kernel_t k = lookup_kernel(plan.R, plan.M, plan.T);
   if (!k) return cudaErrorInvalidValue;
   StreamArgs a;
+  memset(&a.tail, 0, sizeof(a.tail));
+  a.fuse = 0;
   a.D = D; a.L = L; a.st = st; a.partials = partials; a.muT = muT; a.muU = muU;
   a.n = s.n; a.ntiles = plan.ntiles; a.ld = s.ld; a.p2 = s.p2; a.q2 = s.q2;
   a.nwX = plan.nwX; a.nwY = plan.nwY; a.nstage = plan.nstage; a.write_mu = write_mu;
   a.cX = plan.cX; a.bigX = plan.bigX; a.cY = plan.cY; a.bigY = plan.bigY;
+  if (ft) {
+    // ONE launch per EM iteration: streaming pass + cross-CTA reduction + exchange + update (em_tail.cuh).  Cooperative:
+    // the tail's grid barriers need every CTA resident (1 CTA per SM, grid <= SM count).
+    a.fuse = 1;
+    a.tail.momvec = ft->momvec; a.tail.L = ft->L; a.tail.st = ft->st; a.tail.trace = ft->trace; a.tail.gscratch = ft->gscratch;
+    a.tail.p = s.p; a.tail.q = s.q; a.tail.use_x = ft->xchg ? 1 : 0;
+    if (ft->xchg) a.tail.x = *ft->xchg;
+    void* args[] = {(void*)&a};
+    return cudaLaunchCooperativeKernel((const void*)k, dim3(plan.grid), dim3(plan.threads), args, plan.smem_bytes, stream);
+  }
   k<<<plan.grid, plan.threads, plan.smem_bytes, stream>>>(a);
   return cudaGetLastError();
 }

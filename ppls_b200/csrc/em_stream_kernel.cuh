@@ -22,6 +22,7 @@
 // CTA-wide barrier inside the loop, warps drift freely within the 2-tile window.
 #pragma once
 #include "common.cuh"
+#include "em_tail.cuh"
 
 namespace ppls {
 
@@ -69,6 +70,10 @@ struct StreamArgs {
   int32_t ld, p2, q2, nwX, nwY, nstage, write_mu;
   // chunk split: X warps 0..nwX-1; the first bigX of them own cX+1 chunks, the rest cX (same for Y)
   int32_t cX, bigX, cY, bigY;
+  // fuse != 0: the launch is cooperative and goes on, after the last tile, with the cross-CTA reduction, the
+  // (multi-GPU) exchange and the whole update of the iteration (em_tail.cuh)
+  int32_t fuse;
+  TailArgs tail;
 };
 
 // Launch bound = the most threads the planner may ask for with M chunks per warp: compute warps
@@ -288,6 +293,8 @@ __global__ void __launch_bounds__(max_threads_for(R, M, T), 1) em_stream_kernel(
   constexpr int V = T * R;
   static_assert(V <= 32 && V % 2 == 0, "T*R must be even and fit one warp");
   if (a.st->done && !a.write_mu) return;         // the posterior-means pass runs after the end
+  if (a.fuse && blockIdx.x == 0 && threadIdx.x == 0)
+    reinterpret_cast<unsigned long long*>(a.tail.gscratch + tail_clock_offset(gridDim.x, R))[3] = global_timer_ns();
 
   extern __shared__ __align__(128) unsigned char smem[];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -426,6 +433,7 @@ __global__ void __launch_bounds__(max_threads_for(R, M, T), 1) em_stream_kernel(
     for (int i = 0; i < T; ++i) sum += red[(which * R + l) * 32 + i * R + k];
     out[(size_t)a.ld * R + e] = sum;
   }
+  if (a.fuse) stream_tail<R>(a.tail, a.partials, a.ld, a.p2, smem);
 }
 
 typedef void (*stream_kernel_t)(const StreamArgs);
