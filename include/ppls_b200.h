@@ -99,6 +99,15 @@ int ppls_ctx_create(ppls_ctx** out, int device);
 int ppls_nccl_unique_id(void* id_out, size_t nbytes);
 int ppls_ctx_create_dist(ppls_ctx** out, int device, int rank, int world,
                          const void* nccl_id, size_t nbytes);
+/* ONE process, SEVERAL GPUs of one node (what a single R session needs): the context drives the listed
+ * devices from the calling thread -- one stream per device, direct peer access, the same one-shot peer exchange of the
+ * moment vector as the one-process-per-GPU form, no NCCL.  ppls_data_from_host / ppls_data_synthetic then split the ROWS
+ * over the devices (shard i = rows [N i/G, N (i+1)/G), uploaded concurrently), ppls_fit_* / ppls_simult_run /
+ * ppls_loglik / ppls_data_export / ppls_data_info work on the whole; results are bitwise those of the
+ * one-process-per-GPU form.  Every device must reach every other by peer access (NVLink / NVSwitch).  The other entry
+ * points (sequential, batched, variances, meta, column-sharded) return PPLS_E_UNSUPPORTED on such a context; so do
+ * shapes that take the wide-row path.  n_devices == 1 is ppls_ctx_create. */
+int ppls_ctx_create_multi(ppls_ctx** out, const int* device_ids, int n_devices);
 int ppls_ctx_destroy(ppls_ctx* ctx);
 int ppls_ctx_info(const ppls_ctx* ctx, int* device, int* rank, int* world, int* sm_count);
 /* Synchronise the context's stream (for callers that time with their own clock). */

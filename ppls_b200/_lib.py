@@ -50,6 +50,7 @@ SIGNATURES = {
     "ppls_ctx_create": (C.c_int, [_vpp, C.c_int]),
     "ppls_nccl_unique_id": (C.c_int, [_vp, C.c_size_t]),
     "ppls_ctx_create_dist": (C.c_int, [_vpp, C.c_int, C.c_int, C.c_int, _vp, C.c_size_t]),
+    "ppls_ctx_create_multi": (C.c_int, [_vpp, _ip, C.c_int]),
     "ppls_ctx_destroy": (C.c_int, [_vp]),
     "ppls_ctx_info": (C.c_int, [_vp, _ip, _ip, _ip, _ip]),
     "ppls_ctx_sync": (C.c_int, [_vp]),

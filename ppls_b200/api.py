@@ -67,6 +67,21 @@ class Context:
         L.check(lib.ppls_ctx_info(self._h, None, None, None, C.byref(sm)))
         self.sm_count = sm.value
 
+    @classmethod
+    def multi(cls, devices) -> "Context":
+        """ONE process driving several GPUs (ppls_ctx_create_multi): rows of X and Y are split over `devices`, the moment
+        vector travels by direct peer stores; what `device = 0:7` means in the R wrapper (r/PPLS_simult_b200.R)."""
+        devs = [int(d) for d in devices]
+        self = cls.__new__(cls)
+        self._h = C.c_void_p()
+        arr = (C.c_int * len(devs))(*devs)
+        L.check(L.lib().ppls_ctx_create_multi(C.byref(self._h), arr, len(devs)))
+        self.device, self.rank, self.world, self.devices = devs[0], 0, len(devs), devs
+        sm = C.c_int()
+        L.check(L.lib().ppls_ctx_info(self._h, None, None, None, C.byref(sm)))
+        self.sm_count = sm.value
+        return self
+
     @staticmethod
     def nccl_unique_id() -> bytes:
         buf = C.create_string_buffer(L.PPLS_NCCL_ID_BYTES)

@@ -9,8 +9,10 @@
 #include <cstdlib>
 #include <cstring>
 #include <cmath>
+#include <algorithm>
 #include <string>
 #include <vector>
+#include <thread>
 #include <new>
 
 using namespace ppls;
@@ -77,6 +79,11 @@ struct ppls_ctx {
   char* xbuf = nullptr;
   void* xpeer[XCHG_MAXW] = {};
   XchgDev xdev{};
+  // single-process multi-device form (ppls_ctx_create_multi): the handle the caller holds is a GROUP whose `subs`
+  // are ordinary per-device contexts (rank = position, world = count) that reach each other's exchange blocks by
+  // direct peer access; `group` points back from a member.  No NCCL communicator exists in this form.
+  std::vector<ppls_ctx*> subs;
+  ppls_ctx* group = nullptr;
 };
 
 struct ppls_data {
@@ -89,10 +96,18 @@ struct ppls_data {
   int colshard = 0;
   int64_t p_glob = 0, q_glob = 0;          // global logical column counts
   std::vector<int32_t> xoff, yoff;         // [world+1] cumulative padded (p2 / q2) widths of the ranks' blocks
+  // multi-device context: the handle is a group of row shards (one per device, in row order)
+  std::vector<ppls_data*> shards;
+  std::vector<int64_t> shard_row0;
 };
+
+static const size_t XCHG_CTRL = 1024, XCHG_SLOT = 65536;   // exchange block: control words | inbox of 2 x world x slot doubles
 
 static int ctx_activate(const ppls_ctx* ctx) {
   if (!ctx) return fail(PPLS_E_INVALID, "null context");
+  if (!ctx->subs.empty())        // (the entry points that serve a multi-device context never get here with the group handle)
+    return fail(PPLS_E_UNSUPPORTED, "not available on a multi-device context: the row-sharded EM loop (data_from_host / synthetic / "
+                                    "export, fit_*, simult_run, loglik, orth) is; use a single-device context or one process per GPU");
   CU(cudaSetDevice(ctx->device));
   return PPLS_OK;
 }
@@ -146,7 +161,6 @@ static int allreduce_sum(ppls_ctx* ctx, double* dbuf, size_t count);
 // Peer exchange set-up: every rank allocates [control 1 KB | inbox 2 x world x slot doubles], publishes its
 // CUDA IPC handle (bytes carried as doubles through one NCCL sum) and maps every peer's block.  All ranks
 // then agree (a second sum) whether everybody succeeded; otherwise the NCCL allreduce stays in use.
-static const size_t XCHG_CTRL = 1024, XCHG_SLOT = 65536;
 static void xchg_setup(ppls_ctx* c) {
   const char* env = getenv("PPLS_XCHG");
   if (c->world < 2 || c->world > XCHG_MAXW || (env && *env && atoi(env) == 0)) return;
@@ -228,8 +242,73 @@ extern "C" int ppls_ctx_create_dist(ppls_ctx** out, int device, int rank, int wo
   return PPLS_OK;
 }
 
+// Single-process multi-device context (ppls_ctx_create(ppls_ctx**, const int* device_ids, int n)): one host
+// thread, one stream per device, direct peer access instead of CUDA IPC, the same inbox / flag exchange.
+extern "C" int ppls_ctx_create_multi(ppls_ctx** out, const int* device_ids, int n_devices) {
+  if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+  *out = nullptr;
+  if (!device_ids || n_devices < 1 || n_devices > XCHG_MAXW) return fail(PPLS_E_INVALID, "need 1..16 device ids");
+  for (int i = 0; i < n_devices; ++i)
+    for (int j = 0; j < i; ++j)
+      if (device_ids[i] == device_ids[j]) return fail(PPLS_E_INVALID, "a device is listed twice");
+  if (n_devices == 1) return ctx_create_common(out, device_ids[0]);
+  ppls_ctx* g = new (std::nothrow) ppls_ctx();
+  if (!g) return fail(PPLS_E_OOM, "host allocation failed");
+  g->device = device_ids[0]; g->rank = 0; g->world = n_devices;
+  int rc = PPLS_OK;
+  for (int i = 0; i < n_devices && rc == PPLS_OK; ++i) {
+    ppls_ctx* c = nullptr;
+    rc = ctx_create_common(&c, device_ids[i]);
+    if (rc == PPLS_OK) { c->rank = i; c->world = n_devices; c->group = g; g->subs.push_back(c); }
+  }
+  const size_t bytes = XCHG_CTRL + (size_t)2 * n_devices * XCHG_SLOT * sizeof(double);
+  for (int i = 0; i < n_devices && rc == PPLS_OK; ++i) {
+    ppls_ctx* c = g->subs[i];
+    cudaSetDevice(c->device);
+    for (int j = 0; j < n_devices && rc == PPLS_OK; ++j) {
+      if (j == i) continue;
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, c->device, g->subs[j]->device);
+      if (!can) { rc = fail(PPLS_E_UNSUPPORTED, "devices of a multi-device context must have peer access to each other"); break; }
+      cudaError_t e = cudaDeviceEnablePeerAccess(g->subs[j]->device, 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+      if (e != cudaSuccess) rc = fail(PPLS_E_CUDA, std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+    }
+    if (rc == PPLS_OK) {
+      cudaError_t e = cudaMalloc(&c->xbuf, bytes);
+      if (e == cudaSuccess) e = cudaMemset(c->xbuf, 0, bytes);
+      if (e != cudaSuccess) rc = fail(PPLS_E_OOM, std::string("exchange block: ") + cudaGetErrorString(e));
+    }
+  }
+  if (rc != PPLS_OK) { const std::string msg = g_err; ppls_ctx_destroy(g); g_err = msg; return rc; }
+  g->sm_count = g->subs[0]->sm_count;
+  for (int i = 0; i < n_devices; ++i) {
+    ppls_ctx* c = g->subs[i];
+    XchgDev& x = c->xdev;
+    memset(&x, 0, sizeof(x));
+    for (int r = 0; r < n_devices; ++r) {
+      char* base = g->subs[r]->xbuf;
+      x.flags[r] = (unsigned long long*)base;
+      x.inbox[r] = (double*)(base + XCHG_CTRL);
+    }
+    x.epoch = (unsigned long long*)(c->xbuf + 512);
+    x.counter = (unsigned int*)(c->xbuf + 520);
+    x.failed = (int*)(c->xbuf + 524);
+    x.rank = i; x.world = n_devices; x.slot = (long long)XCHG_SLOT;
+    c->xchg_on = true;
+  }
+  *out = g;
+  return PPLS_OK;
+}
+
 extern "C" int ppls_ctx_destroy(ppls_ctx* ctx) {
   if (!ctx) return PPLS_OK;
+  if (!ctx->subs.empty()) {
+    for (ppls_ctx* c : ctx->subs) if (c) { cudaSetDevice(c->device); if (c->stream) cudaStreamSynchronize(c->stream); }
+    for (ppls_ctx* c : ctx->subs) ppls_ctx_destroy(c);
+    delete ctx;
+    return PPLS_OK;
+  }
   cudaSetDevice(ctx->device);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (int r = 0; r < XCHG_MAXW; ++r)
@@ -252,6 +331,10 @@ extern "C" int ppls_ctx_info(const ppls_ctx* ctx, int* device, int* rank, int* w
 }
 
 extern "C" int ppls_ctx_sync(ppls_ctx* ctx) {
+  if (ctx && !ctx->subs.empty()) {
+    for (ppls_ctx* c : ctx->subs) { int r = ppls_ctx_sync(c); if (r) return r; }
+    return PPLS_OK;
+  }
   int rc = ctx_activate(ctx);
   if (rc) return rc;
   CU(cudaStreamSynchronize(ctx->stream));
@@ -259,6 +342,7 @@ extern "C" int ppls_ctx_sync(ppls_ctx* ctx) {
 }
 
 extern "C" int ppls_probe(ppls_ctx* ctx, const ppls_data* d, int32_t which, double* value) {
+  if (ctx && !ctx->subs.empty()) { ctx = ctx->subs[0]; if (d && !d->shards.empty()) d = d->shards[0]; }
   int rc = ctx_activate(ctx);
   if (rc) return rc;
   if (!value) return fail(PPLS_E_INVALID, "null output pointer");
@@ -296,6 +380,9 @@ extern "C" int ppls_probe(ppls_ctx* ctx, const ppls_data* d, int32_t which, doub
 // sum `count` doubles (device, in place) over all ranks
 static int allreduce_sum(ppls_ctx* ctx, double* dbuf, size_t count) {
   if (ctx->world == 1) return PPLS_OK;
+  if (!ctx->comm)
+    return fail(PPLS_E_UNSUPPORTED, "this path needs a collective: on a multi-device context only the row-sharded EM loop "
+                                    "is available (use one process per GPU, ppls_ctx_create_dist, for the others)");
   int nr = g_nccl.AllReduce(dbuf, dbuf, count, kNcclFloat64, kNcclSum, ctx->comm, ctx->stream);
   if (nr) return nccl_fail(nr, "ncclAllReduce");
   return PPLS_OK;
@@ -323,7 +410,8 @@ static int data_finalize(ppls_ctx* ctx, ppls_data* d) {
   if (e != cudaSuccess) { cudaFree(scratch); return fail(PPLS_E_CUDA, std::string("ssq kernel: ") + cudaGetErrorString(e)); }
   double nloc = (double)d->s.n;
   e = cudaMemcpyAsync(ctx->d_small + 2, &nloc, sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
-  int rc = (e == cudaSuccess) ? allreduce_sum(ctx, ctx->d_small, 3) : fail(PPLS_E_CUDA, cudaGetErrorString(e));
+  // (member of a multi-device context: local sums only -- the group adds its shards' sums on the host, in rank order)
+  int rc = (e != cudaSuccess) ? fail(PPLS_E_CUDA, cudaGetErrorString(e)) : (ctx->group ? PPLS_OK : allreduce_sum(ctx, ctx->d_small, 3));
   double h[3] = {0, 0, 0};
   if (!rc) {
     e = cudaMemcpyAsync(h, ctx->d_small, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
@@ -364,12 +452,69 @@ static int data_finalize(ppls_ctx* ctx, ppls_data* d) {
 
 static int data_from_host_impl(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
                                int64_t n, int64_t p, int64_t q, int colshard, ppls_data** out);
+
+static bool is_group(const ppls_ctx* c) { return c && !c->subs.empty(); }
+static int no_group(const ppls_ctx* c, const char* what) {
+  if (is_group(c))
+    return fail(PPLS_E_UNSUPPORTED, std::string(what) + ": not available on a multi-device context (the row-sharded EM loop is; "
+                                    "use a single-device context or one process per GPU for this entry point)");
+  return PPLS_OK;
+}
+
+// Multi-device context: shard i holds rows [N i / G, N (i+1) / G).  `make(i, row0, rows, &shard)` builds one shard on
+// member i; the shards are built by one host thread EACH (uploads from pageable memory block their thread, so this is
+// what lets the G copies run concurrently), then ||X||^2, ||Y||^2 and N are added on the host in rank order.
+template <class Make>
+static int group_data_build(ppls_ctx* g, int64_t n, Make make, ppls_data** out) {
+  const int G = (int)g->subs.size();
+  if (n < G) return fail(PPLS_E_INVALID, "fewer rows than devices");
+  ppls_data* d = new (std::nothrow) ppls_data();
+  if (!d) return fail(PPLS_E_OOM, "host allocation failed");
+  d->ctx = g;
+  d->shards.assign(G, nullptr); d->shard_row0.assign(G + 1, 0);
+  for (int i = 0; i <= G; ++i) d->shard_row0[i] = n * i / G;
+  std::vector<int> rcs(G, PPLS_OK);
+  std::vector<std::string> errs(G);
+  std::vector<std::thread> th;
+  for (int i = 0; i < G; ++i)
+    th.emplace_back([&, i] {
+      rcs[i] = make(i, d->shard_row0[i], d->shard_row0[i + 1] - d->shard_row0[i], &d->shards[i]);
+      if (rcs[i]) errs[i] = g_err;           // (thread-local message of the worker)
+    });
+  for (auto& t : th) t.join();
+  for (int i = 0; i < G; ++i)
+    if (rcs[i]) {
+      const int rc = rcs[i];
+      const std::string msg = "device " + std::to_string(g->subs[i]->device) + ": " + errs[i];
+      ppls_data_destroy(d);
+      return fail(rc, msg);
+    }
+  double sx = 0.0, sy = 0.0;
+  for (int i = 0; i < G; ++i) { sx += d->shards[i]->ssq[0]; sy += d->shards[i]->ssq[1]; }
+  for (int i = 0; i < G; ++i) { d->shards[i]->ssq[0] = sx; d->shards[i]->ssq[1] = sy; d->shards[i]->n_total = n; }
+  d->s = d->shards[0]->s; d->s.n = n;
+  d->ssq[0] = sx; d->ssq[1] = sy; d->n_total = n;
+  d->p_glob = d->s.p; d->q_glob = d->s.q;
+  *out = d;
+  return PPLS_OK;
+}
+
 extern "C" int ppls_data_from_host(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
                                    int64_t n, int64_t p, int64_t q, ppls_data** out) {
+  if (is_group(ctx)) {
+    if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+    *out = nullptr;
+    if (!X || !Y) return fail(PPLS_E_INVALID, "null X or Y");
+    if (ldX < n || ldY < n) return fail(PPLS_E_INVALID, "leading dimension smaller than the row count");
+    return group_data_build(ctx, n, [&](int i, int64_t row0, int64_t rows, ppls_data** sh) {
+      return data_from_host_impl(ctx->subs[i], X + row0, ldX, Y + row0, ldY, rows, p, q, 0, sh);
+    }, out);
+  }
   return data_from_host_impl(ctx, X, ldX, Y, ldY, n, p, q, 0, out);
 }
 extern "C" int ppls_data_from_host_cols(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
                                         int64_t n, int64_t p_local, int64_t q_local, ppls_data** out) {
+  { int rg = no_group(ctx, "ppls_data_from_host_cols"); if (rg) return rg; }
   return data_from_host_impl(ctx, X, ldX, Y, ldY, n, p_local, q_local, 1, out);
 }
 static int data_from_host_impl(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
@@ -459,11 +604,19 @@ static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p
                                const HostOrth* ho = nullptr);
 extern "C" int ppls_data_synthetic(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r,
                                    uint64_t seed, const ppls_params* truth, ppls_data** out) {
+  if (is_group(ctx)) {
+    if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+    *out = nullptr;
+    return group_data_build(ctx, n, [&](int i, int64_t lo, int64_t rows, ppls_data** sh) {
+      return data_synthetic_impl(ctx->subs[i], rows, row0 + lo, p, q, 0, 0, 0, r, seed, truth, sh);
+    }, out);
+  }
   return data_synthetic_impl(ctx, n, row0, p, q, 0, 0, 0, r, seed, truth, out);
 }
 extern "C" int ppls_data_synthetic_cols(ppls_ctx* ctx, int64_t n, int64_t p_local, int64_t q_local, int64_t colX0,
                                         int64_t colY0, int32_t r, uint64_t seed, const ppls_params* truth_local,
                                         ppls_data** out) {
+  { int rg = no_group(ctx, "ppls_data_synthetic_cols"); if (rg) return rg; }
   return data_synthetic_impl(ctx, n, 0, p_local, q_local, colX0, colY0, 1, r, seed, truth_local, out);
 }
 static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int64_t colX0, int64_t colY0,
@@ -527,6 +680,7 @@ static int data_synthetic_impl(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p
 extern "C" int ppls_data_simulc(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t p, int64_t q, int32_t r, int32_t nx, int32_t ny,
                                 uint64_t seed, const ppls_params* truth, const double* P_Yosc, const double* P_Xosc,
                                 const double* sigTo, const double* sigUo, ppls_data** out) {
+  { int rg = no_group(ctx, "ppls_data_simulc"); if (rg) return rg; }
   if (nx < 0 || ny < 0 || nx > MAXR || ny > MAXR) return fail(PPLS_E_INVALID, "orthogonal components outside 0..8");
   if ((nx > 0 && (!P_Yosc || !sigTo)) || (ny > 0 && (!P_Xosc || !sigUo))) return fail(PPLS_E_INVALID, "null orthogonal loadings");
   HostOrth ho;
@@ -536,6 +690,18 @@ extern "C" int ppls_data_simulc(ppls_ctx* ctx, int64_t n, int64_t row0, int64_t 
 
 extern "C" int ppls_data_export(ppls_ctx* ctx, const ppls_data* d, int64_t row0, int64_t n, double* X, int64_t ldX,
                                 double* Y, int64_t ldY) {
+  if (d && !d->shards.empty()) {
+    if (!X || !Y) return fail(PPLS_E_INVALID, "null argument");
+    if (row0 < 0 || n < 0 || row0 + n > d->s.n || ldX < n || ldY < n) return fail(PPLS_E_INVALID, "row range / leading dimension");
+    for (size_t i = 0; i < d->shards.size(); ++i) {       // the part of [row0, row0 + n) that lives on shard i
+      const int64_t lo = std::max(row0, d->shard_row0[i]), hi = std::min(row0 + n, d->shard_row0[i + 1]);
+      if (hi <= lo) continue;
+      int rc = ppls_data_export(d->shards[i]->ctx, d->shards[i], lo - d->shard_row0[i], hi - lo, X + (lo - row0), ldX,
+                                Y + (lo - row0), ldY);
+      if (rc) return rc;
+    }
+    return PPLS_OK;
+  }
   int rc = ctx_activate(ctx);
   if (rc) return rc;
   if (!d || !X || !Y) return fail(PPLS_E_INVALID, "null argument");
@@ -580,6 +746,8 @@ extern "C" int ppls_data_info(const ppls_data* d, int64_t* n, int64_t* p, int64_
 
 extern "C" int ppls_data_destroy(ppls_data* d) {
   if (!d) return PPLS_OK;
+  for (ppls_data* sh : d->shards) ppls_data_destroy(sh);
+  d->shards.clear();
   if (d->ctx) cudaSetDevice(d->ctx->device);
   if (d->D) cudaFree(d->D);
   delete d;
@@ -634,6 +802,7 @@ struct ppls_fit {
   int32_t* done_host = nullptr;  // pinned, mapped: set by the device when it raises `done` (FitState::done_host)
   bool finished = false;
   int32_t passes = 0;
+  std::vector<ppls_fit*> parts;  // multi-device context: one fit per device, driven in lockstep
   // timing
   std::vector<cudaEvent_t> ev_free;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_k1, ev_tail;
@@ -642,6 +811,8 @@ struct ppls_fit {
 
 static void fit_free(ppls_fit* f) {
   if (!f) return;
+  for (ppls_fit* part : f->parts) fit_free(part);
+  f->parts.clear();
   if (f->ctx) cudaSetDevice(f->ctx->device);
   for (auto& pr : f->ev_k1) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   for (auto& pr : f->ev_tail) cudaEventDestroy(pr.second);
@@ -659,6 +830,23 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
                            bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out);
 extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
                                ppls_fit** out) {
+  if (is_group(ctx)) {
+    if (!out) return fail(PPLS_E_INVALID, "null output pointer");
+    *out = nullptr;
+    if (!d || !opts) return fail(PPLS_E_INVALID, "null data or options");
+    if (d->ctx != ctx || d->shards.size() != ctx->subs.size()) return fail(PPLS_E_INVALID, "data belongs to another context");
+    ppls_fit* f = new (std::nothrow) ppls_fit();
+    if (!f) return fail(PPLS_E_OOM, "host allocation failed");
+    f->ctx = ctx; f->data = d; f->opts = *opts; f->R = opts->r;
+    for (size_t i = 0; i < ctx->subs.size(); ++i) {
+      ppls_fit* part = nullptr;
+      int rc = fit_create_impl(ctx->subs[i], d->shards[i], opts, init, false, nullptr, 0, nullptr, &part);
+      if (rc) { const std::string msg = g_err; fit_free(f); g_err = msg; return rc; }
+      f->parts.push_back(part);
+    }
+    *out = f;
+    return PPLS_OK;
+  }
   return fit_create_impl(ctx, d, opts, init, false, nullptr, 0, nullptr, out);
 }
 static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
@@ -700,6 +888,11 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     f->wide = true;
   }
   f->veclen = momvec_len(d->s.ld, R);
+  if (ctx->group && (f->wide || f->cols || seq || (size_t)f->veclen > XCHG_SLOT)) {
+    fit_free(f);
+    return fail(PPLS_E_UNSUPPORTED, "multi-device context: this shape takes the wide-row path, which exchanges through NCCL -- "
+                                    "use one process per GPU (ppls_ctx_create_dist)");
+  }
   {
     const char* ef = getenv("PPLS_FUSE_TAIL");
     f->fused = !f->wide && !f->cols && !seq && opts->orth_type == PPLS_ORTH_SVD && f->plan.grid >= 32 &&
@@ -778,6 +971,7 @@ static cudaEvent_t fit_event(ppls_fit* f) {
 // read the control block back (after a stream sync) and fold finished timings
 static int fit_poll(ppls_fit* f) {
   ppls_ctx* ctx = f->ctx;
+  { int rc0 = ctx_activate(ctx); if (rc0) return rc0; }
   CU(cudaMemcpyAsync(f->st_host, f->st, sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
   if (f->fused)
     CU(cudaMemcpyAsync(f->clk_host, f->tail_scratch + stream_tail_clock_offset(f->plan), 3 * sizeof(unsigned long long),
@@ -805,111 +999,165 @@ static int fit_poll(ppls_fit* f) {
   return PPLS_OK;
 }
 
-extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_done, int32_t* finished) {
-  if (!f) return fail(PPLS_E_INVALID, "null fit handle");
+// Enqueue ONE data pass of fit `f` on its device (no synchronisation).
+static int fit_enqueue_pass(ppls_fit* f) {
   int rc = ctx_activate(f->ctx);
   if (rc) return rc;
   ppls_ctx* ctx = f->ctx;
   const DataShape& s = f->data->s;
   const bool timing = (f->opts.flags & PPLS_F_TIMING) != 0;
-  int check_every = f->opts.check_every > 0 ? f->opts.check_every : 16;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  if (timing) { ev0 = fit_event(f); ev1 = fit_event(f); cudaEventRecord(ev0, ctx->stream); }
-  // row-sharded multi-GPU, fused-kernel path: the moment vector travels by peer stores (em_update.cu)
+  // row-sharded multi-GPU, fused-kernel path: the moment vector travels by peer stores (em_tail.cuh / em_update.cu)
   const bool use_x = ctx->xchg_on && !f->wide && !f->cols && !f->seq && (size_t)f->veclen <= XCHG_SLOT;
-  int32_t since_check = 0;
-  // passes the device may still run: it stops by itself (done flag), the host only bounds the queue
-  for (int32_t i = 0; i < n_passes && !f->finished; ++i) {
-    if (f->passes > f->opts.max_steps) break;
-    if (*reinterpret_cast<volatile int32_t*>(f->done_host)) break;      // the device has ended the run: stop queueing
-    cudaEvent_t a = nullptr, b = nullptr;
-    if (timing) { a = fit_event(f); b = fit_event(f); cudaEventRecord(a, ctx->stream); }
-    cudaError_t e;
-    if (f->fused) {
-      FusedTail ft{f->momvec, f->L, f->st, f->trace, f->tail_scratch, ctx->world > 1 ? &ctx->xdev : nullptr};
-      e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream, &ft);
-      if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
-      if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("fused EM iteration: ") + cudaGetErrorString(e));
-      f->tm.peer_exchange = ctx->world > 1 ? 1 : 0;
-      f->tm.kernel_launches += 1;
-      f->passes += 1;
-      if (++since_check >= check_every) {
-        rc = fit_poll(f);
-        if (rc) return rc;
-        since_check = 0;
-      }
-      continue;
-    }
-    if (f->wide) {
-      e = launch_wide_project(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, ctx->stream);
-      if (e == cudaSuccess && f->cols) {      // column-sharded: the N x 2r projection sums are what ranks exchange
-        rc = allreduce_sum(ctx, f->wide_ws + f->woff.proj, (size_t)s.n * 2 * f->R);
-        if (rc) return rc;
-      }
-      if (e == cudaSuccess) e = launch_wide_accum(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, f->momvec, ctx->stream);
-      if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
-      f->tm.kernel_launches += 3;      // 5 launches in this branch, 2 in the other; +3 more below
-    } else {
-      e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream);
-      if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
-      if (e == cudaSuccess && use_x) e = launch_xsend(f->partials, f->plan.grid, f->veclen, ctx->xdev, f->st, ctx->stream);
-      else if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
-    }
-    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
-    if (f->cols) {
-      // global G = every rank's rows (zeros elsewhere) summed; the Gram tail is identical on all ranks
-      // (it comes from the exchanged projections), so rank 0 alone contributes it
-      const int R_ = f->R, ne = s.ld * R_;
-      const size_t glen = (size_t)f->sg.ld * R_, tail = (size_t)3 * R_ * R_;
-      e = cudaMemsetAsync(f->Gglob, 0, (glen + tail) * sizeof(double), ctx->stream);
-      if (e == cudaSuccess) rows_local_to_global<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->momvec, f->Gglob, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
-      if (e == cudaSuccess && ctx->rank == 0)
-        e = cudaMemcpyAsync(f->Gglob + glen, f->momvec + (size_t)s.ld * R_, tail * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
-      if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("column-sharded gather: ") + cudaGetErrorString(e));
-      rc = allreduce_sum(ctx, f->Gglob, glen + tail);
-      if (rc) return rc;
-      e = launch_em_update(f->sg, R_, f->Gglob, f->Lglob, f->Lscratch_g, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
-      if (e == cudaSuccess) rows_global_to_local<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->Lglob, f->L, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
-      if (e == cudaSuccess) e = cudaGetLastError();
-      f->tm.kernel_launches += 2;
-    } else if (use_x) {
-      e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream, &ctx->xdev);
-    } else {
-      rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
-      if (rc) return rc;
-      if (f->seq) e = launch_seq_update(s, f->momvec, f->L, f->st, f->trace, f->prev, f->nprev, 0, ctx->stream);
-      else e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
-    }
-    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
-    if (timing) { cudaEvent_t c = fit_event(f); cudaEventRecord(c, ctx->stream); f->ev_tail.emplace_back(b, c); }
-    f->tm.peer_exchange = use_x ? 1 : 0;
-    f->tm.kernel_launches += 3;
+  cudaEvent_t a = nullptr, b = nullptr;
+  if (timing) { a = fit_event(f); b = fit_event(f); cudaEventRecord(a, ctx->stream); }
+  cudaError_t e;
+  if (f->fused) {
+    FusedTail ft{f->momvec, f->L, f->st, f->trace, f->tail_scratch, ctx->world > 1 ? &ctx->xdev : nullptr};
+    e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream, &ft);
+    if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("fused EM iteration: ") + cudaGetErrorString(e));
+    f->tm.peer_exchange = ctx->world > 1 ? 1 : 0;
+    f->tm.kernel_launches += 1;
     f->passes += 1;
-    if (++since_check >= check_every) {
-      rc = fit_poll(f);
+    return PPLS_OK;
+  }
+  if (f->wide) {
+    e = launch_wide_project(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, ctx->stream);
+    if (e == cudaSuccess && f->cols) {      // column-sharded: the N x 2r projection sums are what ranks exchange
+      rc = allreduce_sum(ctx, f->wide_ws + f->woff.proj, (size_t)s.n * 2 * f->R);
       if (rc) return rc;
-      since_check = 0;
     }
+    if (e == cudaSuccess) e = launch_wide_accum(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, f->momvec, ctx->stream);
+    if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+    f->tm.kernel_launches += 3;      // 5 launches in this branch, 2 in the other; +3 more below
+  } else {
+    e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, nullptr, nullptr, 0, ctx->stream);
+    if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+    if (e == cudaSuccess && use_x) e = launch_xsend(f->partials, f->plan.grid, f->veclen, ctx->xdev, f->st, ctx->stream);
+    else if (e == cudaSuccess) e = launch_reduce_partials(f->partials, f->plan.grid, f->veclen, f->momvec, f->st, ctx->stream);
   }
-  if (timing) cudaEventRecord(ev1, ctx->stream);
-  rc = fit_poll(f);
-  if (rc) return rc;
-  if (timing) {
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, ev0, ev1) == cudaSuccess) f->tm.loop_ms += ms;
-    f->ev_free.push_back(ev0); f->ev_free.push_back(ev1);
+  if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("streaming pass: ") + cudaGetErrorString(e));
+  if (f->cols) {
+    // global G = every rank's rows (zeros elsewhere) summed; the Gram tail is identical on all ranks
+    // (it comes from the exchanged projections), so rank 0 alone contributes it
+    const int R_ = f->R, ne = s.ld * R_;
+    const size_t glen = (size_t)f->sg.ld * R_, tail = (size_t)3 * R_ * R_;
+    e = cudaMemsetAsync(f->Gglob, 0, (glen + tail) * sizeof(double), ctx->stream);
+    if (e == cudaSuccess) rows_local_to_global<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->momvec, f->Gglob, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
+    if (e == cudaSuccess && ctx->rank == 0)
+      e = cudaMemcpyAsync(f->Gglob + glen, f->momvec + (size_t)s.ld * R_, tail * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream);
+    if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("column-sharded gather: ") + cudaGetErrorString(e));
+    rc = allreduce_sum(ctx, f->Gglob, glen + tail);
+    if (rc) return rc;
+    e = launch_em_update(f->sg, R_, f->Gglob, f->Lglob, f->Lscratch_g, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
+    if (e == cudaSuccess) rows_global_to_local<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->Lglob, f->L, s.p2, s.q2, f->xoff, f->yoff_abs, R_);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    f->tm.kernel_launches += 2;
+  } else if (use_x) {
+    e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream, &ctx->xdev);
+  } else {
+    rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
+    if (rc) return rc;
+    if (f->seq) e = launch_seq_update(s, f->momvec, f->L, f->st, f->trace, f->prev, f->nprev, 0, ctx->stream);
+    else e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
   }
-  // passes actually executed on the device (later launches were no-ops once done was set)
-  const int32_t dev_passes = f->st_host->done ? f->st_host->steps_done + 1 : f->st_host->pass;
-  f->tm.passes = dev_passes;
-  if (passes_done) *passes_done = dev_passes;
-  if (finished) *finished = f->finished ? 1 : 0;
+  if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
+  if (timing) { cudaEvent_t c = fit_event(f); cudaEventRecord(c, ctx->stream); f->ev_tail.emplace_back(b, c); }
+  f->tm.peer_exchange = use_x ? 1 : 0;
+  f->tm.kernel_launches += 3;
+  f->passes += 1;
   return PPLS_OK;
 }
 
+// A fit on a multi-device context is one part per device, driven in lockstep by this host thread: pass k is
+// enqueued on every device before pass k+1 (the launches are asynchronous; the kernels of a pass meet in the peer
+// exchange).  A plain fit is its own single part.
+static ppls_fit** fit_parts(ppls_fit* f, ppls_fit** self, size_t* n) {
+  if (f->parts.empty()) { *self = f; *n = 1; return self; }
+  *n = f->parts.size();
+  return f->parts.data();
+}
+
+extern "C" int ppls_fit_iterate(ppls_fit* f, int32_t n_passes, int32_t* passes_done, int32_t* finished) {
+  if (!f) return fail(PPLS_E_INVALID, "null fit handle");
+  ppls_fit* self = nullptr;
+  size_t np = 0;
+  ppls_fit** parts = fit_parts(f, &self, &np);
+  ppls_fit* lead = parts[0];
+  int rc;
+  const bool timing = (lead->opts.flags & PPLS_F_TIMING) != 0;
+  const int check_every = lead->opts.check_every > 0 ? lead->opts.check_every : 16;
+  std::vector<cudaEvent_t> ev0(np, nullptr), ev1(np, nullptr);
+  if (timing)
+    for (size_t i = 0; i < np; ++i) {
+      rc = ctx_activate(parts[i]->ctx);
+      if (rc) return rc;
+      ev0[i] = fit_event(parts[i]); ev1[i] = fit_event(parts[i]);
+      cudaEventRecord(ev0[i], parts[i]->ctx->stream);
+    }
+  int32_t since_check = 0;
+  // passes the device may still run: it stops by itself (done flag), the host only bounds the queue
+  for (int32_t i = 0; i < n_passes && !lead->finished; ++i) {
+    if (lead->passes > lead->opts.max_steps) break;
+    if (*reinterpret_cast<volatile int32_t*>(lead->done_host)) break;      // the device has ended the run: stop queueing
+    for (size_t k = 0; k < np; ++k) {
+      rc = fit_enqueue_pass(parts[k]);
+      if (rc) return rc;
+    }
+    if (++since_check >= check_every) {
+      for (size_t k = 0; k < np; ++k) { rc = fit_poll(parts[k]); if (rc) return rc; }
+      since_check = 0;
+    }
+  }
+  for (size_t k = 0; k < np; ++k) {
+    rc = ctx_activate(parts[k]->ctx);
+    if (rc) return rc;
+    if (timing) cudaEventRecord(ev1[k], parts[k]->ctx->stream);
+  }
+  for (size_t k = 0; k < np; ++k) {
+    ppls_fit* g = parts[k];
+    rc = ctx_activate(g->ctx);
+    if (rc) return rc;
+    rc = fit_poll(g);
+    if (rc) return rc;
+    if (timing) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, ev0[k], ev1[k]) == cudaSuccess) g->tm.loop_ms += ms;
+      g->ev_free.push_back(ev0[k]); g->ev_free.push_back(ev1[k]);
+    }
+    // passes actually executed on the device (later launches were no-ops once done was set)
+    g->tm.passes = g->st_host->done ? g->st_host->steps_done + 1 : g->st_host->pass;
+  }
+  if (f != lead) { f->finished = lead->finished; f->passes = lead->passes; }
+  if (passes_done) *passes_done = (int32_t)lead->tm.passes;
+  if (finished) *finished = lead->finished ? 1 : 0;
+  return PPLS_OK;
+}
+
+static int fit_result_impl(ppls_fit* f, ppls_params* est, double* loglik, int32_t* steps_done, double* moments,
+                           double* mu_T, double* mu_U, int64_t ldmu);
 extern "C" int ppls_fit_result(ppls_fit* f, ppls_params* est, double* loglik, int32_t* steps_done, double* moments,
                                double* mu_T, double* mu_U) {
   if (!f) return fail(PPLS_E_INVALID, "null fit handle");
+  if (!f->parts.empty()) {
+    // parameters, trace and moments are identical on every device (rank-ordered sums): take them from the first;
+    // the posterior means are per row: every device writes its rows of the caller's n x r arrays
+    if ((mu_T == nullptr) != (mu_U == nullptr)) return fail(PPLS_E_INVALID, "pass both mu_T and mu_U or neither");
+    int rc = fit_result_impl(f->parts[0], est, loglik, steps_done, moments, nullptr, nullptr, 0);
+    if (rc || !mu_T) return rc;
+    const int64_t N = f->data->s.n;
+    for (size_t i = 0; i < f->parts.size(); ++i) {
+      const int64_t r0 = f->data->shard_row0[i];
+      rc = fit_result_impl(f->parts[i], nullptr, nullptr, nullptr, nullptr, mu_T + r0, mu_U + r0, N);
+      if (rc) return rc;
+    }
+    return PPLS_OK;
+  }
+  return fit_result_impl(f, est, loglik, steps_done, moments, mu_T, mu_U, f->data->s.n);
+}
+// mu_T / mu_U: this fit's rows, column-major with leading dimension ldmu
+static int fit_result_impl(ppls_fit* f, ppls_params* est, double* loglik, int32_t* steps_done, double* moments,
+                           double* mu_T, double* mu_U, int64_t ldmu) {
   int rc = ctx_activate(f->ctx);
   if (rc) return rc;
   ppls_ctx* ctx = f->ctx;
@@ -954,8 +1202,8 @@ extern "C" int ppls_fit_result(ppls_fit* f, ppls_params* est, double* loglik, in
     CU(cudaStreamSynchronize(ctx->stream));
     for (int64_t i = 0; i < s.n; ++i)
       for (int k = 0; k < R; ++k) {
-        mu_T[i + (size_t)k * s.n] = mu[(size_t)i * R + k];
-        mu_U[i + (size_t)k * s.n] = mu[(size_t)(npad + i) * R + k];
+        mu_T[i + (size_t)k * ldmu] = mu[(size_t)i * R + k];
+        mu_U[i + (size_t)k * ldmu] = mu[(size_t)(npad + i) * R + k];
       }
   } else if (mu_T) {
     // One more pass with the final parameters writes the posterior means (EM_W_multi.R:802).
@@ -963,8 +1211,12 @@ extern "C" int ppls_fit_result(ppls_fit* f, ppls_params* est, double* loglik, in
     CU(cudaMalloc(&dmu, (size_t)2 * s.n * R * sizeof(double)));
     cudaError_t e = launch_em_stream(f->plan, s, f->data->D, f->L, f->st, f->partials, dmu, dmu + (size_t)s.n * R, 1, ctx->stream);
     f->tm.kernel_launches += 1;
-    if (e == cudaSuccess) e = cudaMemcpyAsync(mu_T, dmu, (size_t)s.n * R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(mu_U, dmu + (size_t)s.n * R, (size_t)s.n * R * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(mu_T, (size_t)ldmu * sizeof(double), dmu, (size_t)s.n * sizeof(double), (size_t)s.n * sizeof(double), (size_t)R,
+                            cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess)
+      e = cudaMemcpy2DAsync(mu_U, (size_t)ldmu * sizeof(double), dmu + (size_t)s.n * R, (size_t)s.n * sizeof(double),
+                            (size_t)s.n * sizeof(double), (size_t)R, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cudaFree(dmu);
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("posterior-means pass: ") + cudaGetErrorString(e));
@@ -974,6 +1226,16 @@ extern "C" int ppls_fit_result(ppls_fit* f, ppls_params* est, double* loglik, in
 
 extern "C" int ppls_fit_timing(const ppls_fit* f, ppls_timing* out) {
   if (!f || !out) return fail(PPLS_E_INVALID, "null argument");
+  if (!f->parts.empty()) {            // multi-device: the slowest device's times, the launches of all
+    *out = f->parts[0]->tm;
+    for (size_t i = 1; i < f->parts.size(); ++i) {
+      const ppls_timing& t = f->parts[i]->tm;
+      out->stream_ms = std::max(out->stream_ms, t.stream_ms); out->loop_ms = std::max(out->loop_ms, t.loop_ms);
+      out->tail_ms = std::max(out->tail_ms, t.tail_ms); out->stream_phase_ms = std::max(out->stream_phase_ms, t.stream_phase_ms);
+      out->kernel_launches += t.kernel_launches; out->bytes_per_pass += t.bytes_per_pass;
+    }
+    return PPLS_OK;
+  }
   *out = f->tm;
   return PPLS_OK;
 }
@@ -1209,6 +1471,7 @@ extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr
 // orth(G, type): OmicsPLS::orth as PPLS_simult calls it (EM_W_multi.R:732-733).  Host in, host out.
 extern "C" int ppls_orth(ppls_ctx* ctx, const double* G, int64_t ldG, int64_t n, int32_t r, int32_t orth_type,
                          double* out, int64_t ldOut) {
+  if (ctx && !ctx->subs.empty()) ctx = ctx->subs[0];          // context-only work: the first device does it
   int rc = ctx_activate(ctx);
   if (rc) return rc;
   if (!G || !out) return fail(PPLS_E_INVALID, "null G or out");
@@ -1240,7 +1503,7 @@ extern "C" int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const p
   if (rc) return rc;
   int32_t done = 0, fin = 0;
   rc = ppls_fit_iterate(f, 1, &done, &fin);
-  if (rc == PPLS_OK) *out = f->st_host->loglik_last;
+  if (rc == PPLS_OK) *out = (f->parts.empty() ? f : f->parts[0])->st_host->loglik_last;
   fit_free(f);
   return rc;
 }

@@ -83,6 +83,7 @@ __device__ __forceinline__ void raise_done(FitState* st) {
 // ---- launchers (host functions defined in the .cu files) -------------------------------
 struct StreamPlan {          // how K1 is launched for one shape
   int R, M, T, nstage;
+  int keep;                  // KEEP form: the tile is read from shared memory once, x stays in registers (em_stream_kernel.cuh)
   int nwX, nwY;              // warps owning X column chunks / Y column chunks
   int cX, bigX, cY, bigY;    // chunks per warp: the first bigX X-warps own cX+1, the rest cX (Y alike)
   int threads, grid, ctas_per_sm;

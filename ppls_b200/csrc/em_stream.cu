@@ -11,21 +11,21 @@ static int env_int(const char* name, int dflt) {
   return (v && *v) ? atoi(v) : dflt;
 }
 
-static stream_kernel_t lookup_kernel(int R, int M, int T) {
+static stream_kernel_t lookup_kernel(int R, int M, int T, int keep) {
   switch (R) {
-    case 1: return lookup_kernel_r1(M, T);
-    case 2: return lookup_kernel_r2(M, T);
-    case 3: return lookup_kernel_r3(M, T);
-    case 4: return lookup_kernel_r4(M, T);
-    case 5: return lookup_kernel_r5(M, T);
-    case 6: return lookup_kernel_r6(M, T);
-    case 7: return lookup_kernel_r7(M, T);
-    case 8: return lookup_kernel_r8(M, T);
+    case 1: return lookup_kernel_r1(M, T, keep);
+    case 2: return lookup_kernel_r2(M, T, keep);
+    case 3: return lookup_kernel_r3(M, T, keep);
+    case 4: return lookup_kernel_r4(M, T, keep);
+    case 5: return lookup_kernel_r5(M, T, keep);
+    case 6: return lookup_kernel_r6(M, T, keep);
+    case 7: return lookup_kernel_r7(M, T, keep);
+    case 8: return lookup_kernel_r8(M, T, keep);
   }
   return nullptr;
 }
 
-static int max_threads_rt(int R, int M, int T) { return max_threads_for(R, M, T); }
+static int max_threads_rt(int R, int M, int T, int keep) { return max_threads_for(R, M, T, keep != 0); }
 
 // Split chX X-chunks and chY Y-chunks (64 columns each) over nw compute warps.
 static bool split_chunks(int chX, int chY, int nw, StreamPlan* p) {
@@ -52,6 +52,7 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
   const int chX = (s.p2 / 2 + 31) / 32, chY = (s.q2 / 2 + 31) / 32;
   const size_t smem_max = 227 * 1024;  // usable dynamic shared memory per CTA (1 CTA per SM)
   const int envT = env_int("PPLS_K1_T", 0), envW = env_int("PPLS_K1_WARPS", 0), envS = env_int("PPLS_K1_STAGES", 0);
+  const int keep = env_int("PPLS_K1_KEEP", 0) ? 1 : 0;
   const size_t rowbytes = (size_t)s.ld * 8;
   // candidates: T in {8,4,2} (larger T amortises the per-tile hand-offs), compute warps from the
   // preferred count (2 per SM sub-partition) upwards until the chunks per warp fit the register budget
@@ -69,7 +70,7 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
       StreamPlan p{};
       split_chunks(chX, chY, nw, &p);
       const int nwc = p.nwX + p.nwY;
-      if (p.M > 6 || !lookup_kernel(R, p.M, T) || (nwc + 2) * 32 > max_threads_rt(R, p.M, T)) {
+      if (p.M > 6 || !lookup_kernel(R, p.M, T, keep) || (nwc + 2) * 32 > max_threads_rt(R, p.M, T, keep)) {
         if (envW || nwc < nw) break;           // fixed by the caller / no more chunks to spread
         continue;
       }
@@ -86,7 +87,7 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
       const double score = (inflight >= 72.0 * 1024 ? 1e9 : inflight) + T * 1e3 - nwc;
       if (score > best_score) {
         best_score = score; best = p;
-        best.R = R; best.T = T; best.nstage = ns; best.threads = (nwc + 2) * 32;
+        best.R = R; best.T = T; best.nstage = ns; best.threads = (nwc + 2) * 32; best.keep = keep;
         best.smem_bytes = stream_smem_layout(R, T, ns, nwc, s.ld).total;
       }
       break;
@@ -97,7 +98,7 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
     return cudaErrorInvalidValue;
   }
   *plan = best;
-  stream_kernel_t k = lookup_kernel(R, plan->M, plan->T);
+  stream_kernel_t k = lookup_kernel(R, plan->M, plan->T, plan->keep);
   plan->ntiles = (s.n + plan->T - 1) / plan->T;
   plan->ctas_per_sm = 1;
   int64_t grid = (int64_t)sm_count;
@@ -113,8 +114,8 @@ cudaError_t plan_stream(const DataShape& s, int R, int sm_count, StreamPlan* pla
                                        (int)plan->smem_bytes);
   if (e != cudaSuccess) { *why = "cudaFuncSetAttribute(MaxDynamicSharedMemorySize) failed"; return e; }
   if (env_int("PPLS_K1_VERBOSE", 0))
-    fprintf(stderr, "[ppls] K1 plan: R=%d M=%d T=%d stages=%d warps=%d(X %dx%d+%d)+%d(Y %dx%d+%d)+2 grid=%d smem=%zu\n",
-            R, plan->M, plan->T, plan->nstage, plan->nwX, plan->nwX, plan->cX, plan->bigX, plan->nwY, plan->nwY,
+    fprintf(stderr, "[ppls] K1 plan: keep=%d R=%d M=%d T=%d stages=%d warps=%d(X %dx%d+%d)+%d(Y %dx%d+%d)+2 grid=%d smem=%zu\n",
+            plan->keep, R, plan->M, plan->T, plan->nstage, plan->nwX, plan->nwX, plan->cX, plan->bigX, plan->nwY, plan->nwY,
             plan->cY, plan->bigY, plan->grid, plan->smem_bytes);
   return cudaSuccess;
 }
@@ -128,7 +129,7 @@ size_t stream_tail_clock_offset(const StreamPlan& plan) { return tail_clock_offs
 cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const double* D,
                              const double* L, const FitState* st, double* partials,
                              double* muT, double* muU, int write_mu, cudaStream_t stream, const FusedTail* ft) {
-  stream_kernel_t k = lookup_kernel(plan.R, plan.M, plan.T);
+  stream_kernel_t k = lookup_kernel(plan.R, plan.M, plan.T, plan.keep);
   if (!k) return cudaErrorInvalidValue;
   StreamArgs a;
   memset(&a.tail, 0, sizeof(a.tail));

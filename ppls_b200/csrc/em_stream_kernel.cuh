@@ -80,9 +80,12 @@ struct StreamArgs {
 // capped per M (wide M -> few fat warps) and by the register file.  Per thread: loadings 4MR +
 // accumulators 4MR + partial projections 2TR (phase A) / mu 2TR (phase B) + ~56 for addresses,
 // staging and the loads in flight.
-__host__ __device__ constexpr int regs_estimate(int R, int M, int T) { return 8 * M * R + 2 * T * R + 56; }
-__host__ __device__ constexpr int max_threads_for(int R, int M, int T) {
-  int r = regs_estimate(R, M, T);
+// KEEP (the tile's x values stay in registers from phase A to phase B): 4MT more.
+__host__ __device__ constexpr int regs_estimate(int R, int M, int T, bool keep = false) {
+  return 8 * M * R + (keep ? 4 * M * T : 0) + 2 * T * R + 56;
+}
+__host__ __device__ constexpr int max_threads_for(int R, int M, int T, bool keep = false) {
+  int r = regs_estimate(R, M, T, keep);
   if (r > 255) r = 255;
   int by_regs = (65536 / r) / 128 * 128;         // ptxas budgets registers for the CTA size rounded up to 128
   int by_m = ((M >= 4 ? 6 : (M == 3 ? 8 : (M == 2 ? 10 : 20))) + 2) * 32;
@@ -136,7 +139,7 @@ __host__ __device__ inline StreamSmem stream_smem_layout(int R, int T, int nstag
 // ------------------------------------------------------------------------------------------
 // Compute-warp loop, specialised on the number of 64-column chunks CNT this warp owns.
 // ------------------------------------------------------------------------------------------
-template <int R, int T, int CNT>
+template <int R, int T, int CNT, bool KEEP>
 __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char* smem, const StreamSmem& lay,
                                              int warp, int lane, int nwc, int my_tiles, bool isY, int c0,
                                              double* out) {
@@ -217,6 +220,84 @@ __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char*
     if (sB == (uint32_t)a.nstage) { sB = 0; offB = 0; }
   };
 
+  if constexpr (KEEP) {
+    // ---- KEEP form: the tile is read from shared memory ONCE.  Its values stay in registers from the projection
+    // (phase A) to the accumulation (phase B) of the SAME tile; the ring stage is released as soon as phase A has
+    // consumed the loads, so the copies of later tiles run under the reducer's turnaround.
+    for (int it = 0; it < my_tiles; ++it) {
+      const uint32_t buf = (uint32_t)it & 1u;
+      mbar_wait(full0 + 8u * sA, phA);
+      double x[T][CNT][2];
+      const uint32_t rb = xaddr + offA;
+#pragma unroll
+      for (int i = 0; i < T; ++i) {
+        const uint32_t ra = rb + (uint32_t)i * rowbytes;
+#pragma unroll
+        for (int m = 0; m < CNT; ++m) {
+          switch (m) {
+            case 0: lds128<0>(x[i][m][0], x[i][m][1], ra); break;
+            case 1: lds128<512>(x[i][m][0], x[i][m][1], ra); break;
+            case 2: lds128<1024>(x[i][m][0], x[i][m][1], ra); break;
+            case 3: lds128<1536>(x[i][m][0], x[i][m][1], ra); break;
+            case 4: lds128<2048>(x[i][m][0], x[i][m][1], ra); break;
+            default: lds128<2560>(x[i][m][0], x[i][m][1], ra); break;
+          }
+        }
+      }
+      double pf[V];
+#pragma unroll
+      for (int v = 0; v < V; ++v) pf[v] = 0.0;
+#pragma unroll
+      for (int i = 0; i < T; ++i)
+#pragma unroll
+        for (int m = 0; m < CNT; ++m)
+#pragma unroll
+          for (int k = 0; k < R; ++k) {
+            pf[i * R + k] = fma(x[i][m][0], w[m][0][k], pf[i * R + k]);
+            pf[i * R + k] = fma(x[i][m][1], w[m][1][k], pf[i * R + k]);
+          }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(empty0 + 8u * sA);      // every lane's loads have been consumed: the stage is free
+      offA += stage_bytes; ++sA;
+      if (sA == (uint32_t)a.nstage) { sA = 0; offA = 0; phA ^= 1u; }
+#pragma unroll
+      for (int vp = 0; vp < NP; ++vp) red_w[vp * RP2 + lane] = make_double2(pf[2 * vp], pf[2 * vp + 1]);
+      __syncwarp();
+      double s0 = 0.0, s1 = 0.0, u0 = 0.0, u1 = 0.0;
+      if (ract) {
+#pragma unroll
+        for (int j = 0; j < SEG; j += 2) {
+          const double2 e = rsrc[j * H];
+          s0 += e.x; s1 += e.y;
+          if (j + 1 < SEG) { const double2 f = rsrc[(j + 1) * H]; u0 += f.x; u1 += f.y; }
+        }
+      }
+      s0 += u0; s1 += u1;
+#pragma unroll
+      for (int o = H / 2; o > 0; o >>= 1) {
+        s0 += __shfl_xor_sync(0xffffffffu, s0, o);
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+      }
+      if (ract && rh == 0) wsum2[((size_t)buf * nwc + warp) * NP + rvp] = make_double2(s0, s1);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(part0 + 8u * buf);
+      // ---- phase B of the same tile, from registers ----------------------------------------------------------
+      mbar_wait(muready0 + 8u * buf, ((uint32_t)it >> 1) & 1u);
+      double mus[V];
+      const uint32_t ma = mu_addr0 + buf * (2u * V * 8u);
+#pragma unroll
+      for (int v = 0; v < V; v += 2) lds128<0>(mus[v], mus[v + 1], ma + v * 8);
+#pragma unroll
+      for (int i = 0; i < T; ++i)
+#pragma unroll
+        for (int m = 0; m < CNT; ++m)
+#pragma unroll
+          for (int k = 0; k < R; ++k) {
+            acc[m][0][k] = fma(x[i][m][0], mus[i * R + k], acc[m][0][k]);
+            acc[m][1][k] = fma(x[i][m][1], mus[i * R + k], acc[m][1][k]);
+          }
+    }
+  } else {
   for (int it = 0; it < my_tiles; ++it) {
     const uint32_t buf = (uint32_t)it & 1u;
     mbar_wait(full0 + 8u * sA, phA);
@@ -273,6 +354,7 @@ __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char*
     if (it >= 1) phaseB(it - 1);
   }
   if (my_tiles >= 1) phaseB(my_tiles - 1);
+  }
 
   // ---- epilogue: this CTA's partial G ------------------------------------------------------
 #pragma unroll
@@ -288,8 +370,8 @@ __device__ __forceinline__ void compute_warp(const StreamArgs& a, unsigned char*
 // Warp roles.  Warps 0..nwc-1 (nwc = nwX + nwY): COMPUTE (above).  Warp nwc: REDUCER -- sums
 // the warps' projection partials, forms mu_T/mu_U and the Gram terms.  Warp nwc+1: PRODUCER --
 // keeps the shared-memory ring fed with cp.async.bulk.
-template <int R, int M, int T>
-__global__ void __launch_bounds__(max_threads_for(R, M, T), 1) em_stream_kernel(const StreamArgs a) {
+template <int R, int M, int T, bool KEEP>
+__global__ void __launch_bounds__(max_threads_for(R, M, T, KEEP), 1) em_stream_kernel(const StreamArgs a) {
   constexpr int V = T * R;
   static_assert(V <= 32 && V % 2 == 0, "T*R must be even and fit one warp");
   if (a.st->done && !a.write_mu) return;         // the posterior-means pass runs after the end
@@ -345,7 +427,7 @@ __global__ void __launch_bounds__(max_threads_for(R, M, T), 1) em_stream_kernel(
     const int cb = isY ? a.cY : a.cX, big = isY ? a.bigY : a.bigX;
     const int cnt = cb + (wg < big ? 1 : 0);
     const int c0 = wg * cb + (wg < big ? wg : big);
-#define PPLS_CW(c) compute_warp<R, T, (M >= c ? c : 1)>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out)
+#define PPLS_CW(c) compute_warp<R, T, (M >= c ? c : 1), KEEP>(a, smem, lay, warp, lane, nwc, my_tiles, isY, c0, out)
     if (M >= 6 && cnt == 6) PPLS_CW(6);
     else if (M >= 5 && cnt == 5) PPLS_CW(5);
     else if (M >= 4 && cnt == 4) PPLS_CW(4);
@@ -438,13 +520,13 @@ __global__ void __launch_bounds__(max_threads_for(R, M, T), 1) em_stream_kernel(
 
 typedef void (*stream_kernel_t)(const StreamArgs);
 // one translation unit per R (em_stream_inst.cu with -DPPLS_INST_R=r) defines these
-stream_kernel_t lookup_kernel_r1(int M, int T);
-stream_kernel_t lookup_kernel_r2(int M, int T);
-stream_kernel_t lookup_kernel_r3(int M, int T);
-stream_kernel_t lookup_kernel_r4(int M, int T);
-stream_kernel_t lookup_kernel_r5(int M, int T);
-stream_kernel_t lookup_kernel_r6(int M, int T);
-stream_kernel_t lookup_kernel_r7(int M, int T);
-stream_kernel_t lookup_kernel_r8(int M, int T);
+stream_kernel_t lookup_kernel_r1(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r2(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r3(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r4(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r5(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r6(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r7(int M, int T, int keep);
+stream_kernel_t lookup_kernel_r8(int M, int T, int keep);
 
 }  // namespace ppls

@@ -23,15 +23,15 @@ struct TailArgs {
   double* L;                    // [ld][R] loadings: read by the streaming phase, overwritten with theta_{k+1}
   FitState* st;
   double* trace;
-  double* gscratch;             // [2][G][2][R*R] Gram partials | done_now (int) | barrier words (2 x u32) |
-                                // clocks (u64): streaming ns, tail ns, launches, start stamp of the running launch
+  double* gscratch;             // [2][G][2][R*R] Gram partials | u64 control words: arrivals of all CTAs, arrivals of the row
+                                // CTAs, scalar-part flag | clocks: streaming ns, tail ns, launches, start stamp, scalar ns
   int32_t p, q;
   int32_t use_x;
   XchgDev x;
 };
 
 __host__ __device__ inline size_t tail_scratch_doubles(int grid, int R) { return (size_t)2 * grid * 2 * R * R + 8; }
-__host__ __device__ inline size_t tail_clock_offset(int grid, int R) { return (size_t)2 * grid * 2 * R * R + 2; }   // doubles
+__host__ __device__ inline size_t tail_clock_offset(int grid, int R) { return (size_t)2 * grid * 2 * R * R + 3; }   // doubles
 __host__ __device__ inline int tail_rows_per_cta(int ld, int grid) { return (ld + grid - 2) / (grid - 1); }
 // dynamic shared memory the tail needs (it reuses the streaming phase's carve-up from offset 0)
 __host__ __device__ inline size_t tail_smem_bytes(int R, int ld, int grid, int threads) {
@@ -46,20 +46,22 @@ __host__ __device__ inline size_t tail_smem_bytes(int R, int ld, int grid, int t
   return d * 8 + 64;
 }
 
-// All CTAs of the grid (co-resident).  Self-resetting: count in bar[0], generation in bar[1].
-__device__ __forceinline__ void tail_grid_barrier(unsigned int* bar, bool sys) {
+// Barriers of the tail.  All CTAs are co-resident (cooperative launch, one CTA per SM).  The counters only grow: pass
+// k of a fit (every launch that gets here runs the same number of barriers) waits for a target derived from k, so
+// nothing is ever reset and a CTA that only WAITS (CTA 0 on the row CTAs' counter) needs no arrival of its own.
+__device__ __forceinline__ void tail_arrive_wait(unsigned long long* cnt, unsigned long long target, bool sys) {
   __syncthreads();
   if (threadIdx.x == 0) {
     if (sys) __threadfence_system(); else __threadfence();
-    volatile unsigned int* vb = bar;
-    const unsigned int gen = vb[1];
-    if (atomicAdd(bar, 1u) == gridDim.x - 1) {
-      vb[0] = 0u;
-      __threadfence();
-      atomicAdd(bar + 1, 1u);
-    } else {
-      while (vb[1] == gen) { }
-    }
+    atomicAdd(cnt, 1ull);
+    while (*reinterpret_cast<volatile unsigned long long*>(cnt) < target) { }
+    __threadfence();
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ void tail_wait(const unsigned long long* cnt, unsigned long long target) {
+  if (threadIdx.x == 0) {
+    while (*reinterpret_cast<const volatile unsigned long long*>(cnt) < target) { }
     __threadfence();
   }
   __syncthreads();
@@ -95,9 +97,13 @@ __device__ __forceinline__ void tail_sum8(int nelem, int n, Load f, Sink sink) {
     const bool act = e < nelem;
     double s0 = 0.0, s1 = 0.0;
     if (act) {
-      int c = y;
-      for (; c + 8 < n; c += 16) { s0 += f(e, c); s1 += f(e, c + 8); }
-      if (c < n) s0 += f(e, c);
+      for (int c0 = y; c0 < n; c0 += 64) {        // 8 loads in flight per lane, then added in the fixed order
+        double v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const int c = c0 + 8 * j; v[j] = (c < n) ? f(e, c) : 0.0; }
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) { s0 += v[j]; s1 += v[j + 1]; }
+      }
     }
     double s = s0 + s1;
     s += __shfl_xor_sync(0xffffffffu, s, 1);
@@ -136,17 +142,21 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
   double* nswork = sm;        sm += 2 * 3 * RR;
   double* SMm = sm;           sm += 2 * RR;
   ScalarShared* ssh = reinterpret_cast<ScalarShared*>(sm);
-  // ---- global scratch ---------------------------------------------------------------------------------------
+  // ---- global scratch: Gram partials, then the control words (u64) ------------------------------------------
   double* ph0 = t.gscratch;
   double* ph1 = ph0 + (size_t)G * 2 * RR;
-  int* done_now = reinterpret_cast<int*>(ph1 + (size_t)G * 2 * RR);
-  unsigned int* gbar = reinterpret_cast<unsigned int*>(done_now) + 2;
-  unsigned long long* clk = reinterpret_cast<unsigned long long*>(ph1 + (size_t)G * 2 * RR + 2);   // stream ns, tail ns, launches
+  unsigned long long* ctl = reinterpret_cast<unsigned long long*>(ph1 + (size_t)G * 2 * RR);
+  unsigned long long* cntA = ctl + 0;     // arrivals of ALL CTAs
+  unsigned long long* cntR = ctl + 1;     // arrivals of the row CTAs
+  unsigned long long* flagS = ctl + 2;    // 2 (pass + 1) + done, stored by CTA 0 when the scalar part is through
+  unsigned long long* clk = ctl + 3;      // streaming ns, tail ns, launches, start stamp, scalar-part ns
   const bool xon = t.use_x != 0;
-  const unsigned long long next = xon ? (*t.x.epoch + 1) : 0ull;    // epoch moves only after every CTA is past barrier 2
+  const unsigned long long pass = (unsigned long long)st->pass;     // CTA 0 moves it only after barrier A
+  const unsigned long long next = xon ? (*t.x.epoch + 1) : 0ull;    // ... and the epoch likewise
+  const unsigned long long NA = xon ? 2ull : 1ull;
 
   unsigned long long t1 = 0;
-  tail_grid_barrier(gbar, false);                                   // every CTA's partial vector is in global memory
+  tail_arrive_wait(cntA, (unsigned long long)G * (NA * pass + 1), false);     // A: every CTA's partial vector is in global memory
   if (b == 0 && tid == 0) { t1 = global_timer_ns(); clk[0] += t1 - clk[3]; }
 
   // ---- own elements of the reduced vector: rows [row_lo, row_hi) of G (row CTAs), the Gram tail (CTA 0) --------
@@ -162,7 +172,7 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
     tail_sum8(nelem, G,
               [&](int e, int c) { return __ldcg(partials + (size_t)c * len + e0 + e); },
               [&](int e, double s, int y) { for (int r = y; r < t.x.world; r += 8) t.x.inbox[r][off + e] = s; });
-    tail_grid_barrier(gbar, true);                                  // all CTAs' peer stores are ordered before the flags
+    tail_arrive_wait(cntA, (unsigned long long)G * (NA * pass + 2), true);    // A2: all CTAs' peer stores are ordered before the flags
     if (b == 0 && tid < t.x.world) {
       __threadfence_system();
       st_relaxed_sys(t.x.flags[tid] + (next & 1ull) * XCHG_MAXW + t.x.rank, next);
@@ -176,16 +186,69 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
   }
   __syncthreads();
 
-  // ---- CTA 0: scalar part.  Row CTAs: partial Gram of their rows of G -------------------------------------------
   if (rb < 0) {
+    // ================= CTA 0: the scalar part, off the row CTAs' path =================
+    volatile int* s_done = reinterpret_cast<volatile int*>(ssh + 1);
     if (tid < 32) {
       UpdateArgs ua;
       ua.momvec = t.momvec; ua.L = t.L; ua.Lscratch = nullptr; ua.st = st; ua.trace = t.trace; ua.gscratch = nullptr;
       ua.p = t.p; ua.q = t.q; ua.p2 = p2; ua.q2 = ld - p2; ua.ld = ld; ua.use_x = 0;
-      const int d = update_scalars<R>(ua, ssh);
-      if (tid == 0) *done_now = d;
+      int d = update_scalars<R>(ua, ssh);
+      if (tid == 0) {
+        if (xon) {
+          if (*reinterpret_cast<volatile int*>(t.x.failed)) { st->status = PPLS_E_NCCL; d = 1; }   // a peer never answered
+          *t.x.epoch = next;
+        }
+        *s_done = d;
+        __threadfence();
+        *reinterpret_cast<volatile unsigned long long*>(flagS) = 2ull * (pass + 1) + (d ? 1ull : 0ull);
+        clk[4] += global_timer_ns() - t1;
+      }
     }
-  } else {
+    __syncthreads();
+    if (*s_done) {                                                  // the run ended with this pass: theta_k stays
+      if (tid == 0) { raise_done(st); clk[1] += global_timer_ns() - t1; clk[2] += 1ull; }
+      return;
+    }
+    // W'W, C'C of the new loadings from the row CTAs' second Gram: M S M with M = (3I - S)/2
+    tail_wait(cntR, (unsigned long long)nrb * (2 * pass + 2));
+    tail_sum8(2 * NV, nrb,
+              [&](int e, int c) { return __ldcg(ph1 + ((size_t)c * 2 + e / NV) * RR + e % NV); },
+              [&](int e, double s, int y) {
+                if (y == 0) { int k, l; tail_unpack<R>(e % NV, k, l); double* Sw = S + (e / NV) * RR; Sw[k * R + l] = s; Sw[l * R + k] = s; }
+              });
+    __syncthreads();
+    for (int e = tid; e < 2 * RR; e += nt) {
+      const int i = (e % RR) / R, j = (e % RR) % R;
+      Mat[e] = (i == j ? 1.5 : 0.0) - 0.5 * S[e];
+    }
+    __syncthreads();
+    for (int e = tid; e < 2 * RR; e += nt) {                         // S M
+      const int w = e / RR, i = (e % RR) / R, j = (e % RR) % R;
+      double sacc = 0.0;
+      for (int k = 0; k < R; ++k) sacc += S[w * RR + i * R + k] * Mat[w * RR + k * R + j];
+      SMm[e] = sacc;
+    }
+    __syncthreads();
+    for (int e = tid; e < 2 * RR; e += nt) {                         // M (S M); M is symmetric
+      const int w = e / RR, i = (e % RR) / R, j = (e % RR) % R;
+      double sacc = 0.0;
+      for (int k = 0; k < R; ++k) sacc += Mat[w * RR + i * R + k] * SMm[w * RR + k * R + j];
+      (w ? st->CtC : st->WtW)[e % RR] = sacc;
+      nswork[e] = sacc;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      bool ok = true;
+      for (int e = 0; e < 2 * RR; ++e) ok = ok && finite_d(nswork[e]);
+      if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); st->steps_done = st->pass - 1; }
+      clk[1] += global_timer_ns() - t1; clk[2] += 1ull;
+    }
+    return;
+  }
+
+  // ================= row CTAs: W = orth(X'mu_T), C = orth(Y'mu_U) on their rows (Maximiz_M, :732-733) =================
+  {
     double v[2 * NV];
 #pragma unroll
     for (int e = 0; e < 2 * NV; ++e) v[e] = 0.0;
@@ -203,24 +266,17 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
     tail_block_reduce(v, 2 * NV, S, red);
     if (tid < 2 * NV) ph0[((size_t)rb * 2 + tid / NV) * RR + tid % NV] = S[tid];
   }
-  tail_grid_barrier(gbar, false);                                   // barrier 2
-  if (xon) {
-    if (*reinterpret_cast<volatile int*>(t.x.failed)) {             // a peer never answered (raised before the barrier)
-      if (b == 0 && tid == 0) { st->status = PPLS_E_NCCL; raise_done(st); }
-      return;
-    }
-    if (b == 0 && tid == 0) *t.x.epoch = next;
-  }
+  tail_arrive_wait(cntR, (unsigned long long)nrb * (2 * pass + 1), false);     // B: every row CTA's Gram partial of G
 
   // ---- T = G (G'G)^{-1/2} on the rows in shared memory, partial Gram of T ---------------------------------------
-  if (rb >= 0) {
-    tail_sum8(2 * NV, nrb,
-              [&](int e, int c) { return __ldcg(ph0 + ((size_t)c * 2 + e / NV) * RR + e % NV); },
-              [&](int e, double s, int y) {
-                if (y == 0) { int k, l; tail_unpack<R>(e % NV, k, l); double* Sw = S + (e / NV) * RR; Sw[k * R + l] = s; Sw[l * R + k] = s; }
-              });
-    __syncthreads();
-    block_inv_sqrt<R, 2>(S, Mat, nswork);
+  tail_sum8(2 * NV, nrb,
+            [&](int e, int c) { return __ldcg(ph0 + ((size_t)c * 2 + e / NV) * RR + e % NV); },
+            [&](int e, double s, int y) {
+              if (y == 0) { int k, l; tail_unpack<R>(e % NV, k, l); double* Sw = S + (e / NV) * RR; Sw[k * R + l] = s; Sw[l * R + k] = s; }
+            });
+  __syncthreads();
+  block_inv_sqrt<R, 2>(S, Mat, nswork);
+  {
     double v[2 * NV];
 #pragma unroll
     for (int e = 0; e < 2 * NV; ++e) v[e] = 0.0;
@@ -248,16 +304,9 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
     tail_block_reduce(v, 2 * NV, S, red);
     if (tid < 2 * NV) ph1[((size_t)rb * 2 + tid / NV) * RR + tid % NV] = S[tid];
   }
-  tail_grid_barrier(gbar, false);                                   // barrier 3
-  if (*reinterpret_cast<volatile int*>(done_now)) {                 // the run ended with this pass: theta_k stays
-    if (rb < 0 && tid == 0) {
-      raise_done(st);
-      const unsigned long long t2 = global_timer_ns();
-      clk[1] += t2 - t1; clk[2] += 1ull;
-    }
-    return;
-  }
-  // ---- one Newton-Schulz step L = T M, M = (3I - S)/2, S = T'T; W'W = C'C = M S M by CTA 0 -----------------------
+  tail_arrive_wait(cntR, (unsigned long long)nrb * (2 * pass + 2), false);     // C: every row CTA's Gram partial of T
+
+  // ---- one Newton-Schulz step L = T M, M = (3I - S)/2, S = T'T --------------------------------------------------
   tail_sum8(2 * NV, nrb,
             [&](int e, int c) { return __ldcg(ph1 + ((size_t)c * 2 + e / NV) * RR + e % NV); },
             [&](int e, double s, int y) {
@@ -268,46 +317,23 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
     const int i = (e % RR) / R, j = (e % RR) % R;
     Mat[e] = (i == j ? 1.5 : 0.0) - 0.5 * S[e];
   }
-  __syncthreads();
-  if (rb >= 0) {
-    for (int j = tid; j < nrows; j += nt) {
-      const double* M = Mat + ((row_lo + j >= p2) ? RR : 0);
-      double row[R], res[R];
+  // theta_k's loadings stay untouched until CTA 0 has decided whether the run ends with this pass
+  tail_wait(flagS, 2ull * (pass + 1));
+  if (*reinterpret_cast<volatile unsigned long long*>(flagS) & 1ull) return;
+  for (int j = tid; j < nrows; j += nt) {
+    const double* M = Mat + ((row_lo + j >= p2) ? RR : 0);
+    double row[R], res[R];
 #pragma unroll
-      for (int k = 0; k < R; ++k) row[k] = Ts[j * R + k];
+    for (int k = 0; k < R; ++k) row[k] = Ts[j * R + k];
 #pragma unroll
-      for (int l = 0; l < R; ++l) {
-        double sacc = 0.0;
-#pragma unroll
-        for (int k = 0; k < R; ++k) sacc += row[k] * M[k * R + l];
-        res[l] = sacc;
-      }
-#pragma unroll
-      for (int l = 0; l < R; ++l) t.L[(size_t)(row_lo + j) * R + l] = res[l];
-    }
-  } else {
-    for (int e = tid; e < 2 * RR; e += nt) {                         // S M
-      const int w = e / RR, i = (e % RR) / R, j = (e % RR) % R;
+    for (int l = 0; l < R; ++l) {
       double sacc = 0.0;
-      for (int k = 0; k < R; ++k) sacc += S[w * RR + i * R + k] * Mat[w * RR + k * R + j];
-      SMm[e] = sacc;
+#pragma unroll
+      for (int k = 0; k < R; ++k) sacc += row[k] * M[k * R + l];
+      res[l] = sacc;
     }
-    __syncthreads();
-    for (int e = tid; e < 2 * RR; e += nt) {                         // M (S M); M is symmetric
-      const int w = e / RR, i = (e % RR) / R, j = (e % RR) % R;
-      double sacc = 0.0;
-      for (int k = 0; k < R; ++k) sacc += Mat[w * RR + i * R + k] * SMm[w * RR + k * R + j];
-      (w ? st->CtC : st->WtW)[e % RR] = sacc;
-      S[e] = sacc;
-    }
-    __syncthreads();
-    if (tid == 0) {
-      bool ok = true;
-      for (int e = 0; e < 2 * RR; ++e) ok = ok && finite_d(S[e]);
-      if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); st->steps_done = st->pass - 1; }
-      const unsigned long long t2 = global_timer_ns();
-      clk[1] += t2 - t1; clk[2] += 1ull;
-    }
+#pragma unroll
+    for (int l = 0; l < R; ++l) t.L[(size_t)(row_lo + j) * R + l] = res[l];
   }
 }
 

@@ -82,6 +82,9 @@ def main():
         errs["simult_default_loglik"] = relmax(sim["loglik"], o2["loglik"])
         ok = (same_ranks and errs["loglik"] < 1e-10 and errs["seq_loglik"] < 1e-10 and errs["simult_default_loglik"] < 1e-10
               and all(v < 1e-8 for v in errs.values()) and errs["repeat"] == 0.0 and (world != 2 or errs["vs_nccl"] == 0.0))
+        if os.environ.get("PPLS_DUMP"):      # for the single-process multi-device test: must agree bit for bit
+            np.savez(os.environ["PPLS_DUMP"], W=xa["W"], C=xa["C"], B=xa["B"], sigT=xa["sigT"], loglik=xa["loglik"],
+                     sig=np.array([xa["sigE"], xa["sigF"], xa["sigH"]]))
         print("ROWSHARD", "OK" if ok else "FAIL", world, "ranks", (N, p, q, r), "same_on_all_ranks", same_ranks,
               {k: float(f"{v:.2e}") for k, v in errs.items()}, flush=True)
     dist.barrier()

@@ -3,7 +3,7 @@ the CPU oracle and against the oracle run on fresh seeded inputs."""
 import numpy as np
 import pytest
 
-from helpers import (TOL_PARAM, golden_cases, init_of, load_golden, loglik_tol, moment_tol, relmax)
+from helpers import (TOL_LOGLIK, TOL_PARAM, golden_cases, init_of, load_golden, loglik_tol, moment_tol, relmax)
 
 pytestmark = pytest.mark.gpu
 
@@ -266,6 +266,68 @@ def test_row_sharded_two_gpus_peer_exchange():
                         "127.0.0.1", "--master-port", "29543", os.path.join(root, "tests", "mgpu_rowshard.py")],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "ROWSHARD OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_multi_device_context_matches_oracle_and_the_torchrun_form(tmp_path):
+    """ONE process driving 2 GPUs (ppls_ctx_create_multi; what `device = 0:1` means in the R wrapper): host X, Y split
+    over the devices, the EM loop with the peer exchange, results gathered -- against the oracle, against a
+    single-device run, and BIT FOR BIT against the one-process-per-GPU form (tests/mgpu_rowshard.py under torchrun)."""
+    import os, subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    from oracle import cbind, ppls_fused as F
+    from ppls_b200 import Context, Data, Fit, PPLS_simult, PPLSError, synth
+    N, p, q, r, steps = 20001, 301, 77, 3, 12
+    truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
+    st = synth.start_params(truth, 3)
+    Lo = cbind.load()
+    X, Y = cbind.gen_data(Lo, 4242, 0, N, truth)
+    o = F.fused_loop(Lo, X, Y, st["W"], st["C"], st["B"], st["sigE"], st["sigF"], st["sigH"], st["sigT"], EMsteps=steps, atol=-np.inf)
+    mctx = Context.multi([0, 1])
+    assert mctx.world == 2
+    try:
+        for make in ("host", "synthetic"):
+            d = Data.from_host(mctx, X, Y) if make == "host" else Data.synthetic(mctx, N, p, q, truth, seed=4242)
+            assert (d.n, d.p, d.q, d.n_total) == (N, p, q, N)
+            assert abs(d.ssqX / float(np.sum(X * X)) - 1) < 1e-12
+            Xb, Yb = d.export(9000, 2500)                       # a row range across the shard boundary
+            assert np.array_equal(Xb, X[9000:11500]) and np.array_equal(Yb, Y[9000:11500])
+            f = Fit(d, st, r, steps, -np.inf, "SVD")
+            f.run()
+            res = f.result(want_mu=True)
+            f.close(); d.close()
+            assert relmax(res["loglik"], o["loglik"]) < TOL_LOGLIK
+            for k in ("W", "C", "B", "sigT"):
+                assert relmax(res[k], o[k]) < TOL_PARAM, k
+            assert relmax(res["mu_T"], o["mu_T"]) < TOL_PARAM and relmax(res["mu_U"], o["mu_U"]) < TOL_PARAM
+            if make == "host":
+                first = res
+            else:                                               # the device generator makes the same bits as the host one
+                assert np.array_equal(res["W"], first["W"]) and np.array_equal(res["loglik"], first["loglik"])
+        # the public call on the multi-device context, QR type (update kernel K2 with the exchange, not the fused tail)
+        out = PPLS_simult(X, Y, r, EMsteps=5, atol=-np.inf, type="QR", init=st, ctx=mctx, want_mu=False)
+        one = PPLS_simult(X, Y, r, EMsteps=5, atol=-np.inf, type="QR", init=st, ctx=Context(0), want_mu=False)
+        assert relmax(out["loglik"], one["loglik"]) < 1e-12 and relmax(out["estimates"]["W"], one["estimates"]["W"]) < 1e-9
+        # entry points that need a collective the multi-device form does not have say so
+        with pytest.raises(PPLSError):
+            from ppls_b200 import PPLS
+            dd = Data.from_host(mctx, X, Y)
+            try:
+                PPLS(None, None, 2, 5, data=dd)
+            finally:
+                dd.close()
+    finally:
+        mctx.close()
+    # bit for bit against the one-process-per-GPU form
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    dump = str(tmp_path / "rowshard.npz")
+    rr = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                         "127.0.0.1", "--master-port", "29547", os.path.join(root, "tests", "mgpu_rowshard.py")],
+                        capture_output=True, text=True, timeout=900, env=dict(os.environ, PPLS_DUMP=dump))
+    assert rr.returncode == 0 and "ROWSHARD OK" in rr.stdout, rr.stdout[-2000:] + rr.stderr[-2000:]
+    z = np.load(dump)
+    assert np.array_equal(z["W"], first["W"]) and np.array_equal(z["C"], first["C"]) and np.array_equal(z["loglik"], first["loglik"])
+    assert np.array_equal(z["B"], first["B"]) and np.array_equal(z["sigT"], first["sigT"])
 
 
 @pytest.mark.parametrize("n,r", [(37, 1), (500, 2), (1201, 3), (50001, 5), (900, 8)])
