@@ -431,18 +431,21 @@ def bench_stream(env, name, K, W, args, want_e2e):
 
 
 def bench_c5(env, K, W, args):
-    """BASELINE config 5: 64 start states of N=1e5, p=200, q=50, r=2 over one resident dataset.  At N > 1 the STARTS are
-    split across the ranks, the 200 MB dataset replicated (no collective at all); value = batch EM
-    iterations/s (one iteration = all 64 starts advance one step), time = max over ranks."""
-    from ppls_b200 import Context, Data, PPLS_simult_batched, synth
+    """BASELINE config 5: 64 start states of N=1e5, p=200, q=50, r=2 over one resident dataset; value = batch EM
+    iterations/s (one iteration = all 64 starts advance one step), time = max over ranks.  At N > 1 the ROWS are split
+    (every rank runs all 64 starts on its rows; one allreduce of the starts' moment vectors per iteration): splitting the
+    STARTS instead (SURVEY.md 8e's other option, no collective) does not scale with this kernel -- its GEMM tile is 128
+    components wide, and 32 starts x 2 components fill half of it (measured on 2 GPUs: 1677 vs 1729 batch-it/s on one)."""
+    from ppls_b200 import Data, PPLS_simult_batched, synth
     world, rank = env.world, env.rank
-    ctx = Context(env.local)                     # a single-GPU context: this rank's starts need no exchange
+    ctx = env.ctx
     N, p, q, r = WORKLOADS["c5"]
     if args.rows and args.workload == "c5":
         N = args.rows
     truth = synth.truth_params(p, q, r)
-    data = Data.synthetic(ctx, N, p, q, truth, seed=SEED + 4)
-    lo, hi = C5_STARTS * rank // world, C5_STARTS * (rank + 1) // world
+    row0, n_local = shard_rows(N, rank, world)
+    data = Data.synthetic(ctx, n_local, p, q, truth, seed=SEED + 4, row0=row0)
+    lo, hi = 0, C5_STARTS
     inits = [synth.start_params(truth, seed=1000 + s) for s in range(lo, hi)]
     W = max(W, 1)
     PPLS_simult_batched(None, None, r, inits, EMsteps=W, atol=-float("inf"), data=data)
@@ -459,12 +462,12 @@ def bench_c5(env, K, W, args):
     fp64_peak = ctx.probe("fp64_dmma")
     flops = C5_STARTS * 4.0 * N * (p + q) * r * tm["passes"]
     best = float(max(x["loglik"][-1] for x in res))
-    data.close(); ctx.close()
+    data.close()
     return {"value": K / (loop_ms * 1e-3), "unit": "batch EM iterations/s (64 starts each)", "ms_per_step": loop_ms / K,
             "scaling": "strong",
             "config": {"workload": workload_label("c5", N, p, q, r),
-                       "sharding": f"starts split over {world} rank(s) ({hi - lo} on rank 0), dataset replicated, no collective",
-                       "path": f"all {(hi - lo) * r} components of a rank per data pass (two FP64 GEMMs, em_batch.cu)",
+                       "sharding": f"row-sharded {world} x {n_local}, all {C5_STARTS} starts on every rank" + ("" if world == 1 else ", one NCCL allreduce of the starts' moment vectors per iteration"),
+                       "path": f"all {C5_STARTS * r} components per data pass (two FP64 GEMMs, em_batch.cu)",
                        "wall_ms_per_step_incl_setup": wall_ms / K},
             "clocks": clocks, "gpu_launches": int(tm["kernel_launches"]),
             "roofline": {"bound": "fp64 (tensor DMMA / FMA pipe; SURVEY.md 8d config 5)", "achieved": flops / (loop_ms * 1e-3) / 1e12 / world,
