@@ -199,6 +199,40 @@ int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int3
                         const ppls_params* guesses, ppls_params* est, double* sig, double* logvalues,
                         int32_t* steps, double* last_incr, int32_t* comps_done);
 
+/* ... with the `constraints` and `critfunc` arguments of PPLS / PPLSi (EM_W_multi.R:116-117, :229-230).  constraints: NULL or
+ * nr_comp entries (fconstraint, :85-92): the values named in `mask` replace the start value (:142-146) and the estimate after
+ * every EM step (:160-167).  Fixed loadings must have unit norm and be orthogonal to the earlier components (the deflation of
+ * :270-271 is applied implicitly here; PPLS_E_UNSUPPORTED otherwise).  crit_abs != 0: critfunc = abs, else the identity
+ * (:172: break when critfunc(logvalue[i+1] - logvalue[i]) < atol). */
+#define PPLS_FIX_W    1u
+#define PPLS_FIX_C    2u
+#define PPLS_FIX_B    4u
+#define PPLS_FIX_SIGE 8u
+#define PPLS_FIX_SIGF 16u
+#define PPLS_FIX_SIGH 32u
+#define PPLS_FIX_SIGT 64u
+typedef struct {
+  uint32_t mask;        /* PPLS_FIX_* */
+  uint32_t reserved;
+  const double* W;      /* p values (PPLS_FIX_W) */
+  const double* C;      /* q values (PPLS_FIX_C) */
+  double B, sigE, sigF, sigH, sigT;
+} ppls_constraints;
+int ppls_sequential_run_ex(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int32_t EMsteps, double atol,
+                           const ppls_params* guesses, const ppls_constraints* constraints, int32_t crit_abs,
+                           ppls_params* est, double* sig, double* logvalues, int32_t* steps, double* last_incr,
+                           int32_t* comps_done);
+
+/* Start state of ONE component as PPLSi draws it (EM_W_multi.R:126-141).  kind PPLS_GUESS_EQUAL: orth(rep(1,p)), orth(rep(1,q)),
+ * B = 1, sigH = sigT = 1, sigE = 1/p, sigF = 1/q (:135-136).  kind PPLS_GUESS_RANDOM (:133): orth(runif(p)), orth(runif(q)),
+ * B = rchisq(1,1), (sigH, sigT) = rchisq(2,100)/100, (sigE, sigF) = rchisq(2,10)/100 -- drawn ON THE DEVICE from the counter-based
+ * generator keyed by (seed, component): the distribution of the reference's start, repeatable bit for bit; R's own RNG stream
+ * cannot be reproduced outside R.  out: W p x 1, C q x 1, B[1], sigT[1] caller-allocated.  ("o2m" needs OmicsPLS::o2m: pass its
+ * result as a custom guess.) */
+#define PPLS_GUESS_EQUAL  0
+#define PPLS_GUESS_RANDOM 1
+int ppls_initial_guess(ppls_ctx* ctx, int32_t kind, int64_t p, int64_t q, uint64_t seed, int32_t component, ppls_params* out);
+
 /* logl_W(X, Y, W, C, B, sigE, sigF, sigH, sigT) of EM_W_multi.R:296-326 (-> loglC_fast, loglC.cpp:318-338)
  * for r components: one streaming pass over the resident data. */
 int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out);

@@ -14,6 +14,8 @@ SO = os.path.join(HERE, "libppls_oracle.so")
 def declare(L):
     L.ppls_gen_normal.restype = C.c_double
     L.ppls_gen_normal.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32]
+    L.ppls_gen_uniform.restype = C.c_double
+    L.ppls_gen_uniform.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_uint32]
     L.ppls_gen_normals.restype = None
     L.ppls_gen_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_uint64, C.c_int64, C.c_int32, C.c_void_p]
     L.ppls_gen_data.restype = None
@@ -91,3 +93,19 @@ def moments(L, X, Y, W, Cm, aT, bT, aU, bU, nranks=1, want_mu=False):
                           G1.ctypes.data, G2.ctypes.data, Gam.ctypes.data, ssq.ctypes.data,
                           muT.ctypes.data if want_mu else None, muU.ctypes.data if want_mu else None)
     return dict(G1=G1, G2=G2, Gam=Gam, ssqX=ssq[0], ssqY=ssq[1], mu_T=muT, mu_U=muU)
+
+
+def random_guess(L, p, q, seed, comp):
+    """PPLSi's initialGuess = "random" (EM_W_multi.R:133) on the counter-based generator: the host restatement of
+    ppls_b200's device kernel (data.cu::guess_kernel) -- streams 16 (W), 17 (C), 18 (chi-square scalars)."""
+    u = np.array([L.ppls_gen_uniform(seed, 16, comp, j) for j in range(p)])
+    v = np.array([L.ppls_gen_uniform(seed, 17, comp, j) for j in range(q)])
+
+    def chisq(first, k):
+        s = 0.0
+        for e in range(k):
+            z = L.ppls_gen_normal(seed, 18, comp, first + e)
+            s += z * z
+        return s
+    return dict(W=u / np.sqrt(np.sum(u * u)), C=v / np.sqrt(np.sum(v * v)), B=chisq(0, 1), sigH=chisq(1, 100) / 100.0,
+                sigT=chisq(101, 100) / 100.0, sigE=chisq(201, 10) / 100.0, sigF=chisq(211, 10) / 100.0)

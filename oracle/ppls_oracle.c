@@ -116,6 +116,13 @@ double ppls_gen_normal(uint64_t seed, uint32_t stream, uint64_t row, uint32_t co
   return det_ndtri(u);
 }
 
+/* One uniform in (0, 1) from the same counter (the draw the normal above is made from). */
+double ppls_gen_uniform(uint64_t seed, uint32_t stream, uint64_t row, uint32_t col) {
+  uint32_t c[4] = {(uint32_t)row, (uint32_t)(row >> 32), col, stream};
+  philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+  return ((double)(c[0] >> 5) * 67108864.0 + (double)(c[1] >> 6) + 0.5) / 9007199254740992.0;
+}
+
 void ppls_gen_normals(uint64_t seed, uint32_t stream, uint64_t row0, int64_t nrows, int32_t ncols,
                       double* out /* nrows x ncols column-major */) {
 #pragma omp parallel for schedule(static)

@@ -70,21 +70,43 @@ def emstep_w(X, Y, W, C, B, sigX, sigY, sigH, sigT):
     return emstepc_fast(np.ravel(W), np.ravel(C), float(B), X, Y, sigX, sigY, sigH, sigT, c1, c2, c3)
 
 
-def initial_guess(p, q, kind="equal", custom=None):
-    """EM_W_multi.R:126-141 ("equal": orth(rep(1,p)) is the normalised ones vector)."""
+def initial_guess(p, q, kind="equal", custom=None, seed=0, comp=0):
+    """EM_W_multi.R:126-141 ("equal": orth(rep(1,p)) is the normalised ones vector; "random", :133: orth(runif(p)),
+    orth(runif(q)), rchisq draws -- from the counter-based generator keyed by (seed, comp), the host restatement of
+    ppls_b200's device kernel, since R's RNG stream does not exist outside R)."""
     if custom is not None or kind == "custom":
         g = custom
         return (np.ravel(g["W"]).astype(float), np.ravel(g["C"]).astype(float), float(g["B"]),
                 np.array([float(g["sigE"]), float(g["sigF"])]), np.array([float(g["sigH"]), float(g["sigT"])]))
+    if kind == "random":
+        from . import cbind
+        g = cbind.random_guess(cbind.load(), p, q, int(seed), int(comp))
+        return (g["W"], g["C"], float(g["B"]), np.array([g["sigE"], g["sigF"]]), np.array([g["sigH"], g["sigT"]]))
     if kind != "equal":
-        raise ValueError("oracle restates initialGuess 'equal' and 'custom' only")
+        raise ValueError("oracle restates initialGuess 'equal', 'random' and 'custom' only")
     return (np.ones(p) / math.sqrt(p), np.ones(q) / math.sqrt(q), 1.0, np.array([1.0 / p, 1.0 / q]), np.array([1.0, 1.0]))
 
 
-def pplsi(X, Y, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None):
-    """EM_W_multi.R:116-180 with critfunc = identity and no constraints."""
+def _constrain(cons, Wnw, Cnw, Bnw, signw, siglatnw):
+    """EM_W_multi.R:142-146 / :163-167: fixed values replace the estimates."""
+    if not cons:
+        return Wnw, Cnw, Bnw, signw, siglatnw
+    g = lambda k: cons.get(k)                                                                    # noqa: E731
+    Wnw = np.ravel(g("W")).astype(float) if g("W") is not None else Wnw
+    Cnw = np.ravel(g("C")).astype(float) if g("C") is not None else Cnw
+    Bnw = float(g("B")) if g("B") is not None else Bnw
+    signw = np.array([float(g("sigE")) if g("sigE") is not None else signw[0], float(g("sigF")) if g("sigF") is not None else signw[1]])
+    siglatnw = np.array([float(g("sigH")) if g("sigH") is not None else siglatnw[0],
+                         float(g("sigT")) if g("sigT") is not None else siglatnw[1]])
+    return Wnw, Cnw, Bnw, signw, siglatnw
+
+
+def pplsi(X, Y, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None, seed=0, comp=0, critfunc=None, constraints=None):
+    """EM_W_multi.R:116-180; critfunc None = identity (:116), constraints a dict as fconstraint makes it (:85-92)."""
+    crit = critfunc or (lambda x: x)
     N, p = X.shape; q = Y.shape[1]
-    Wnw, Cnw, Bnw, signw, siglatnw = initial_guess(p, q, initialGuess, customGuess)
+    Wnw, Cnw, Bnw, signw, siglatnw = initial_guess(p, q, initialGuess, customGuess, seed, comp)
+    Wnw, Cnw, Bnw, signw, siglatnw = _constrain(constraints, Wnw, Cnw, Bnw, signw, siglatnw)      # :142-146
     logvalue = [R.logl_w(X, Y, Wnw, Cnw, Bnw, signw[0], signw[1], siglatnw[0], siglatnw[1])]      # :150
     i = 0
     for i in range(1, EMsteps + 1):
@@ -92,14 +114,16 @@ def pplsi(X, Y, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None):
             return dict(W=None, C=None, B=None, sig=None, logvalue=None, Last_increment=None, Number_steps=i)
         fit = emstep_w(X, Y, Wnw, Cnw, Bnw, signw[0], signw[1], siglatnw[0], siglatnw[1])
         Bnw, Wnw, Cnw, signw, siglatnw = fit["B"], fit["W"], fit["C"], fit["sighat"], fit["siglathat"]
+        Wnw, Cnw, Bnw, signw, siglatnw = _constrain(constraints, Wnw, Cnw, Bnw, signw, siglatnw)  # :163-167
         logvalue.append(R.logl_w(X, Y, Wnw, Cnw, Bnw, signw[0], signw[1], siglatnw[0], siglatnw[1]))  # :171
-        if logvalue[i] - logvalue[i - 1] < atol:                                                     # :172
+        if crit(logvalue[i] - logvalue[i - 1]) < atol:                                               # :172
             break
     return dict(W=Wnw, C=Cnw, B=Bnw, sig=np.concatenate([signw, siglatnw]), logvalue=np.array(logvalue),
                 Last_increment=logvalue[i] - logvalue[i - 1], Number_steps=i)
 
 
-def ppls(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None):
+def ppls(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None, seed=0, critfunc=None,
+         constraints=None):
     """EM_W_multi.R:229-279: components one at a time with explicit deflation (:270-271)."""
     X = np.asarray(X, dtype=np.float64); Y = np.asarray(Y, dtype=np.float64)
     N, p = X.shape; q = Y.shape[1]; a = nr_comp
@@ -110,7 +134,7 @@ def ppls(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGu
     done = a
     for i in range(a):
         guess = customGuess[i] if isinstance(customGuess, (list, tuple)) else customGuess
-        fit = pplsi(Xc, Yc, EMsteps, atol, initialGuess, guess)
+        fit = pplsi(Xc, Yc, EMsteps, atol, initialGuess, guess, seed, i, critfunc, constraints[i] if constraints else None)
         if fit["B"] is None:                                                                         # :257-262
             done = i
             break

@@ -32,6 +32,14 @@ class Params(C.Structure):
                 ("sigE", C.c_double), ("sigF", C.c_double), ("sigH", C.c_double)]
 
 
+class Constraints(C.Structure):
+    _fields_ = [("mask", C.c_uint32), ("reserved", C.c_uint32), ("W", c_double_p), ("C", c_double_p),
+                ("B", C.c_double), ("sigE", C.c_double), ("sigF", C.c_double), ("sigH", C.c_double), ("sigT", C.c_double)]
+
+
+FIX_BITS = {"W": 1, "C": 2, "B": 4, "sigE": 8, "sigF": 16, "sigH": 32, "sigT": 64}
+
+
 class Timing(C.Structure):
     _fields_ = [("stream_ms", C.c_double), ("stream_launches", C.c_int64), ("loop_ms", C.c_double),
                 ("kernel_launches", C.c_int64), ("passes", C.c_int64), ("bytes_per_pass", C.c_int64),
@@ -70,6 +78,9 @@ SIGNATURES = {
     "ppls_fit_timing": (C.c_int, [_vp, C.POINTER(Timing)]),
     "ppls_fit_destroy": (C.c_int, [_vp]),
     "ppls_sequential_run": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_double, _vp, C.POINTER(Params), _vp, _vp, _i32p, _vp, _i32p]),
+    "ppls_sequential_run_ex": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, C.c_double, _vp, _vp, C.c_int32, C.POINTER(Params), _vp, _vp,
+                                         _i32p, _vp, _i32p]),
+    "ppls_initial_guess": (C.c_int, [_vp, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_int32, C.POINTER(Params)]),
     "ppls_loglik": (C.c_int, [_vp, _vp, C.c_int32, C.POINTER(Params), _vp]),
     "ppls_orth": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _vp, C.c_int64]),
     "ppls_variances": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, _vp, C.c_int64, _vp, C.c_double, _vp, _vp, _vp, _vp, _vp, _vp]),

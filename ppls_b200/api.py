@@ -17,7 +17,7 @@ import numpy as np
 
 from . import _lib as L
 
-__all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "logl_W", "orth", "normalise", "default_init",
+__all__ = ["Context", "Data", "Fit", "PPLS_simult", "PPLS_simult_batched", "PPLS", "fconstraint", "logl_W", "orth", "normalise", "default_init",
            "sequential_init", "default_context", "variances", "simulC", "meta_PPLSi"]
 
 
@@ -300,26 +300,37 @@ def default_init(p: int, q: int, a: int) -> dict:
                 sigE=1.0 / np.sqrt(p), sigF=1.0 / np.sqrt(q), sigH=0.1)
 
 
-def sequential_init(data: "Data", a: int) -> dict:
-    """Start state of PPLS_simult (EM_W_multi.R:762-771): 20 steps of the sequential fit per component,
-    run on the GPU over the resident data (ppls_sequential_run).
-    DEVIATION: the reference starts that fit from initialGuess='random' (R's RNG, :133, not reproducible
-    outside R); here it starts from 'equal'.  Pass `init=` to PPLS_simult for any other start."""
-    f0 = PPLS(None, None, a, 20, 1e-4, "equal", data=data, loglikelihoods=False)
-    if f0["W"].shape[1] < a:
-        raise RuntimeError("sequential start fit stopped early (rank-deficient residuals); pass init=")
-    sg = f0["sig"]
-    return dict(W=f0["W"], C=f0["C"], B=f0["B"], sigT=sg[:, 3], sigE=sg[a - 1, 0], sigF=sg[a - 1, 1], sigH=sg[a - 1, 2])
+def sequential_init(data: "Data", a: int, initialGuess: str = "random", seed: int = 0) -> dict:
+    """Start state of PPLS_simult (EM_W_multi.R:762-771): PPLS(X, Y, a, 20, 1e-4, 'random') -- 20 steps of the sequential
+    fit per component from a random start, run on the GPU over the resident data (ppls_sequential_run), with the
+    reference's three attempts (:762-764: a failed fit is retried twice with fresh draws; here attempt k uses seed + k).
+    The draws follow the reference's distributions (:133) on the counter-based generator, not R's RNG stream: the same
+    control flow and the same family of starts, repeatable for a given seed."""
+    last = None
+    for attempt in range(3):
+        try:
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")                      # suppressWarnings(...), :762
+                f0 = PPLS(None, None, a, 20, 1e-4, initialGuess, data=data, loglikelihoods=False, seed=seed + attempt)
+            if f0["W"].shape[1] < a:
+                raise RuntimeError("sequential start fit stopped early (rank-deficient residuals)")
+            sg = f0["sig"]
+            return dict(W=f0["W"], C=f0["C"], B=f0["B"], sigT=sg[:, 3], sigE=sg[a - 1, 0], sigF=sg[a - 1, 1], sigH=sg[a - 1, 2])
+        except (L.PPLSError, RuntimeError) as ex:
+            last = ex
+    raise RuntimeError(f"the sequential start fit failed three times ({last}); pass init=")
 
 
 def PPLS_simult(X, Y, a, EMsteps=10, atol=1e-4, type="SVD", init: Optional[dict] = None,
-                ctx: Optional[Context] = None, data: Optional[Data] = None, want_mu: bool = True, **kwargs):
+                ctx: Optional[Context] = None, data: Optional[Data] = None, want_mu: bool = True, seed: int = 0,
+                start: str = "random", **kwargs):
     """Simultaneous PPLS fit -- drop-in for PPLS_simult (Package/PPLS/R/EM_W_multi.R:758-807).
 
     Returns {'Expectations': {mu_T, mu_U, Ctt, Cuu, Cut, Cee, Cff, Chh}, 'loglik', 'estimates':
     {W, C, B, sigE, sigF, sigH, sigT}} with the reference's shapes (B, sigT, Ctt, Cuu, Cut
-    r x r diagonal matrices; Cee, Cff 1 x 1).  `init` replaces the start of :762-771 (default:
-    sequential_init, the same 20-step sequential fit started from 'equal' instead of 'random').
+    r x r diagonal matrices; Cee, Cff 1 x 1).  `init` replaces the start of :762-771 (default: sequential_init, the
+    reference's PPLS(X, Y, a, 20, 1e-4, 'random') with its three attempts, drawn from `seed`; start='equal' for a
+    deterministic data-independent start).
     `debug=` (the dense Expect_M, :643-667) is accepted and ignored with a warning: the dense
     form is O((p+q)^3) and exists in this repo only inside the CPU oracle."""
     if isinstance(type, (tuple, list)):
@@ -339,7 +350,7 @@ def PPLS_simult(X, Y, a, EMsteps=10, atol=1e-4, type="SVD", init: Optional[dict]
         data = Data.from_host(ctx, X, Y)
     try:
         if init is None:
-            init = sequential_init(data, a)                                                # :762-771
+            init = sequential_init(data, a, start, seed)                                   # :762-771
         W0, C0, B0, T0 = normalise(init["W"], init["C"], init["B"], init["sigT"])          # :773-778
         start = dict(W=W0, C=C0, B=B0, sigT=T0, sigE=init["sigE"], sigF=init["sigF"], sigH=init["sigH"])
         fit = Fit(data, start, a, EMsteps, atol, type)
@@ -413,30 +424,80 @@ def PPLS_simult_batched(X, Y, a, inits, EMsteps=10, atol=1e-4, type="SVD", ctx: 
     return res
 
 
-def _guess(p, q, kind, custom):
-    """Start state of one component (EM_W_multi.R:126-141): 'equal' or 'custom'."""
+def _guess(p, q, kind, custom, ctx=None, seed=0, component=0):
+    """Start state of one component (EM_W_multi.R:126-141): 'equal', 'random' (drawn on the device from the counter-based
+    generator keyed by (seed, component): ppls_initial_guess) or 'custom'."""
     if kind == "custom" or custom is not None:
         if custom is None:
             raise ValueError("initialGuess='custom' needs customGuess")
         g = custom
         return _ParamsBuf(p, q, 1, np.reshape(g["W"], (p, 1)), np.reshape(g["C"], (q, 1)), np.ravel(g["B"])[:1],
                           np.ravel(g["sigT"])[:1], g["sigE"], g["sigF"], g["sigH"])
-    if kind != "equal":
-        raise ValueError("initialGuess must be 'equal' or 'custom' here: 'random' needs R's RNG stream and 'o2m' "
-                         "needs OmicsPLS::o2m (pass their result as customGuess)")
-    return _ParamsBuf(p, q, 1, np.full((p, 1), 1.0 / np.sqrt(p)), np.full((q, 1), 1.0 / np.sqrt(q)), [1.0], [1.0],
-                      1.0 / p, 1.0 / q, 1.0)
+    if kind not in ("equal", "random"):
+        raise ValueError("initialGuess must be 'equal', 'random' or 'custom' here: 'o2m' needs OmicsPLS::o2m "
+                         "(pass its result as customGuess)")
+    g = _ParamsBuf(p, q, 1)
+    L.check(L.lib().ppls_initial_guess((ctx or default_context())._h, 0 if kind == "equal" else 1, p, q, int(seed), int(component),
+                                       C.byref(g.struct)))
+    return g
+
+
+def fconstraint(constraints=None) -> dict:
+    """fconstraint (EM_W_multi.R:85-92): a dict with the keys W, C, B, sigE, sigF, sigH, sigT, each None or the fixed value."""
+    outp = dict(W=None, C=None, B=None, sigE=None, sigF=None, sigH=None, sigT=None)
+    for k, v in (constraints or {}).items():
+        if k in outp:
+            outp[k] = v
+    return outp
+
+
+def _constraints_array(constraints, a, p, q):
+    """list of nr_comp fconstraint dicts -> (ctypes array of ppls_constraints, keep-alive list)."""
+    if constraints is None:
+        return None, []
+    if len(constraints) != a:
+        raise ValueError("There should be a list of constraints for each component, see ?PPLS.")      # :240
+    arr = (L.Constraints * a)()
+    keep = []
+    for i, c in enumerate(constraints):
+        c = fconstraint(c)
+        mask = 0
+        for name, bit in L.FIX_BITS.items():
+            v = c[name]
+            if v is None:
+                continue
+            mask |= bit
+            if name in ("W", "C"):
+                vec = np.ascontiguousarray(np.ravel(v), dtype=np.float64)
+                if vec.size != (p if name == "W" else q):
+                    raise ValueError(f"constraint on {name}: wrong length")
+                keep.append(vec)
+                setattr(arr[i], name, vec.ctypes.data_as(L.c_double_p))
+            else:
+                setattr(arr[i], name, float(np.ravel(v)[0]))
+        arr[i].mask = mask
+    return arr, keep
 
 
 def PPLS(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None,
-         ctx: Optional[Context] = None, data: Optional[Data] = None, loglikelihoods: bool = True):
+         ctx: Optional[Context] = None, data: Optional[Data] = None, loglikelihoods: bool = True, seed: int = 0,
+         critfunc=None, constraints=None):
     """Sequential PPLS fit -- mirror of PPLS (Package/PPLS/R/EM_W_multi.R:229-279) on the GPU: the fit
     PPLS_simult runs for its start values (:762).  critfunc = identity, no constraints.
 
     Returns {'W' p x a, 'C' q x a, 'B' [a], 'sig' a x 4 (sigX, sigY, sigH, sigT), 'Other_output':
     {'Last_increment', 'Number_steps', 'Loglikelihoods', 'logvalues'}}.  customGuess: one dict (used for
     every component, as the reference does) or a list with one dict per component.  If a noise s.d.
-    vanishes at component i the earlier components are returned with a warning (:257-262)."""
+    vanishes at component i the earlier components are returned with a warning (:257-262).  initialGuess='random'
+    (:133) draws every component's start on the device from (seed, component) -- the reference's distribution, not
+    R's RNG stream.  critfunc (:172): None / "identity" or "abs" (or the builtin abs); constraints: a list with one
+    fconstraint dict per component (:230, :142-146, :160-167)."""
+    if critfunc in (None, "identity"):
+        crit_abs = 0
+    elif critfunc in ("abs", abs, np.abs):
+        crit_abs = 1
+    else:
+        raise ValueError("critfunc must be the identity or abs (a flag crosses the C ABI, not an R closure)")
     if isinstance(initialGuess, (tuple, list)):
         initialGuess = initialGuess[0]
     a = int(nr_comp)
@@ -450,8 +511,8 @@ def PPLS(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGu
         p, q = data.p, data.q
         if p < a or q < a:
             raise ValueError("ncol(X) >= nr_comp and ncol(Y) >= nr_comp are required")
-        gs = [_guess(p, q, initialGuess, customGuess[i] if isinstance(customGuess, (list, tuple)) else customGuess)
-              for i in range(a)]
+        gs = [_guess(p, q, initialGuess, customGuess[i] if isinstance(customGuess, (list, tuple)) else customGuess,
+                     ctx=ctx, seed=seed, component=i) for i in range(a)]
         garr = (L.Params * a)(*[g.struct for g in gs])
         out = _ParamsBuf(p, q, a)
         sig = np.zeros((a, 4), order="F")
@@ -459,9 +520,10 @@ def PPLS(X, Y, nr_comp=1, EMsteps=100, atol=1e-4, initialGuess="equal", customGu
         steps = (C.c_int32 * a)()
         last = np.zeros(a)
         ndone = C.c_int32(0)
-        L.check(L.lib().ppls_sequential_run(ctx._h, data._h, a, int(EMsteps), float(atol), garr, C.byref(out.struct),
-                                            sig.ctypes.data, logv.ctypes.data, steps, last.ctypes.data,
-                                            C.byref(ndone)))
+        carr, _keep = _constraints_array(constraints, a, p, q)
+        L.check(L.lib().ppls_sequential_run_ex(ctx._h, data._h, a, int(EMsteps), float(atol), garr, carr, crit_abs,
+                                               C.byref(out.struct), sig.ctypes.data, logv.ctypes.data, steps, last.ctypes.data,
+                                               C.byref(ndone)))
         k = int(ndone.value)
         if k < a:
             warnings.warn(f"From component {k + 1} on the residuals are of rank < 1e-14 and calculations are stopped.")

@@ -790,6 +790,7 @@ struct ppls_fit {
   bool seq = false;              // sequential one-component fit (em_seq.cu) instead of the simultaneous update
   const double* prev = nullptr;  // [nprev][ld] loadings of the earlier components (device, owned by the caller)
   int nprev = 0;
+  SeqCons cons{};                // sequential fit: constraints / critfunc of this component
   bool cols = false;             // column-sharded: the update runs replicated on the GLOBAL (p+q) x r objects
   DataShape sg{};                // global shape (all ranks' column blocks)
   double *Gglob = nullptr, *Lglob = nullptr, *Lscratch_g = nullptr;
@@ -827,7 +828,8 @@ static void fit_free(ppls_fit* f) {
 }
 
 static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
-                           bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out);
+                           bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out,
+                           const SeqCons* cons = nullptr);
 extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
                                ppls_fit** out) {
   if (is_group(ctx)) {
@@ -850,7 +852,8 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
   return fit_create_impl(ctx, d, opts, init, false, nullptr, 0, nullptr, out);
 }
 static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* opts, const ppls_params* init,
-                           bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out) {
+                           bool seq, const double* prev, int nprev, const double* ssq_deflated, ppls_fit** out,
+                           const SeqCons* cons) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   *out = nullptr;
   int rc = ctx_activate(ctx);
@@ -868,6 +871,7 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
   if (!f) return fail(PPLS_E_OOM, "host allocation failed");
   f->ctx = ctx; f->data = d; f->opts = *opts; f->R = R;
   f->seq = seq; f->prev = prev; f->nprev = nprev;
+  if (cons) f->cons = *cons;
   if (seq && (R != 1 || d->colshard)) { fit_free(f); return fail(PPLS_E_UNSUPPORTED, "sequential fit: one component at a time, row-sharded data"); }
   const char* why = "";
   f->cols = d->colshard != 0;
@@ -910,8 +914,11 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
   }
   if (e == cudaSuccess) e = cudaMalloc(&f->Lscratch, Lbytes);
   if (e == cudaSuccess && !f->wide) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
-  if (e == cudaSuccess && f->wide)
-    e = cudaMalloc(&f->wide_ws, wide_workspace_doubles(d->s, f->wplan, &f->woff) * sizeof(double));
+  if (e == cudaSuccess && f->wide) {
+    const size_t wb = wide_workspace_doubles(d->s, f->wplan, &f->woff) * sizeof(double);
+    e = cudaMalloc(&f->wide_ws, wb);
+    if (e == cudaSuccess) e = cudaMemsetAsync(f->wide_ws, 0, wb, ctx->stream);      // pad rows / components of the mu arrays stay zero
+  }
   if (e == cudaSuccess) e = cudaMalloc(&f->momvec, (size_t)f->veclen * sizeof(double));
   if (e == cudaSuccess && !(getenv("PPLS_K2_SINGLE") && atoi(getenv("PPLS_K2_SINGLE"))))
   {
@@ -951,7 +958,7 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     if (e == cudaSuccess) rows_local_to_global<<<(ne + 255) / 256, 256, 0, ctx->stream>>>(f->L, f->Lglob, d->s.p2, d->s.q2, f->xoff, f->yoff_abs, R);
     if (e == cudaSuccess && allreduce_sum(ctx, f->Lglob, (size_t)f->sg.ld * R)) e = cudaErrorUnknown;
     if (e == cudaSuccess) e = launch_em_prepare(f->sg, R, f->Lglob, f->st, ctx->stream);
-  } else if (e == cudaSuccess && seq) e = launch_seq_update(d->s, nullptr, f->L, f->st, f->trace, prev, nprev, 1, ctx->stream);
+  } else if (e == cudaSuccess && seq) e = launch_seq_update(d->s, nullptr, f->L, f->st, f->trace, prev, nprev, 1, ctx->stream, &f->cons);
   else if (e == cudaSuccess) e = launch_em_prepare(d->s, R, f->L, f->st, ctx->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // L (host vector) must outlive the copy
   if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_CUDA, std::string("fit setup: ") + cudaGetErrorString(e)); }
@@ -1058,7 +1065,7 @@ static int fit_enqueue_pass(ppls_fit* f) {
   } else {
     rc = allreduce_sum(ctx, f->momvec, (size_t)f->veclen);
     if (rc) return rc;
-    if (f->seq) e = launch_seq_update(s, f->momvec, f->L, f->st, f->trace, f->prev, f->nprev, 0, ctx->stream);
+    if (f->seq) e = launch_seq_update(s, f->momvec, f->L, f->st, f->trace, f->prev, f->nprev, 0, ctx->stream, &f->cons);
     else e = launch_em_update(s, f->R, f->momvec, f->L, f->Lscratch, f->st, f->trace, f->opts.orth_type, f->upd_scratch, ctx->stream);
   }
   if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("update kernel: ") + cudaGetErrorString(e));
@@ -1407,6 +1414,15 @@ extern "C" int ppls_simult_run_batched(ppls_ctx* ctx, const ppls_data* d, const 
 extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int32_t EMsteps, double atol,
                                    const ppls_params* guesses, ppls_params* est, double* sig, double* logvalues,
                                    int32_t* steps, double* last_incr, int32_t* comps_done) {
+  return ppls_sequential_run_ex(ctx, d, nr_comp, EMsteps, atol, guesses, nullptr, 0, est, sig, logvalues, steps, last_incr, comps_done);
+}
+
+// ... with PPLSi's `constraints` (fconstraint, EM_W_multi.R:85-92; applied to the start, :142-146, and after every EM step,
+// :160-167) and `critfunc` (:172; identity or abs).
+extern "C" int ppls_sequential_run_ex(ppls_ctx* ctx, const ppls_data* d, int32_t nr_comp, int32_t EMsteps, double atol,
+                                      const ppls_params* guesses, const ppls_constraints* constraints, int32_t crit_abs,
+                                      ppls_params* est, double* sig, double* logvalues, int32_t* steps, double* last_incr,
+                                      int32_t* comps_done) {
   int rc = ctx_activate(ctx);
   if (rc) return rc;
   if (!d || !guesses || !est || !sig || !steps || !comps_done) return fail(PPLS_E_INVALID, "null argument");
@@ -1425,11 +1441,60 @@ extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr
   ppls_opts opts{};
   opts.r = 1; opts.max_steps = EMsteps; opts.atol = atol; opts.orth_type = PPLS_ORTH_SVD; opts.check_every = 8;
   *comps_done = 0;
+  double* dcons = nullptr;                      // fixed loadings of the current component, engine layout [ld]
+  CU(cudaMalloc(&dcons, (size_t)sh.ld * sizeof(double)));
+  struct Guard2 { double* p; ~Guard2() { cudaFree(p); } } guard2{dcons};
   for (int i = 0; i < a; ++i) {
     rc = check_params(&guesses[i], "guess");
     if (rc) return rc;
+    // constraints of this component: fixed values replace the start (:142-146) and every later estimate (:160-167)
+    SeqCons sc{};
+    sc.crit_abs = crit_abs ? 1 : 0;
+    ppls_params g = guesses[i];
+    std::vector<double> gW, gC;
+    double gB = g.B[0], gT = g.sigT[0];
+    if (constraints && constraints[i].mask) {
+      const ppls_constraints& c = constraints[i];
+      if (c.mask & ~127u) return fail(PPLS_E_INVALID, "unknown constraint bits");
+      if (((c.mask & PPLS_FIX_W) && !c.W) || ((c.mask & PPLS_FIX_C) && !c.C)) return fail(PPLS_E_INVALID, "constraint on W / C without values");
+      sc.mask = c.mask; sc.B = c.B; sc.sigE = c.sigE; sc.sigF = c.sigF; sc.sigH = c.sigH; sc.sigT = c.sigT;
+      if (c.mask & (PPLS_FIX_W | PPLS_FIX_C)) {
+        // The deflation is implicit here (the data is never rewritten): that is the reference's Xc - (Xc w) w' only for
+        // unit-norm loadings orthogonal to the earlier components -- which EM iterates are by construction, and which a
+        // fixed loading vector has to be.
+        std::vector<double> Lc((size_t)sh.ld, 0.0);
+        for (int side = 0; side < 2; ++side) {
+          if (!(c.mask & (side ? PPLS_FIX_C : PPLS_FIX_W))) continue;
+          const double* v = side ? c.C : c.W;
+          const int len = side ? sh.q : sh.p;
+          double nn = 0.0;
+          for (int j = 0; j < len; ++j) nn += v[j] * v[j];
+          bool ok = fabs(nn - 1.0) < 1e-10;
+          for (int k = 0; k < i && ok; ++k) {
+            const double* pk = (side ? est->C : est->W) + (size_t)k * len;
+            double dp = 0.0;
+            for (int j = 0; j < len; ++j) dp += pk[j] * v[j];
+            ok = fabs(dp) < 1e-10;
+          }
+          if (!ok) return fail(PPLS_E_UNSUPPORTED, "fixed loadings must have unit norm and be orthogonal to the earlier components "
+                                                   "(the deflation of the sequential fit is applied implicitly)");
+          for (int j = 0; j < len; ++j) Lc[(size_t)(side ? sh.p2 : 0) + j] = v[j];
+        }
+        CU(cudaMemcpyAsync(dcons, Lc.data(), Lc.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        sc.L = dcons;
+      }
+      if (c.mask & PPLS_FIX_W) g.W = const_cast<double*>(c.W);
+      if (c.mask & PPLS_FIX_C) g.C = const_cast<double*>(c.C);
+      if (c.mask & PPLS_FIX_B) gB = c.B;
+      if (c.mask & PPLS_FIX_SIGE) g.sigE = c.sigE;
+      if (c.mask & PPLS_FIX_SIGF) g.sigF = c.sigF;
+      if (c.mask & PPLS_FIX_SIGH) g.sigH = c.sigH;
+      if (c.mask & PPLS_FIX_SIGT) gT = c.sigT;
+      g.B = &gB; g.sigT = &gT;
+    }
     ppls_fit* f = nullptr;
-    rc = fit_create_impl(ctx, d, &opts, &guesses[i], true, dprev, i, ssq, &f);
+    rc = fit_create_impl(ctx, d, &opts, &g, true, dprev, i, ssq, &f, &sc);
     if (rc) return rc;
     int32_t done = 0, fin = 0;
     while (!fin) {
@@ -1451,8 +1516,8 @@ extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     fit_free(f);
     if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("sequential fit readback: ") + cudaGetErrorString(e));
-    for (int j = 0; j < sh.p; ++j) est->W[j + (size_t)i * sh.p] = L[j];
-    for (int j = 0; j < sh.q; ++j) est->C[j + (size_t)i * sh.q] = L[sh.p2 + j];
+    for (int j = 0; j < sh.p; ++j) est->W[j + (size_t)i * sh.p] = (sc.mask & PPLS_FIX_W) ? g.W[j] : L[j];
+    for (int j = 0; j < sh.q; ++j) est->C[j + (size_t)i * sh.q] = (sc.mask & PPLS_FIX_C) ? g.C[j] : L[sh.p2 + j];
     est->B[i] = h->b[0]; est->sigT[i] = h->t[0];
     sig[i + 0 * a] = h->sigE; sig[i + 1 * a] = h->sigF; sig[i + 2 * a] = h->sigH; sig[i + 3 * a] = h->t[0];
     steps[i] = k;
@@ -1463,6 +1528,37 @@ extern "C" int ppls_sequential_run(ppls_ctx* ctx, const ppls_data* d, int32_t nr
     *comps_done = i + 1;
   }
   if (*comps_done > 0) { est->sigE = sig[*comps_done - 1]; est->sigF = sig[*comps_done - 1 + a]; est->sigH = sig[*comps_done - 1 + 2 * a]; }
+  return PPLS_OK;
+}
+
+// ---- start state of one component: PPLSi's initialGuess "equal" / "random" (EM_W_multi.R:126-141) -----------------------
+extern "C" int ppls_initial_guess(ppls_ctx* ctx, int32_t kind, int64_t p, int64_t q, uint64_t seed, int32_t component,
+                                  ppls_params* out) {
+  if (ctx && !ctx->subs.empty()) ctx = ctx->subs[0];
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  rc = check_params(out, "out");
+  if (rc) return rc;
+  if (p < 1 || q < 1 || p > (1 << 24) || q > (1 << 24)) return fail(PPLS_E_INVALID, "p, q out of range");
+  if (component < 0) return fail(PPLS_E_INVALID, "negative component index");
+  if (kind == PPLS_GUESS_EQUAL) {
+    for (int64_t j = 0; j < p; ++j) out->W[j] = 1.0 / sqrt((double)p);
+    for (int64_t j = 0; j < q; ++j) out->C[j] = 1.0 / sqrt((double)q);
+    out->B[0] = 1.0; out->sigT[0] = 1.0; out->sigH = 1.0; out->sigE = 1.0 / (double)p; out->sigF = 1.0 / (double)q;
+    return PPLS_OK;
+  }
+  if (kind != PPLS_GUESS_RANDOM) return fail(PPLS_E_INVALID, "initialGuess must be 'equal' or 'random' here ('o2m': pass a custom guess)");
+  double* d = nullptr;
+  CU(cudaMalloc(&d, (size_t)(p + q + 5) * sizeof(double)));
+  cudaError_t e = launch_guess(d, (int)p, d + p, (int)q, d + p + q, seed, (uint32_t)component, ctx->stream);
+  double sc[5] = {0, 0, 0, 0, 0};
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out->W, d, (size_t)p * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out->C, d + p, (size_t)q * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(sc, d + p + q, sizeof(sc), cudaMemcpyDeviceToHost, ctx->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return fail(PPLS_E_CUDA, std::string("initial guess: ") + cudaGetErrorString(e));
+  out->B[0] = sc[0]; out->sigE = sc[1]; out->sigF = sc[2]; out->sigH = sc[3]; out->sigT[0] = sc[4];
   return PPLS_OK;
 }
 

@@ -23,20 +23,24 @@ struct DataShape {
   int32_t ld;       // p2 + q2
   // Wide shapes (ld > PANEL_LD_MIN) are stored PANEL-MAJOR instead: the padded column space is cut into
   // panels of PANEL_W columns (X panels, then Y panels; the last panel of each is zero-padded) and
-  // D[panel][n][PANEL_W] -- a CTA of the wide-row path then streams ONE contiguous 1 KB x n block.
+  // D[panel][n][PANEL_PITCH] -- a CTA of the wide-row path then streams ONE contiguous block of n panel rows.  A stored
+  // panel row is PANEL_PITCH = 128 + 4 doubles (4 zero pad values, +3.1 % bytes): one bulk copy lands a whole tile in
+  // shared memory with a row pitch of 1056 bytes, which is what makes the FP64 tensor-core fragment loads of
+  // em_wide2.cu conflict-free (8 rows x 32 bytes and 4 rows x 64 bytes both touch 32 distinct banks per half-warp).
   int32_t panel, npX, npY;
 };
 constexpr int PANEL_W = 128;
+constexpr int PANEL_PITCH = PANEL_W + 4;
 constexpr int PANEL_LD_MIN = 2304;
 __host__ __device__ inline size_t data_index(const DataShape& s, int64_t i, int c) {
   if (!s.panel) return (size_t)i * s.ld + c;
   const int cy = c - s.p2;
   const int P = (c < s.p2) ? c / PANEL_W : s.npX + cy / PANEL_W;
   const int j = (c < s.p2) ? c % PANEL_W : cy % PANEL_W;
-  return ((size_t)P * s.n + i) * PANEL_W + j;
+  return ((size_t)P * s.n + i) * PANEL_PITCH + j;
 }
 __host__ __device__ inline size_t data_elems(const DataShape& s) {
-  return s.panel ? (size_t)(s.npX + s.npY) * s.n * PANEL_W : (size_t)s.n * s.ld;
+  return s.panel ? (size_t)(s.npX + s.npY) * s.n * PANEL_PITCH : (size_t)s.n * s.ld;
 }
 
 // Layout of the per-CTA partial vector and of the reduced vector ("moment vector"):
@@ -96,10 +100,16 @@ struct WidePlan {            // two-pass wide-row path (em_wide.cu)
   int scX, scY, nslabX, nslabY;      // slab widths (columns) and counts
   int nrg, rows_per_rg, nblk_mu;
   int slots;                         // CTAs resident at once = grid of the persistent wide kernel (0: one CTA per work item)
+  int v2, nstage2;                   // DMMA form (em_wide2.cu; panel-major storage): nrg / rows_per_rg are whole 64-row tiles
+  int sm_count;
 };
-struct WideOffsets { size_t ppart, proj, mu, gpart, gram; };   // offsets (doubles) into the wide workspace
+struct WideOffsets { size_t ppart, proj, mu, gpart, gram, mu8; };   // offsets (doubles) into the wide workspace
 cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, const char** why);
 int64_t wide_npad(int64_t n);
+// em_wide2.cu: the two passes on the FP64 tensor pipe (panel-major storage)
+void plan_wide2(const DataShape& s, int sm_count, WidePlan* w);
+cudaError_t launch_wide2(int mode, const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st,
+                         double* ppart, const double* mu8, double* gpart, int sm_count, cudaStream_t stream);
 size_t wide_workspace_doubles(const DataShape& s, const WidePlan& w, WideOffsets* o);
 cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const double* D, const double* L,
                                 const FitState* st, double* ws, const WideOffsets& o, cudaStream_t stream);
@@ -201,8 +211,16 @@ size_t update_grid_scratch_doubles(int ld, int R);
 cudaError_t launch_em_prepare(const DataShape& s, int R, const double* L, FitState* st, cudaStream_t stream);
 
 // em_seq.cu: update of the sequential one-component fit (R = 1; `prev` = earlier components' loadings)
+// Constraints of PPLSi (fconstraint, EM_W_multi.R:85-92, applied at :142-146 and :160-167): fixed values that replace the
+// estimates after every EM step; critfunc (:172) = identity or abs.
+struct SeqCons {
+  uint32_t mask = 0;              // bit 0 W, 1 C, 2 B, 3 sigE, 4 sigF, 5 sigH, 6 sigT
+  int32_t crit_abs = 0;           // critfunc = abs
+  const double* L = nullptr;      // device [ld]: fixed loadings (W rows then C rows) where the mask says so
+  double B = 0, sigE = 0, sigF = 0, sigH = 0, sigT = 0;
+};
 cudaError_t launch_seq_update(const DataShape& s, const double* momvec, double* L, FitState* st, double* trace,
-                              const double* prev, int nprev, int prepare, cudaStream_t stream);
+                              const double* prev, int nprev, int prepare, cudaStream_t stream, const SeqCons* cons = nullptr);
 
 // data.cu
 cudaError_t launch_retile(const double* colmajor, int64_t ldc, int64_t nrows, int ncols,
@@ -224,6 +242,8 @@ cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t c
                          const double* Ltruth /*[ld][R]*/, const double* b, const double* t,
                          double sigE, double sigF, double sigH, cudaStream_t stream, const SynthOrth* orth = nullptr);
 
+// initialGuess = "random" (EM_W_multi.R:133) on the device generator: W [p], C [q], sc = {B, sigE, sigF, sigH, sigT}
+cudaError_t launch_guess(double* W, int p, double* C, int q, double* sc, uint64_t seed, uint32_t comp, cudaStream_t stream);
 // probe.cu: measured ceilings for bench.py's roofline lines
 cudaError_t probe_read(const void* x, size_t bytes, int sm_count, int launches, double* scratch, double* gbs, cudaStream_t stream);
 cudaError_t probe_dmma(int sm_count, double* scratch, double* tflops, cudaStream_t stream);

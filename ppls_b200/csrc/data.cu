@@ -293,4 +293,48 @@ cudaError_t launch_synth(double* D, const DataShape& s, int64_t row0, uint32_t c
   return cudaGetLastError();
 }
 
+// ---- initialGuess = "random" of PPLSi (Package/PPLS/R/EM_W_multi.R:133) on the counter-based generator ------------------
+//   Wnw = orth(runif(p)); Cnw = orth(runif(q)); Bnw = rchisq(1,1); siglatnw = rchisq(2,100)/100; signw = rchisq(2,10)/100
+// (orth of one column = the normalised vector; a chi-square with k degrees of freedom = the sum of k squared normals.)
+// R's RNG stream cannot exist outside R: the draws come from Philox (seed, component), streams 16 (W), 17 (C), 18 (scalars),
+// so only the DISTRIBUTION of the reference's start is reproduced, bit-exactly repeatable for a given seed.
+__device__ __forceinline__ double gen_uniform(uint64_t seed, uint32_t stream, uint64_t row, uint32_t col) {
+  uint32_t c[4] = {(uint32_t)row, (uint32_t)(row >> 32), col, stream};
+  philox4x32_10(c, (uint32_t)seed, (uint32_t)(seed >> 32));
+  return ((double)(c[0] >> 5) * 67108864.0 + (double)(c[1] >> 6) + 0.5) / 9007199254740992.0;
+}
+__global__ void __launch_bounds__(256) guess_kernel(double* __restrict__ W, int p, double* __restrict__ C, int q,
+                                                    double* __restrict__ sc /*B, sigE, sigF, sigH, sigT*/, uint64_t seed,
+                                                    uint32_t comp) {
+  __shared__ double red[256];
+  for (int side = 0; side < 2; ++side) {
+    double* v = side ? C : W;
+    const int n = side ? q : p;
+    double s = 0.0;
+    for (int j = threadIdx.x; j < n; j += 256) { const double u = gen_uniform(seed, 16u + side, comp, (uint32_t)j); v[j] = u; s += u * u; }
+    red[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if ((int)threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o]; __syncthreads(); }
+    const double nrm = sqrt(red[0]);
+    __syncthreads();
+    for (int j = threadIdx.x; j < n; j += 256) v[j] = v[j] / nrm;
+  }
+  if (threadIdx.x == 0) {
+    auto chisq = [&](uint32_t first, int k) {
+      double s = 0.0;
+      for (int e = 0; e < k; ++e) { const double z = gen_normal(seed, 18u, comp, first + (uint32_t)e); s += z * z; }
+      return s;
+    };
+    sc[0] = chisq(0u, 1);                  // Bnw
+    sc[3] = chisq(1u, 100) / 100.0;        // siglatnw[1] = sigH
+    sc[4] = chisq(101u, 100) / 100.0;      // siglatnw[2] = sigT
+    sc[1] = chisq(201u, 10) / 100.0;       // signw[1] = sigE
+    sc[2] = chisq(211u, 10) / 100.0;       // signw[2] = sigF
+  }
+}
+cudaError_t launch_guess(double* W, int p, double* C, int q, double* sc, uint64_t seed, uint32_t comp, cudaStream_t stream) {
+  guess_kernel<<<1, 256, 0, stream>>>(W, p, C, q, sc, seed, comp);
+  return cudaGetLastError();
+}
+
 }  // namespace ppls

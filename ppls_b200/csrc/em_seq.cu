@@ -23,6 +23,7 @@ struct SeqArgs {
   double* trace;          // logvalue[0 .. steps]
   const double* prev;     // [nprev][ld] loadings of the earlier components (unit norm, mutually orthogonal)
   int32_t nprev, p, q, p2, q2, ld, prepare;
+  SeqCons cons;
 };
 
 __device__ double seq_block_sum(double v, double* scratch) {       // fixed tree: deterministic
@@ -145,7 +146,10 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
     a.trace[k] = st->loglik_last;
     // ---- end of the component?  (:172 break rule, EMsteps exhausted, :153-155 vanishing noise variance) ----
     bool done = false;
-    if (k >= 1 && (a.trace[k] - a.trace[k - 1]) < st->atol) done = true;
+    if (k >= 1) {                                        // critfunc(logvalue[i+1] - logvalue[i]) < atol, critfunc = I or abs
+      const double incr = a.trace[k] - a.trace[k - 1];
+      if ((a.cons.crit_abs ? fabs(incr) : incr) < st->atol) done = true;
+    }
     if (k >= st->max_steps) done = true;
     if (!isfinite(st->loglik_last)) { st->status = PPLS_E_NONFINITE; done = true; }
     if (!done && (sigX < 100 * 2.220446049250313e-16 || sigY < 100 * 2.220446049250313e-16)) {
@@ -156,6 +160,12 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
     s_done = done ? 1 : 0;
     if (!done) {
       seq_em_scalars(st, xx, xy, yy, N, p, q);
+      // constraints (:160-167): fixed values replace the estimates before the log-likelihood of the step is taken
+      if (a.cons.mask & 4u) st->b[0] = a.cons.B;
+      if (a.cons.mask & 8u) st->sigE = a.cons.sigE;
+      if (a.cons.mask & 16u) st->sigF = a.cons.sigF;
+      if (a.cons.mask & 32u) st->sigH = a.cons.sigH;
+      if (a.cons.mask & 64u) st->t[0] = a.cons.sigT;
       st->pass = k + 1;
       const bool ok = isfinite(st->b[0]) && isfinite(st->sigE) && isfinite(st->sigF) && isfinite(st->sigH) && isfinite(st->t[0]);
       if (!ok) { st->status = PPLS_E_NONFINITE; raise_done(st); st->steps_done = k; s_done = 1; }
@@ -165,12 +175,17 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
   __syncthreads();
   if (s_done) return;
   // ---- W = normalized(t(Xc) mu_T / N), C = normalized(t(Yc) mu_U / N)  (loglC.cpp:358,363,381-382) ---------
-  for (int e = threadIdx.x; e < a.ld; e += SEQ_THREADS) a.L[e] = a.momvec[e];
+  // (a constrained side keeps its fixed loadings, deflated like the data they multiply: Xc w = X (I - P P') w)
+  for (int e = threadIdx.x; e < a.ld; e += SEQ_THREADS) {
+    const bool fixed = (e < a.p2) ? (a.cons.mask & 1u) != 0 : (a.cons.mask & 2u) != 0;
+    a.L[e] = fixed ? a.cons.L[e] : a.momvec[e];
+  }
   __syncthreads();
   seq_deflate(a.L, a.prev, a.nprev, a.ld, 0, a.p2, scratch);          // t(Xc) = (I - P P') t(X)
   seq_deflate(a.L, a.prev, a.nprev, a.ld, a.p2, a.ld, scratch);
   for (int part = 0; part < 2; ++part) {
     const int lo = part ? a.p2 : 0, hi = part ? a.ld : a.p2;
+    if (a.cons.mask & (part ? 2u : 1u)) continue;                    // block-uniform
     double s = 0.0;
     for (int e = lo + threadIdx.x; e < hi; e += SEQ_THREADS) { const double v = a.L[e] / N; a.L[e] = v; s += v * v; }
     s = seq_block_sum(s, scratch);
@@ -181,8 +196,9 @@ __global__ void __launch_bounds__(SEQ_THREADS, 1) seq_update_kernel(const SeqArg
 }
 
 cudaError_t launch_seq_update(const DataShape& s, const double* momvec, double* L, FitState* st, double* trace,
-                              const double* prev, int nprev, int prepare, cudaStream_t stream) {
+                              const double* prev, int nprev, int prepare, cudaStream_t stream, const SeqCons* cons) {
   SeqArgs a;
+  if (cons) a.cons = *cons;
   a.momvec = momvec; a.L = L; a.st = st; a.trace = trace; a.prev = prev; a.nprev = nprev; a.prepare = prepare;
   a.p = s.p; a.q = s.q; a.p2 = s.p2; a.q2 = s.q2; a.ld = s.ld;
   seq_update_kernel<<<1, SEQ_THREADS, 0, stream>>>(a);

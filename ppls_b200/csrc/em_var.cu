@@ -337,8 +337,8 @@ static GramArgs gram_args(const VarPlan& p, const DataShape& s, const double* D,
   a.D = D; a.n = s.n; a.nb = p.nb; a.ntiles = p.ntiles;
   a.w2 = which ? s.q2 : s.p2;
   if (s.panel) {
-    a.pitch = PANEL_W; a.block_stride = (size_t)s.n * PANEL_W;
-    a.base = which ? (size_t)s.npX * s.n * PANEL_W : 0; a.masked = 0;
+    a.pitch = PANEL_PITCH; a.block_stride = (size_t)s.n * PANEL_PITCH;
+    a.base = which ? (size_t)s.npX * s.n * PANEL_PITCH : 0; a.masked = 0;
   } else {
     a.pitch = (size_t)s.ld; a.block_stride = VT; a.base = (size_t)p.c0; a.masked = 1;
   }

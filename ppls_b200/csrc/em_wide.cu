@@ -69,7 +69,7 @@ __global__ void __maxnreg__(NCH * R <= 10 ? 96 : 255) wide_kernel(const WideArgs
   // the compute warps finish the current one, and the ring / barriers are set up once per launch.
   const int nslab = a.nslabX + a.nslabY;
   const int nitem = nslab * a.nrg;
-  const uint32_t pitch = (uint32_t)NCH * 64u * 8u;                            // smem row pitch (bytes)
+  const uint32_t pitch = a.panel ? PANEL_PITCH * 8u : (uint32_t)NCH * 64u * 8u;   // smem row pitch (bytes): a stored panel row / the slab width
   const uint32_t mubytes = (MODE == MODE_ACCUM) ? WIDE_TR * R * 8u : 0u;
   const uint32_t stage_bytes = WIDE_TR * pitch + mubytes;
   const uint32_t sbase = smem_u32(smem);
@@ -106,7 +106,7 @@ __global__ void __maxnreg__(NCH * R <= 10 ? 96 : 255) wide_kernel(const WideArgs
       int64_t gt = 0;                                                          // tiles issued so far (all items)
       for (int it = blockIdx.x; it < nitem; it += gridDim.x) {
         const Item q = item_of(it);
-        const uint32_t segbytes = a.panel ? PANEL_W * 8u : (uint32_t)q.width * 8u;   // a panel is stored whole (zero-padded)
+        const uint32_t segbytes = a.panel ? PANEL_PITCH * 8u : (uint32_t)q.width * 8u;   // a panel is stored whole (zero-padded)
         for (int t = 0; t < q.ntile; ++t, ++gt) {
           if (gt >= a.nstage) mbar_wait(bars + 8u * (a.nstage + s), par);
           const int64_t row0 = q.rbeg + (int64_t)(MODE == MODE_ACCUM ? q.ntile - 1 - t : t) * WIDE_TR;   // pass 2 walks back
@@ -114,7 +114,7 @@ __global__ void __maxnreg__(NCH * R <= 10 ? 96 : 255) wide_kernel(const WideArgs
           const uint32_t full = bars + 8u * s, dst = sbase + s * stage_bytes;
           mbar_expect_tx(full, (uint32_t)rows * segbytes + mubytes);
           if (a.panel) {
-            bulk_g2s(dst, a.D + ((size_t)q.slab * a.n + row0) * PANEL_W, (uint32_t)rows * segbytes, full);
+            bulk_g2s(dst, a.D + ((size_t)q.slab * a.n + row0) * PANEL_PITCH, (uint32_t)rows * segbytes, full);
           } else {
             for (int i = 0; i < rows; ++i)
               bulk_g2s(dst + (uint32_t)i * pitch, a.D + (size_t)(row0 + i) * a.ld + q.cbeg, segbytes, full);
@@ -256,7 +256,7 @@ constexpr int WMU_ROWS = 128;
 __global__ void __launch_bounds__(WMU_ROWS) wide_mu_kernel(const double* __restrict__ proj, int64_t n, int R,
                                                            double* __restrict__ mu /*[2][npad][R]*/, int64_t npad,
                                                            double* __restrict__ gram_part /*[nblk][3R^2]*/,
-                                                           const FitState* st) {
+                                                           const FitState* st, double* __restrict__ mu8 /*[2][npad][8] or null*/) {
   if (st->done) return;
   __shared__ double pj[WMU_ROWS][2 * MAXR];
   const int64_t i = (int64_t)blockIdx.x * WMU_ROWS + threadIdx.x;
@@ -265,8 +265,10 @@ __global__ void __launch_bounds__(WMU_ROWS) wide_mu_kernel(const double* __restr
     for (int k = 0; k < R; ++k) {
       const double xw = proj[i * 2 * R + k], yc = proj[i * 2 * R + R + k];
       pj[threadIdx.x][k] = xw; pj[threadIdx.x][R + k] = yc;
-      mu[(size_t)i * R + k] = st->aT[k] * xw + st->bT[k] * yc;
-      mu[(size_t)(npad + i) * R + k] = st->aU[k] * xw + st->bU[k] * yc;
+      const double mt = st->aT[k] * xw + st->bT[k] * yc, mw = st->aU[k] * xw + st->bU[k] * yc;
+      mu[(size_t)i * R + k] = mt;
+      mu[(size_t)(npad + i) * R + k] = mw;
+      if (mu8) { mu8[(size_t)i * 8 + k] = mt; mu8[(size_t)(npad + i) * 8 + k] = mw; }     // (pad components / rows stay zero)
     }
   }
   __syncthreads();
@@ -327,8 +329,8 @@ static wide_kernel_t wide_lookup(int R, int NCH, int mode) {
   return nullptr;
 }
 
-static size_t wide_smem(int R, int NCH, int nstage, int mode) {
-  const size_t stage = (size_t)WIDE_TR * NCH * 64 * 8 + (mode == MODE_ACCUM ? (size_t)WIDE_TR * R * 8 : 0);
+static size_t wide_smem(int R, int NCH, int nstage, int mode, int panel = 0) {
+  const size_t stage = (size_t)WIDE_TR * (panel ? PANEL_PITCH : NCH * 64) * 8 + (mode == MODE_ACCUM ? (size_t)WIDE_TR * R * 8 : 0);
   return stage * nstage + (mode == MODE_ACCUM ? (size_t)NCH * 64 * R * 8 : 0) + 2 * (size_t)nstage * 8;
 }
 
@@ -365,13 +367,13 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
   }
   w->R = R;
   w->nstage = 4;
-  while (w->nstage > 2 && wide_smem(R, w->NCH, w->nstage, MODE_ACCUM) > 200 * 1024) --w->nstage;
+  while (w->nstage > 2 && wide_smem(R, w->NCH, w->nstage, MODE_ACCUM, s.panel) > 200 * 1024) --w->nstage;
   // CTAs resident at once, as the runtime sees it for these kernels (registers and shared memory)
   int occ_min = 1 << 30;
   for (int mode = MODE_PROJECT; mode <= MODE_ACCUM; ++mode) {
     wide_kernel_t k = wide_lookup(R, w->NCH, mode);
     if (!k) { *why = "wide path: no kernel for this (nr_comp, slab width)"; return cudaErrorInvalidValue; }
-    const size_t smem = wide_smem(R, w->NCH, w->nstage, mode);
+    const size_t smem = wide_smem(R, w->NCH, w->nstage, mode, s.panel);
     cudaError_t e = cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { *why = "cudaFuncSetAttribute failed (wide path)"; return e; }
     int occ = 0;
@@ -395,13 +397,18 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
   w->nrg = (int)((s.n + w->rows_per_rg - 1) / w->rows_per_rg);
   { const char* ep = getenv("PPLS_WIDE_PERSIST"); w->slots = (ep && *ep && atoi(ep) == 0) ? 0 : slots; }   // 0: one CTA per work item
   w->nblk_mu = (int)((s.n + WMU_ROWS - 1) / WMU_ROWS);
+  w->v2 = 0; w->nstage2 = 0; w->sm_count = sm_count;
+  {
+    const char* ed = getenv("PPLS_WIDE_DMMA");
+    if (s.panel && !(ed && *ed && atoi(ed) == 0)) plan_wide2(s, sm_count, w);      // tensor-pipe form of both passes
+  }
   if (getenv("PPLS_K1_VERBOSE") && atoi(getenv("PPLS_K1_VERBOSE")))
     fprintf(stderr, "[ppls] wide plan: R=%d slabs X %d x %d cols, Y %d x %d cols, NCH=%d, row groups %d x %d rows, stages=%d, resident CTAs %d\n",
             R, w->nslabX, w->scX, w->nslabY, w->scY, w->NCH, w->nrg, w->rows_per_rg, w->nstage, slots);
   return cudaSuccess;
 }
 
-int64_t wide_npad(int64_t n) { return (n + WIDE_TR - 1) / WIDE_TR * WIDE_TR; }
+int64_t wide_npad(int64_t n) { return (n + 63) / 64 * 64; }      // whole tiles of either form (16 / 64 rows)
 
 size_t wide_workspace_doubles(const DataShape& s, const WidePlan& w, WideOffsets* o) {
   size_t off = 0;
@@ -411,6 +418,7 @@ size_t wide_workspace_doubles(const DataShape& s, const WidePlan& w, WideOffsets
   o->mu = take((size_t)2 * wide_npad(s.n) * w.R);
   o->gpart = take((size_t)w.nrg * s.ld * w.R);
   o->gram = take((size_t)w.nblk_mu * 3 * w.R * w.R);
+  o->mu8 = take(w.v2 ? (size_t)2 * wide_npad(s.n) * 8 : 0);      // DMMA form: mu with the components padded to 8
   return off;
 }
 
@@ -423,7 +431,11 @@ cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const dou
   a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage; a.panel = s.panel;
   const int nitem = (w.nslabX + w.nslabY) * w.nrg;
   const int grid = (w.slots > 0 && w.slots < nitem) ? w.slots : nitem;
-  wide_lookup(w.R, w.NCH, MODE_PROJECT)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_PROJECT), stream>>>(a);
+  if (w.v2) {
+    cudaError_t e2 = launch_wide2(1, w, s, D, L, st, ws + o.ppart, nullptr, nullptr, w.sm_count, stream);
+    if (e2 != cudaSuccess) return e2;
+  } else
+  wide_lookup(w.R, w.NCH, MODE_PROJECT)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_PROJECT, s.panel), stream>>>(a);
   const int64_t ne = s.n * w.R;
   wide_proj_sum_kernel<<<(unsigned)((ne + 31) / 32), dim3(32, 8), 0, stream>>>(ws + o.ppart, s.n, w.R, w.nslabX, w.nslabY, ws + o.proj, st);
   return cudaGetLastError();
@@ -433,14 +445,19 @@ cudaError_t launch_wide_project(const WidePlan& w, const DataShape& s, const dou
 cudaError_t launch_wide_accum(const WidePlan& w, const DataShape& s, const double* D, const double* L,
                               const FitState* st, double* ws, const WideOffsets& o, double* momvec,
                               cudaStream_t stream) {
-  wide_mu_kernel<<<w.nblk_mu, WMU_ROWS, 0, stream>>>(ws + o.proj, s.n, w.R, ws + o.mu, wide_npad(s.n), ws + o.gram, st);
+  wide_mu_kernel<<<w.nblk_mu, WMU_ROWS, 0, stream>>>(ws + o.proj, s.n, w.R, ws + o.mu, wide_npad(s.n), ws + o.gram, st,
+                                                   w.v2 ? ws + o.mu8 : nullptr);
   WideArgs a{};
   a.D = D; a.L = L; a.st = st; a.ppart = ws + o.ppart; a.mu = ws + o.mu; a.gpart = ws + o.gpart;
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.q2 = s.q2; a.scX = w.scX; a.scY = w.scY; a.nslabX = w.nslabX;
   a.nslabY = w.nslabY; a.nrg = w.nrg; a.rows_per_rg = w.rows_per_rg; a.nstage = w.nstage; a.panel = s.panel;
   const int nitem = (w.nslabX + w.nslabY) * w.nrg;
   const int grid = (w.slots > 0 && w.slots < nitem) ? w.slots : nitem;
-  wide_lookup(w.R, w.NCH, MODE_ACCUM)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_ACCUM), stream>>>(a);
+  if (w.v2) {
+    cudaError_t e2 = launch_wide2(2, w, s, D, L, st, nullptr, ws + o.mu8, ws + o.gpart, w.sm_count, stream);
+    if (e2 != cudaSuccess) return e2;
+  } else
+  wide_lookup(w.R, w.NCH, MODE_ACCUM)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_ACCUM, s.panel), stream>>>(a);
   const int64_t glen = (int64_t)s.ld * w.R; const int glen2 = 3 * w.R * w.R;
   wide_finalize_kernel<<<(unsigned)((glen + glen2 + 255) / 256), 256, 0, stream>>>(ws + o.gpart, w.nrg, glen, ws + o.gram, w.nblk_mu,
                                                                               glen2, momvec, st);

@@ -32,7 +32,7 @@ def fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, xchg):
         # the sequential fit (start-value path of PPLS_simult, NCCL exchange) with several components: the deflation
         # of component i+1 reads the Gram of the pass that ended component i, which the host has over-queued
         seq = PPLS(None, None, 3, 15, 1e-4, "equal", data=d, loglikelihoods=False)
-        sim = PPLS_simult(None, None, 2, EMsteps=6, atol=-np.inf, data=d, want_mu=False)       # init=None: sequential start
+        sim = PPLS_simult(None, None, 2, EMsteps=6, atol=-np.inf, data=d, want_mu=False, start="equal")   # init=None: sequential start
         seq["simult_default_start"] = sim
         # batched multi-start on row shards (both data paths: packs through K1, two-GEMM form): start 0 is `st`
         inits = [st] + [synth.start_params(truth, 50 + j) for j in range(2)]

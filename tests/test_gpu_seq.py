@@ -108,24 +108,103 @@ def test_sequential_argument_errors(ctx):
     with pytest.raises(ValueError):
         PPLS(g["X"], g["Y"], 6, ctx=ctx)           # ncol(X) = 5 < nr_comp
     with pytest.raises(ValueError):
-        PPLS(g["X"], g["Y"], 1, initialGuess="random", ctx=ctx)
+        PPLS(g["X"], g["Y"], 1, initialGuess="o2m", ctx=ctx)        # needs OmicsPLS::o2m: pass its result as customGuess
     with pytest.raises(PPLSError):
         PPLS(g["X"], g["Y"], 1, EMsteps=0, ctx=ctx)
 
 
+def test_random_initial_guess_is_the_reference_distribution_and_the_oracle_bits(ctx):
+    """initialGuess = "random" (EM_W_multi.R:133) drawn on the device: the same numbers as the host restatement
+    (oracle/cbind.py::random_guess), unit-norm positive loadings, chi-square scalars with the reference's means
+    (B ~ chisq_1, sigH, sigT ~ chisq_100/100, sigE, sigF ~ chisq_10/100), different for every (seed, component)."""
+    import ctypes as C
+    from oracle import cbind
+    from ppls_b200 import _lib as L
+    from ppls_b200.api import _guess
+    Lo = cbind.load()
+    p, q = 257, 33
+    draws = []
+    for seed, comp in [(7, 0), (7, 1), (8, 0)] + [(100 + s, 0) for s in range(60)]:
+        g = _guess(p, q, "random", None, ctx=ctx, seed=seed, component=comp)
+        o = cbind.random_guess(Lo, p, q, seed, comp)
+        assert np.max(np.abs(g.W[:, 0] - o["W"])) < 1e-15 and np.max(np.abs(g.C[:, 0] - o["C"])) < 1e-15
+        assert (g.B[0], g.sigT[0], g.struct.sigE, g.struct.sigF, g.struct.sigH) == (o["B"], o["sigT"], o["sigE"], o["sigF"], o["sigH"])
+        assert abs(np.sum(g.W**2) - 1) < 1e-14 and np.all(g.W > 0) and abs(np.sum(g.C**2) - 1) < 1e-14
+        draws.append((g.B[0], g.sigT[0], g.struct.sigH, g.struct.sigE, g.struct.sigF))
+    d = np.array(draws)
+    assert len({tuple(r) for r in draws}) == len(draws)
+    assert 0.5 < d[:, 0].mean() < 1.6 and np.all(np.abs(d[:, 1:3].mean(axis=0) - 1.0) < 0.06)
+    assert np.all(np.abs(d[:, 3:5].mean(axis=0) - 0.1) < 0.02)
+    eq = _guess(p, q, "equal", None, ctx=ctx)
+    assert np.allclose(eq.W, 1 / np.sqrt(p)) and eq.struct.sigE == 1.0 / p and eq.B[0] == 1.0
+
+
+@pytest.mark.parametrize("name,seed", [("seq_equal_3", 1), ("seq_odd_2", 5)])
+def test_sequential_fit_from_random_starts(ctx, name, seed):
+    from oracle import ppls_seq
+    from ppls_b200 import PPLS
+    g = load_seq(name)
+    a = int(g["a"])
+    ref = ppls_seq.ppls(g["X"], g["Y"], a, 20, 1e-4, "random", seed=seed)
+    out = PPLS(g["X"], g["Y"], a, 20, 1e-4, "random", ctx=ctx, seed=seed, loglikelihoods=False)
+    _check(out, ref["W"], ref["C"], ref["B"], ref["sig"], ref["Number_steps"], ref["logvalues"])
+
+
+def test_constraints_and_critfunc(ctx):
+    """PPLS(..., critfunc, constraints) (EM_W_multi.R:229-230; fconstraint :85-92, applied at :142-146 and :160-167; critfunc
+    at :172) against the oracle's restatement: fixed scalars per component, fixed loadings on the first component,
+    critfunc = abs, and the refusal of fixed loadings that are not orthogonal to the earlier components."""
+    from oracle import ppls_seq
+    from ppls_b200 import PPLS, PPLSError, fconstraint
+    g = load_seq("seq_equal_3")
+    X, Y = g["X"], g["Y"]
+    p, q = X.shape[1], Y.shape[1]
+    rng = np.random.default_rng(3)
+    w = rng.standard_normal(p); w /= np.linalg.norm(w)
+    cases = [
+        ([dict(sigH=0.2), dict(B=0.7, sigE=0.3), {}], None),
+        ([dict(W=w, sigT=1.1), dict(sigF=0.25), dict(sigH=0.1, B=1.3)], "abs"),
+        ([dict(C=np.ones(q) / np.sqrt(q)), {}, {}], None),
+    ]
+    for cons, crit in cases:
+        ref = ppls_seq.ppls(X, Y, 3, 25, 1e-4, "equal", critfunc=(abs if crit else None), constraints=cons)
+        out = PPLS(X, Y, 3, 25, 1e-4, "equal", ctx=ctx, loglikelihoods=False, critfunc=crit,
+                   constraints=[fconstraint(c) for c in cons])
+        _check(out, ref["W"], ref["C"], ref["B"], ref["sig"], ref["Number_steps"], ref["logvalues"])
+    out = PPLS(X, Y, 1, 10, 1e-4, "equal", ctx=ctx, loglikelihoods=False, constraints=[dict(W=w, B=0.9, sigE=0.4)])
+    assert np.array_equal(out["W"][:, 0], w) and out["B"][0] == 0.9 and out["sig"][0, 0] == 0.4
+    with pytest.raises(PPLSError):                 # second component's fixed loadings not orthogonal to the first's estimate
+        PPLS(X, Y, 2, 5, 1e-4, "equal", ctx=ctx, loglikelihoods=False, constraints=[{}, dict(W=w)])
+    with pytest.raises(ValueError):
+        PPLS(X, Y, 2, 5, ctx=ctx, constraints=[{}])                 # one list entry per component (:240)
+    with pytest.raises(ValueError):
+        PPLS(X, Y, 1, 5, ctx=ctx, critfunc=lambda x: x * x)
+
+
 def test_ppls_simult_whole_call_with_its_own_start(ctx):
-    """PPLS_simult(X, Y, a, ...) without init=: start fit (:762-771, 'equal' instead of 'random'), start
-    normalisation (:773-778), loop (:780-793), result normalisation (:794-799) -- against the same chain of
-    oracle functions."""
+    """PPLS_simult(X, Y, a, ...) without init=: the reference's start fit PPLS(X, Y, a, 20, 1e-4, 'random') (:762-771, drawn
+    from `seed` on the counter-based generator), start normalisation (:773-778), loop (:780-793), result normalisation
+    (:794-799) -- against the same chain of oracle functions; also start='equal'."""
     from oracle import ppls_ref, ppls_seq
     from ppls_b200 import PPLS_simult
     g = load_seq("seq_equal_3")
     X, Y, a = g["X"], g["Y"], 3
+    f0 = ppls_seq.ppls(X, Y, a, 20, 1e-4, "random", seed=11)
+    W0, C0, B0, T0 = ppls_ref.normalise(f0["W"], f0["C"], f0["B"], f0["sig"][:, 3])
+    ref = ppls_ref.ppls_simult_loop(X, Y, W0, C0, B0, f0["sig"][a - 1, 0], f0["sig"][a - 1, 1], f0["sig"][a - 1, 2], T0,
+                                    EMsteps=30, atol=1e-4)
+    out = PPLS_simult(X, Y, a, EMsteps=30, atol=1e-4, ctx=ctx, seed=11)
+    # a random start is far from the fixed point: the rounding differences of the 3 x 20-step start fit are amplified over
+    # the first steps of the loop (1.4e-10 at step 1-4 here) before the iteration contracts them again (1e-12 at the end)
+    assert len(out["loglik"]) == len(ref["loglik"]) and relmax(out["loglik"], ref["loglik"]) < 1e-9
+    assert relmax(out["loglik"][-5:], ref["loglik"][-5:]) < TOL_LOGLIK
+    for k in ("W", "C", "B", "sigT"):
+        assert relmax(out["estimates"][k], ref["estimates"][k]) < TOL_PARAM, k
     f0 = ppls_seq.ppls(X, Y, a, 20, 1e-4, "equal")
     W0, C0, B0, T0 = ppls_ref.normalise(f0["W"], f0["C"], f0["B"], f0["sig"][:, 3])
     ref = ppls_ref.ppls_simult_loop(X, Y, W0, C0, B0, f0["sig"][a - 1, 0], f0["sig"][a - 1, 1], f0["sig"][a - 1, 2], T0,
                                     EMsteps=30, atol=1e-4)
-    out = PPLS_simult(X, Y, a, EMsteps=30, atol=1e-4, ctx=ctx)
+    out = PPLS_simult(X, Y, a, EMsteps=30, atol=1e-4, ctx=ctx, start="equal")
     assert len(out["loglik"]) == len(ref["loglik"]) and relmax(out["loglik"], ref["loglik"]) < TOL_LOGLIK
     for k in ("W", "C", "B", "sigT"):
         assert relmax(out["estimates"][k], ref["estimates"][k]) < TOL_PARAM, k
