@@ -14,10 +14,16 @@
 #include "ppls_b200.h"
 
 namespace {
-struct Handles {                       // released on every exit path, incl. R errors
+// A device-resident dataset: context (one GPU, or several GPUs of one node driven from this R process:
+// ppls_ctx_create_multi) + the uploaded, re-tiled X and Y.  Held by R as an external pointer (ppls_b200_open) so that
+// repeated PPLS_simult_b200 calls on the same X, Y do not pay the host-to-device upload again; released by the
+// finalizer when R collects the pointer, or at once by ppls_b200_close.
+struct Handles {
   ppls_ctx* ctx = nullptr;
   ppls_data* data = nullptr;
-  ~Handles() { if (data) ppls_data_destroy(data); if (ctx) ppls_ctx_destroy(ctx); }
+  int64_t N = 0, p = 0, q = 0;
+  void release() { if (data) ppls_data_destroy(data); if (ctx) ppls_ctx_destroy(ctx); data = nullptr; ctx = nullptr; }
+  ~Handles() { release(); }
 };
 inline void check(int rc, const char* what) {
   if (rc != PPLS_OK) Rcpp::stop("%s failed (%d): %s", what, rc, ppls_last_error());
@@ -25,22 +31,45 @@ inline void check(int rc, const char* what) {
 }  // namespace
 
 // [[Rcpp::export]]
-RcppExport SEXP PPLS_simult_b200_run(SEXP Xs, SEXP Ys, SEXP W0s, SEXP C0s, SEXP B0s, SEXP sigE0s, SEXP sigF0s,
-                                     SEXP sigH0s, SEXP sigT0s, SEXP EMstepss, SEXP atols, SEXP types, SEXP devices) {
+// devices: integer vector of CUDA device ids, e.g. 0L or 0:7 (rows of X and Y are then split over the GPUs).
+RcppExport SEXP ppls_b200_open(SEXP Xs, SEXP Ys, SEXP devicess) {
 BEGIN_RCPP
-  Rcpp::NumericMatrix X(Xs), Y(Ys), W0(W0s), C0(C0s);      // views on R memory (REALSXP), no copies
+  Rcpp::NumericMatrix X(Xs), Y(Ys);                        // views on R memory (REALSXP), no copies
+  Rcpp::IntegerVector dev(devicess);
+  if (Y.nrow() != X.nrow()) Rcpp::stop("X and Y must have the same number of rows");
+  if (dev.size() < 1) Rcpp::stop("need at least one device");
+  Rcpp::XPtr<Handles> h(new Handles(), true);              // finalizer: delete -> ~Handles
+  h->N = X.nrow(); h->p = X.ncol(); h->q = Y.ncol();
+  std::vector<int> ids(dev.begin(), dev.end());
+  check(ppls_ctx_create_multi(&h->ctx, ids.data(), (int)ids.size()), "ppls_ctx_create_multi");
+  check(ppls_data_from_host(h->ctx, X.begin(), h->N, Y.begin(), h->N, h->N, h->p, h->q, &h->data), "ppls_data_from_host");
+  return h;
+END_RCPP
+}
+
+// [[Rcpp::export]]
+RcppExport SEXP ppls_b200_close(SEXP hs) {
+BEGIN_RCPP
+  Rcpp::XPtr<Handles> h(hs);
+  h->release();
+  return R_NilValue;
+END_RCPP
+}
+
+// [[Rcpp::export]]
+RcppExport SEXP PPLS_simult_b200_run(SEXP hs, SEXP W0s, SEXP C0s, SEXP B0s, SEXP sigE0s, SEXP sigF0s,
+                                     SEXP sigH0s, SEXP sigT0s, SEXP EMstepss, SEXP atols, SEXP types) {
+BEGIN_RCPP
+  Rcpp::XPtr<Handles> h(hs);
+  if (!h->ctx || !h->data) Rcpp::stop("the ppls_b200 handle has been closed");
+  Rcpp::NumericMatrix W0(W0s), C0(C0s);
   Rcpp::NumericVector B0(B0s), T0(sigT0s);
-  const int64_t N = X.nrow(), p = X.ncol(), q = Y.ncol();
+  const int64_t N = h->N, p = h->p, q = h->q;
   const int r = W0.ncol();
-  if (Y.nrow() != N) Rcpp::stop("X and Y must have the same number of rows");
   if (W0.nrow() != p || C0.nrow() != q || C0.ncol() != r || B0.size() != r || T0.size() != r)
     Rcpp::stop("start values have the wrong shape");
   const int steps = Rcpp::as<int>(EMstepss);
   const std::string type = Rcpp::as<std::string>(types);
-
-  Handles h;
-  check(ppls_ctx_create(&h.ctx, Rcpp::as<int>(devices)), "ppls_ctx_create");
-  check(ppls_data_from_host(h.ctx, X.begin(), N, Y.begin(), N, N, p, q, &h.data), "ppls_data_from_host");
 
   std::vector<double> W0c(W0.begin(), W0.end()), C0c(C0.begin(), C0.end()), B0c(B0.begin(), B0.end()),
       T0c(T0.begin(), T0.end());                            // ppls_params wants non-const pointers
@@ -54,7 +83,7 @@ BEGIN_RCPP
   Rcpp::NumericVector B(r), sigT(r), loglik(steps), mom(3 * r + 2 + r * r);
   ppls_params est{W.begin(), C.begin(), B.begin(), sigT.begin(), 0.0, 0.0, 0.0};
   int32_t done = 0;
-  check(ppls_simult_run(h.ctx, h.data, &opts, &init, &est, loglik.begin(), &done, mom.begin(), muT.begin(),
+  check(ppls_simult_run(h->ctx, h->data, &opts, &init, &est, loglik.begin(), &done, mom.begin(), muT.begin(),
                         muU.begin()), "ppls_simult_run");
   Rcpp::NumericVector ll(loglik.begin(), loglik.begin() + done);
   for (int e = 0; e < r * r; ++e) Chh[e] = mom[3 * r + 2 + e];
