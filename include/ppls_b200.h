@@ -243,6 +243,19 @@ int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params*
 int ppls_orth(ppls_ctx* ctx, const double* G, int64_t ldG, int64_t n, int32_t r, int32_t orth_type,
               double* out, int64_t ldOut);
 
+/* orth(G, type) WITHOUT ANY ALLOCATION.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same kernel as ppls_orth; the working copy of G that the QR form needs lives in a static device array of
+ * PPLS_ORTH_NOALLOC_MAX_ELEMS doubles (512 KB, held by every GPU that loads the library until exit) instead of a
+ * cudaMalloc'ed buffer.  G_dev, out_dev: DEVICE pointers on the context's device, n x r in the engine's ROW-major
+ * layout (element (j, k) at [j * r + k]); they must not overlap.  n * r > PPLS_ORTH_NOALLOC_MAX_ELEMS -> PPLS_E_UNSUPPORTED
+ * with a message that names the limit.  The call is enqueued on the context's stream and has completed on return; it
+ * calls no cudaMalloc, cudaFree or allocating library routine.  All calls share the one scratch array (it keeps the last
+ * call's contents; nothing in it needs to start at zero): calls that overlap on the GPU -- other contexts, other host
+ * threads on the same device -- race. */
+#define PPLS_ORTH_NOALLOC_MAX_ELEMS 65536
+int ppls_orth_noalloc(ppls_ctx* ctx, const double* G_dev, int64_t n, int32_t r, int32_t orth_type, double* out_dev);
+
 /* ---- standard errors of the loadings: variances.PPLS_simult(fit, data, XorY) (EM_W_multi.R:830-860) ---- */
 /* which = 0: data = X, mu = fit$Expectations$mu_T (n x r column-major, host, this rank's rows), Cdiag =
  * diag(fit$Expectations$Ctt); which = 1: data = Y, mu = mu_U, Cdiag = diag(Cuu).  sigE = fit$estimates$sigE

@@ -83,6 +83,7 @@ SIGNATURES = {
     "ppls_initial_guess": (C.c_int, [_vp, C.c_int32, C.c_int64, C.c_int64, C.c_uint64, C.c_int32, C.POINTER(Params)]),
     "ppls_loglik": (C.c_int, [_vp, _vp, C.c_int32, C.POINTER(Params), _vp]),
     "ppls_orth": (C.c_int, [_vp, _vp, C.c_int64, C.c_int64, C.c_int32, C.c_int32, _vp, C.c_int64]),
+    "ppls_orth_noalloc": (C.c_int, [_vp, _vp, C.c_int64, C.c_int32, C.c_int32, _vp]),
     "ppls_variances": (C.c_int, [_vp, _vp, C.c_int32, C.c_int32, _vp, C.c_int64, _vp, C.c_double, _vp, _vp, _vp, _vp, _vp, _vp]),
     "ppls_data_simulc": (C.c_int, [_vp, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_uint64,
                                    C.POINTER(Params), _vp, _vp, _vp, _vp, _vpp]),

@@ -1590,6 +1590,23 @@ extern "C" int ppls_orth(ppls_ctx* ctx, const double* G, int64_t ldG, int64_t n,
   return PPLS_OK;
 }
 
+// orth(G, type) on device pointers with the kernel's scratch in a static device array: allocates nothing (em_update.cu).
+extern "C" int ppls_orth_noalloc(ppls_ctx* ctx, const double* G_dev, int64_t n, int32_t r, int32_t orth_type, double* out_dev) {
+  if (ctx && !ctx->subs.empty()) ctx = ctx->subs[0];
+  int rc = ctx_activate(ctx);
+  if (rc) return rc;
+  if (!G_dev || !out_dev) return fail(PPLS_E_INVALID, "null G or out");
+  if (r < 1 || r > MAXR) return fail(PPLS_E_INVALID, "nr_comp must be in 1..8");
+  if (n < r) return fail(PPLS_E_INVALID, "orth: need r <= nrow(G)");
+  if (orth_type != PPLS_ORTH_SVD && orth_type != PPLS_ORTH_QR) return fail(PPLS_E_INVALID, "'arg' should be one of 'SVD', 'QR'");
+  if (n * (int64_t)r > orth_static_max_elems())
+    return fail(PPLS_E_UNSUPPORTED, "ppls_orth_noalloc: n * r = " + std::to_string(n * (int64_t)r) + " exceeds the static scratch of " +
+                                    std::to_string(orth_static_max_elems()) + " doubles (PPLS_ORTH_NOALLOC_MAX_ELEMS); use ppls_orth");
+  CU(launch_orth_static(r, G_dev, (int)n, out_dev, orth_type, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  return PPLS_OK;
+}
+
 extern "C" int ppls_loglik(ppls_ctx* ctx, const ppls_data* d, int32_t r, const ppls_params* theta, double* out) {
   if (!out) return fail(PPLS_E_INVALID, "null output pointer");
   ppls_opts opts{};

@@ -182,6 +182,9 @@ cudaError_t launch_meta_update(const DataShape& s, int J, const double* momvecs,
                                int prepare, cudaStream_t stream);
 cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaStream_t stream);
 cudaError_t launch_orth(int R, const double* G, int n, double* out, int orth_type, double* work, cudaStream_t stream);
+// the same kernel with its scratch in a static device array (no allocation): device pointers, n * R <= orth_static_max_elems()
+cudaError_t launch_orth_static(int R, const double* G, int n, double* out, int orth_type, cudaStream_t stream);
+long long orth_static_max_elems();
 
 // ---- standard errors of the loadings (em_var.cu; variances.PPLS_simult, EM_W_multi.R:830-860) -----------
 struct VarPlan {

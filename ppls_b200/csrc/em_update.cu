@@ -512,6 +512,44 @@ cudaError_t launch_orth_polar(int R, const double* G, int n, double* out, cudaSt
   return launch_orth(R, G, n, out, PPLS_ORTH_SVD, nullptr, stream);
 }
 
+// ---- orth(G, type) without any allocation (ppls_orth_noalloc) --------------------------------------------------------
+// The QR form needs a working copy of G (destroyed by the Householder sweeps): `work` above, which ppls_orth gets from
+// cudaMalloc.  Callers that may not allocate (code under CUDA graph capture, tight serving loops) get the same kernel
+// with that scratch in a file-scope device array of ORTH_STATIC_MAX doubles (512 KB; every GPU that loads the library
+// holds it until exit).  All calls share the array: calls that overlap on the GPU race.  Nothing in it has to start at
+// zero (the kernel overwrites the part it uses with a copy of G before reading it).
+constexpr long long ORTH_STATIC_MAX = PPLS_ORTH_NOALLOC_MAX_ELEMS;
+static __device__ __align__(256) double g_orth_scratch[ORTH_STATIC_MAX];
+
+// Device address of the scratch on the CURRENT device.  In host code `g_orth_scratch` is a host-side stand-in, not a
+// device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+static cudaError_t orth_scratch_ptr(double** out) {
+  static double* ptrs[64] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  if (!ptrs[dev]) {
+    double* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_orth_scratch);
+    if (e != cudaSuccess) return e;
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return cudaSuccess;
+}
+
+long long orth_static_max_elems() { return ORTH_STATIC_MAX; }
+
+// G, out: DEVICE pointers, [n][R] row-major.  No cudaMalloc / cudaFree / allocating library call.
+cudaError_t launch_orth_static(int R, const double* G, int n, double* out, int orth_type, cudaStream_t stream) {
+  if ((long long)n * R > ORTH_STATIC_MAX) return cudaErrorInvalidValue;
+  double* work = nullptr;
+  cudaError_t e = orth_scratch_ptr(&work);
+  if (e != cudaSuccess) return e;
+  return launch_orth(R, G, n, out, orth_type, work, stream);
+}
+
 int update_grid_blocks(int ld) {
   int nb = (ld + GT - 1) / GT;
   if (nb > 96) nb = 96;
