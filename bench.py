@@ -218,6 +218,8 @@ class Env:
                 idt.copy_(torch.frombuffer(bytearray(Context.nccl_unique_id()), dtype=torch.uint8))
             dist.broadcast(idt, 0)
             self.ctx = Context(self.local, self.rank, self.world, bytes(idt.cpu().numpy().tobytes()))
+            # host-side barrier (gloo): a rank that waits here runs NO kernel on its GPU (an NCCL barrier would spin one)
+            self.host_group = dist.new_group(backend="gloo")
         else:
             self.ctx = Context(self.local)
 
@@ -327,6 +329,7 @@ def bench_stream(env, name, K, W, args, want_e2e):
     loop_ms = tm1["loop_ms"] - tm0["loop_ms"]
     k1_ms = (tm1["stream_ms"] - tm0["stream_ms"]) / max(tm1["stream_launches"] - tm0["stream_launches"], 1)
     tail_ms = (tm1["tail_ms"] - tm0["tail_ms"]) / K
+    scalar_ms = (tm1.get("scalar_ms", 0.0) - tm0.get("scalar_ms", 0.0)) / K
     launches = tm1["kernel_launches"] - tm0["kernel_launches"]
     per_rank = None
     if world > 1:
@@ -417,7 +420,7 @@ def bench_stream(env, name, K, W, args, want_e2e):
                    "generate_s": round(gen_s, 2), "wall_ms_per_step": wall_ms / K,
                    "exchange": ("none (1 GPU)" if world == 1 else "one-shot peer stores + flags, summed in rank order inside the update kernel"
                                 if tm1.get("peer_exchange") else "NCCL allreduce"),
-                   "tail_ms_per_step": tail_ms,
+                   "tail_ms_per_step": tail_ms, "tail_scalar_part_ms_per_step": scalar_ms,
                    "per_rank_ms_step_k1_tail": per_rank},
         "clocks": clocks, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -517,6 +520,54 @@ def cpu_baseline(args, name, truth, start, N, p, q, r):
             "fused_cpu_note": f"oracle/ppls_fused.py: single-pass OpenMP restatement (best-effort CPU, {omp} threads), same sample and scaling"}
 
 
+def e2e_single_process(env, name, K, args):
+    """N > 1, rank 0 only (the other ranks have released their data and wait): the SAME end-to-end call made the way ONE
+    R session makes it -- a single process driving all N GPUs through ppls_ctx_create_multi (Context.multi): pinned host X, Y
+    -> rows split over the devices and uploaded concurrently -> K EM steps with the peer exchange -> estimates back."""
+    import torch
+    from ppls_b200 import Context, Data, Fit, synth
+    N, p, q, r = WORKLOADS[name]
+    if args.rows and name == args.workload:
+        N = args.rows
+    world = env.world
+    truth = synth.truth_params(p, q, r)
+    start = synth.start_params(truth, seed=1)
+    full = args.e2e_rows == 0 and 8 * N * (p + q) <= 0.55 * host_budget_bytes()
+    ns = N if full else min(N, (args.e2e_rows or 1_000_000) * world)
+    mctx = Context.multi(list(range(world)))
+    pinned = None
+    try:
+        try:
+            pinned = PinnedPair(ns, p, q)
+        except Exception as ex:
+            print(f"[bench] single-process e2e: pinned buffers unavailable ({ex})", file=sys.stderr)
+            return None
+        d0 = Data.synthetic(mctx, ns, p, q, truth, seed=SEED)
+        d0.export(0, ns, out=(pinned.X, pinned.Y))
+        d0.close()
+        mctx.sync(); torch.cuda.synchronize()
+        e0 = time.perf_counter()
+        d2 = Data.from_host(mctx, pinned.X, pinned.Y)
+        up_s = time.perf_counter() - e0
+        f2 = Fit(d2, start, r, EMsteps=K, atol=-float("inf"), type="SVD")
+        f2.run()
+        res = f2.result(want_mu=False)
+        mctx.sync()
+        e_s = time.perf_counter() - e0
+        f2.close(); d2.close()
+    finally:
+        if pinned is not None:
+            pinned.close()
+        mctx.close()
+    scale = N / ns
+    return {"value": K / (e_s * scale), "unit": UNIT, "h2d_bytes_per_step": int(8 * N * (p + q) / K),
+            "d2h_bytes_per_step": int(8 * ((p + q) * r + 2 * r + 3 + K) / K),
+            "path": f"ONE process, {world} GPUs (ppls_ctx_create_multi): upload " + ("the full data" if ns == N else f"{ns} rows, time scaled x{scale:.1f}")
+                    + f" from pinned host memory split over the devices, {K} EM steps, download estimates+loglik",
+            "full_size": ns == N, "seconds_sample": e_s, "upload_seconds_sample": up_s,
+            "upload_gbs_total": 8 * ns * (p + q) / up_s / 1e9, "loglik_last": float(res["loglik"][-1])}
+
+
 def run_ours(args):
     from ppls_b200 import synth
     env = Env(args)
@@ -545,6 +596,15 @@ def run_ours(args):
             except BaseException as ex:                 # a side workload must not take the headline line down
                 others[name] = {"error": f"{type(ex).__name__}: {ex}"}
                 env.barrier()
+    e2e_sp = None
+    if env.world > 1 and not args.no_e2e and args.workload != "c5":
+        env.barrier()                                   # every rank has released its data
+        if env.rank == 0:
+            try:
+                e2e_sp = e2e_single_process(env, args.workload, K, args)
+            except BaseException as ex:
+                e2e_sp = {"error": f"{type(ex).__name__}: {ex}"}
+        env.dist.barrier(group=env.host_group)          # the others wait on the host: rank 0's kernels have their GPUs to themselves
     cpu = None
     if env.rank == 0 and not args.no_cpu and env.world == 1:
         N, p, q, r = WORKLOADS[args.workload]
@@ -557,6 +617,8 @@ def run_ours(args):
                "gpu_launches": main["gpu_launches"], "roofline": main["roofline"]}
         if main.get("e2e"):
             out["e2e"] = main["e2e"]
+        if e2e_sp:
+            out["e2e_single_process"] = e2e_sp
         if "loglik_best" in main:
             out["loglik_best"] = main["loglik_best"]
         if cpu:

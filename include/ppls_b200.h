@@ -86,6 +86,8 @@ typedef struct {
   int64_t peer_exchange;  /* 1: the moment vector travels by the one-shot peer exchange, 0: NCCL / single GPU */
   double  stream_phase_ms;/* fused launches (one kernel per EM iteration): device-clock time of the streaming phase
                              alone, summed; tail_ms is then the device-clock time of reduction + exchange + update */
+  double  scalar_ms;      /* fused launches: of tail_ms, the time until CTA 0 has finished the scalar part (reduction of its
+                             elements + exchange + log-likelihood, E-step moments, break rule, M-step scalars) */
 } ppls_timing;
 
 const char* ppls_version(void);

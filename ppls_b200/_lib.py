@@ -43,7 +43,7 @@ FIX_BITS = {"W": 1, "C": 2, "B": 4, "sigE": 8, "sigF": 16, "sigH": 32, "sigT": 6
 class Timing(C.Structure):
     _fields_ = [("stream_ms", C.c_double), ("stream_launches", C.c_int64), ("loop_ms", C.c_double),
                 ("kernel_launches", C.c_int64), ("passes", C.c_int64), ("bytes_per_pass", C.c_int64),
-                ("tail_ms", C.c_double), ("peer_exchange", C.c_int64), ("stream_phase_ms", C.c_double)]
+                ("tail_ms", C.c_double), ("peer_exchange", C.c_int64), ("stream_phase_ms", C.c_double), ("scalar_ms", C.c_double)]
 
 
 # every exported symbol of include/ppls_b200.h: name -> (restype, argtypes)

@@ -19,6 +19,7 @@ UNITS = {
     **{f"em_stream_inst.cu@r{r}": [f"-DPPLS_INST_R={r}", "-fmad=false"] for r in range(1, 9)},
     "em_wide.cu": [],
     "em_wide2.cu": [],
+    "em_wide3.cu": [],
     "em_update.cu": ["-fmad=false"],
     "em_seq.cu": ["-fmad=false"],
     "em_var.cu": [],

@@ -101,7 +101,7 @@ struct ppls_data {
   std::vector<int64_t> shard_row0;
 };
 
-static const size_t XCHG_CTRL = 1024, XCHG_SLOT = 65536;   // exchange block: control words | inbox of 2 x world x slot doubles
+static const size_t XCHG_CTRL = XCHG_INBOX_OFFSET, XCHG_SLOT = 65536;   // exchange block: control words, per-CTA flags | inbox of 2 x world x slot doubles
 
 static int ctx_activate(const ppls_ctx* ctx) {
   if (!ctx) return fail(PPLS_E_INVALID, "null context");
@@ -215,6 +215,7 @@ static void xchg_setup(ppls_ctx* c) {
   for (int r = 0; r < W; ++r) {
     char* base = (char*)c->xpeer[r];
     x.flags[r] = (unsigned long long*)base;                     // [2][XCHG_MAXW] = 256 B
+    x.cflags[r] = (unsigned long long*)(base + XCHG_CTRL_BYTES);
     x.inbox[r] = (double*)(base + XCHG_CTRL);
   }
   x.epoch = (unsigned long long*)(c->xbuf + 512);
@@ -289,6 +290,7 @@ extern "C" int ppls_ctx_create_multi(ppls_ctx** out, const int* device_ids, int 
     for (int r = 0; r < n_devices; ++r) {
       char* base = g->subs[r]->xbuf;
       x.flags[r] = (unsigned long long*)base;
+      x.cflags[r] = (unsigned long long*)(base + XCHG_CTRL_BYTES);
       x.inbox[r] = (double*)(base + XCHG_CTRL);
     }
     x.epoch = (unsigned long long*)(c->xbuf + 512);
@@ -890,6 +892,8 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     e = plan_wide(d->s, R, ctx->sm_count, &f->wplan, &why);
     if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_UNSUPPORTED, "streaming-kernel plan: " + why1 + "; " + why); }
     f->wide = true;
+    // one pass from HBM when the data is not column-sharded (the sharded form exchanges the projections between the passes)
+    if (!f->cols) { f->wplan.R = R; plan_wide3(d->s, R, ctx->sm_count, &f->wplan); }
   }
   f->veclen = momvec_len(d->s.ld, R);
   if (ctx->group && (f->wide || f->cols || seq || (size_t)f->veclen > XCHG_SLOT)) {
@@ -899,7 +903,13 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
   }
   {
     const char* ef = getenv("PPLS_FUSE_TAIL");
-    f->fused = !f->wide && !f->cols && !seq && opts->orth_type == PPLS_ORTH_SVD && f->plan.grid >= 32 &&
+    // multi-GPU: every rank must take the same decision AND run the same grid (row CTA b of every rank owns the same rows
+    // of the moment vector and exchanges them with CTA b of the peers), so the test uses global quantities only: the
+    // smallest shard, floor(N / world) rows, must fill one tile per SM.
+    const bool grid_ok = ctx->world == 1 ? f->plan.grid >= 32
+                                         : (!f->wide && d->n_total / ctx->world >= (int64_t)ctx->sm_count * f->plan.T &&
+                                            ctx->sm_count <= XCHG_MAXCTA);
+    f->fused = !f->wide && !f->cols && !seq && opts->orth_type == PPLS_ORTH_SVD && grid_ok &&
                stream_tail_fits(f->plan, d->s) && !(ef && *ef && atoi(ef) == 0) &&
                (ctx->world == 1 || (ctx->xchg_on && (size_t)f->veclen <= XCHG_SLOT));
   }
@@ -909,8 +919,8 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     const size_t tb = stream_tail_scratch_doubles(f->plan) * sizeof(double);
     e = cudaMalloc(&f->tail_scratch, tb);
     if (e == cudaSuccess) e = cudaMemsetAsync(f->tail_scratch, 0, tb, ctx->stream);     // barrier words, clocks
-    if (e == cudaSuccess) e = cudaMallocHost(&f->clk_host, 4 * sizeof(unsigned long long));
-    if (e == cudaSuccess) memset(f->clk_host, 0, 4 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMallocHost(&f->clk_host, 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) memset(f->clk_host, 0, 8 * sizeof(unsigned long long));
   }
   if (e == cudaSuccess) e = cudaMalloc(&f->Lscratch, Lbytes);
   if (e == cudaSuccess && !f->wide) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
@@ -963,7 +973,7 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);   // L (host vector) must outlive the copy
   if (e != cudaSuccess) { fit_free(f); return fail(PPLS_E_CUDA, std::string("fit setup: ") + cudaGetErrorString(e)); }
   f->tm.kernel_launches = 1;
-  f->tm.bytes_per_pass = (int64_t)(f->wide ? 16 : 8) * d->s.n * ((int64_t)d->s.p + d->s.q);
+  f->tm.bytes_per_pass = (int64_t)((f->wide && !f->wplan.v3) ? 16 : 8) * d->s.n * ((int64_t)d->s.p + d->s.q);
   *out = f;
   return PPLS_OK;
 }
@@ -981,12 +991,17 @@ static int fit_poll(ppls_fit* f) {
   { int rc0 = ctx_activate(ctx); if (rc0) return rc0; }
   CU(cudaMemcpyAsync(f->st_host, f->st, sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
   if (f->fused)
-    CU(cudaMemcpyAsync(f->clk_host, f->tail_scratch + stream_tail_clock_offset(f->plan), 3 * sizeof(unsigned long long),
+    CU(cudaMemcpyAsync(f->clk_host, f->tail_scratch + stream_tail_clock_offset(f->plan), 8 * sizeof(unsigned long long),
                        cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   if (f->fused) {       // device clocks (globaltimer) of the fused launches: streaming phase | reduction + exchange + update
     f->tm.stream_phase_ms = (double)f->clk_host[0] * 1e-6;
     f->tm.tail_ms = (double)f->clk_host[1] * 1e-6;
+    f->tm.scalar_ms = (double)f->clk_host[4] * 1e-6;
+    if (getenv("PPLS_TAIL_VERBOSE") && f->clk_host[2])
+      fprintf(stderr, "[ppls] fused tail per launch (us): streaming %.1f | tail %.1f = CTA 0: own sums %.1f + staging %.1f + scalar arithmetic %.1f (+ flag) ...\n",
+              f->clk_host[0] * 1e-3 / f->clk_host[2], f->clk_host[1] * 1e-3 / f->clk_host[2], f->clk_host[5] * 1e-3 / f->clk_host[2],
+              f->clk_host[6] * 1e-3 / f->clk_host[2], f->clk_host[7] * 1e-3 / f->clk_host[2]);
   }
   for (auto& pr : f->ev_tail) {       // .first is the K1 end event (owned by ev_k1, recycled below)
     float ms = 0.f;
@@ -1028,7 +1043,10 @@ static int fit_enqueue_pass(ppls_fit* f) {
     f->passes += 1;
     return PPLS_OK;
   }
-  if (f->wide) {
+  if (f->wide && f->wplan.v3) {
+    e = launch_wide_single(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, f->momvec, ctx->stream);
+    if (timing) { cudaEventRecord(b, ctx->stream); f->ev_k1.emplace_back(a, b); }
+  } else if (f->wide) {
     e = launch_wide_project(f->wplan, s, f->data->D, f->L, f->st, f->wide_ws, f->woff, ctx->stream);
     if (e == cudaSuccess && f->cols) {      // column-sharded: the N x 2r projection sums are what ranks exchange
       rc = allreduce_sum(ctx, f->wide_ws + f->woff.proj, (size_t)s.n * 2 * f->R);
@@ -1239,6 +1257,7 @@ extern "C" int ppls_fit_timing(const ppls_fit* f, ppls_timing* out) {
       const ppls_timing& t = f->parts[i]->tm;
       out->stream_ms = std::max(out->stream_ms, t.stream_ms); out->loop_ms = std::max(out->loop_ms, t.loop_ms);
       out->tail_ms = std::max(out->tail_ms, t.tail_ms); out->stream_phase_ms = std::max(out->stream_phase_ms, t.stream_phase_ms);
+      out->scalar_ms = std::max(out->scalar_ms, t.scalar_ms);
       out->kernel_launches += t.kernel_launches; out->bytes_per_pass += t.bytes_per_pass;
     }
     return PPLS_OK;

@@ -102,10 +102,21 @@ struct WidePlan {            // two-pass wide-row path (em_wide.cu)
   int slots;                         // CTAs resident at once = grid of the persistent wide kernel (0: one CTA per work item)
   int v2, nstage2;                   // DMMA form (em_wide2.cu; panel-major storage): nrg / rows_per_rg are whole 64-row tiles
   int sm_count;
+  // single-pass, L2-pipelined form (em_wide3.cu): lanes (row groups with a pipeline each) x CTAs per lane
+  int v3, v3_lanes, v3_cpl, v3_lag, v3_nstage, v3_ns, v3_chunks_per_lane, v3_nchunk;
 };
-struct WideOffsets { size_t ppart, proj, mu, gpart, gram, mu8; };   // offsets (doubles) into the wide workspace
+struct WideOffsets { size_t ppart, proj, mu, gpart, gram, mu8, cnt; };   // offsets (doubles) into the wide workspace
 cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, const char** why);
 int64_t wide_npad(int64_t n);
+// em_wide3.cu: ONE pass from HBM (persistent cooperative kernel, second pass out of the L2)
+bool plan_wide3(const DataShape& s, int R, int sm_count, WidePlan* w);
+size_t wide3_ring_doubles(const DataShape& s, const WidePlan& w);
+size_t wide3_counter_doubles(const WidePlan& w);
+cudaError_t launch_wide3(const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st, double* pring,
+                         double* mu, double* mu8, double* gpart, double* gram_part, double* counters, cudaStream_t stream);
+// the whole iteration of the wide path when the single-pass form is planned (kernel + fixed-order sums -> momvec)
+cudaError_t launch_wide_single(const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st,
+                               double* ws, const WideOffsets& o, double* momvec, cudaStream_t stream);
 // em_wide2.cu: the two passes on the FP64 tensor pipe (panel-major storage)
 void plan_wide2(const DataShape& s, int sm_count, WidePlan* w);
 cudaError_t launch_wide2(int mode, const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st,
@@ -137,9 +148,15 @@ cudaError_t launch_em_stream(const StreamPlan& plan, const DataShape& s, const d
 // straight into every peer's inbox over NVLink (peer-mapped cudaIpc memory), raises a flag there, and the
 // update kernel of each rank sums the world's inbox slots in rank order (bitwise identical on all ranks).
 constexpr int XCHG_MAXW = 16;
+constexpr int XCHG_MAXCTA = 160;          // per-CTA flags of the fused tail: one word per (parity, source rank, CTA)
+// exchange block of a rank: [control words 1 KB | per-CTA flags | inbox]
+constexpr size_t XCHG_CTRL_BYTES = 1024;
+constexpr size_t XCHG_CFLAG_BYTES = (size_t)2 * XCHG_MAXW * XCHG_MAXCTA * 8;
+constexpr size_t XCHG_INBOX_OFFSET = XCHG_CTRL_BYTES + XCHG_CFLAG_BYTES;
 struct XchgDev {
   double* inbox[XCHG_MAXW];               // rank r's inbox [2 parities][world][slot] (own rank: local pointer)
   unsigned long long* flags[XCHG_MAXW];   // rank r's flag words [2 parities][XCHG_MAXW]: epoch of the last arrival
+  unsigned long long* cflags[XCHG_MAXW];  // rank r's per-CTA flag words [2 parities][XCHG_MAXW][XCHG_MAXCTA] (fused tail)
   unsigned long long* epoch;              // local: exchanges completed
   unsigned int* counter;                  // local: send blocks finished (threadfence-reduction pattern)
   int* failed;                            // local: a wait timed out (a peer died)

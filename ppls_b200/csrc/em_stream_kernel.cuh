@@ -53,6 +53,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity), "r"(0x989680u) /* suspend-time hint (ns): sleep, don't spin */ : "memory");
   } while (!ok);
 }
+// Stage release vs. outstanding loads.  An mbarrier arrive that frees a TMA-filled stage must not be ISSUED while loads from
+// that stage are still outstanding: ptxas orders the arrive after the issue of the loads, not after their return (it was
+// seen ahead of the last DMMAs that consume them), and on B200 a refill of the stage was measured to overtake such loads
+// (em_wide3.cu: wrong 32-byte sectors in 1 of ~10^6 tiles).  A value that is 0 but only known once `x` is -- a population
+// count is at most 32 -- added to the barrier address keeps the arrive behind everything `x` depends on.
+// tools/sass_arrive_audit.py checks the compiled kernels for this.
+__device__ __forceinline__ uint32_t zero_once_known(uint32_t x) {
+  uint32_t z;
+  asm volatile("{\n\t.reg .b32 t;\n\tpopc.b32 t, %1;\n\tshr.u32 %0, t, 6;\n\t}" : "=r"(z) : "r"(x));
+  return z;
+}
+__device__ __forceinline__ uint32_t hi_bits(double v) { return (uint32_t)__double2hiint(v); }
+
 __device__ __forceinline__ void fence_proxy_async() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }

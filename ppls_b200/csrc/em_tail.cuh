@@ -4,8 +4,8 @@
 // launch there and running two more kernels (cross-CTA reduction / peer send, then the update K2), the CTAs -- all
 // co-resident: the grid is at most one CTA per SM and the launch is cooperative -- go on together:
 //   barrier | every row CTA sums ITS rows of G = [X'mu_T ; Y'mu_U] over the CTAs' partials in fixed order (CTA 0: the
-//   Gram tail Gxx, Gxy, Gyy) | multi-GPU: the sums go straight into every rank's inbox by peer stores, barrier, flags,
-//   wait for the world's flags, add the ranks in rank order | CTA 0: the scalar part of the update (log-likelihood,
+//   Gram tail Gxx, Gxy, Gyy) | multi-GPU: the sums go straight into every rank's inbox by peer stores; CTA b raises ITS flag
+//   on every rank and waits for CTA b of the peers (the same rows everywhere: no grid barrier), adds the ranks in rank order | CTA 0: the scalar part of the update (log-likelihood,
 //   E-step moments, break rule, M-step scalars: update_scalars of em_update_dev.cuh) while the row CTAs form the
 //   partial Gram of their rows | barrier | T = G (G'G)^{-1/2} on the rows held in shared memory, partial Gram of T |
 //   barrier | one Newton-Schulz step L = T (3I - T'T)/2 written to the loadings (Maximiz_M, EM_W_multi.R:732-733, type
@@ -30,7 +30,7 @@ struct TailArgs {
   XchgDev x;
 };
 
-__host__ __device__ inline size_t tail_scratch_doubles(int grid, int R) { return (size_t)2 * grid * 2 * R * R + 8; }
+__host__ __device__ inline size_t tail_scratch_doubles(int grid, int R) { return (size_t)2 * grid * 2 * R * R + 16; }
 __host__ __device__ inline size_t tail_clock_offset(int grid, int R) { return (size_t)2 * grid * 2 * R * R + 3; }   // doubles
 __host__ __device__ inline int tail_rows_per_cta(int ld, int grid) { return (ld + grid - 2) / (grid - 1); }
 // dynamic shared memory the tail needs (it reuses the streaming phase's carve-up from offset 0)
@@ -153,7 +153,7 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
   const bool xon = t.use_x != 0;
   const unsigned long long pass = (unsigned long long)st->pass;     // CTA 0 moves it only after barrier A
   const unsigned long long next = xon ? (*t.x.epoch + 1) : 0ull;    // ... and the epoch likewise
-  const unsigned long long NA = xon ? 2ull : 1ull;
+  const unsigned long long NA = 1ull;
 
   unsigned long long t1 = 0;
   tail_arrive_wait(cntA, (unsigned long long)G * (NA * pass + 1), false);     // A: every CTA's partial vector is in global memory
@@ -172,12 +172,13 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
     tail_sum8(nelem, G,
               [&](int e, int c) { return __ldcg(partials + (size_t)c * len + e0 + e); },
               [&](int e, double s, int y) { for (int r = y; r < t.x.world; r += 8) t.x.inbox[r][off + e] = s; });
-    tail_arrive_wait(cntA, (unsigned long long)G * (NA * pass + 2), true);    // A2: all CTAs' peer stores are ordered before the flags
-    if (b == 0 && tid < t.x.world) {
-      __threadfence_system();
-      st_relaxed_sys(t.x.flags[tid] + (next & 1ull) * XCHG_MAXW + t.x.rank, next);
+    // CTA b of every rank owns the SAME elements: it needs CTA b of the peers only -- per-CTA flags, no grid barrier.
+    __syncthreads();                                                // the whole CTA's peer stores are issued
+    if (tid < t.x.world) {
+      __threadfence_system();                                       // (cumulative over the bar.sync: orders them before the flag)
+      st_relaxed_sys(t.x.cflags[tid] + ((next & 1ull) * XCHG_MAXW + t.x.rank) * XCHG_MAXCTA + b, next);
     }
-    if (tid < 32) xchg_wait(t.x, next);                             // the world's vectors have landed here
+    if (tid < 32) xchg_wait_cta(t.x, next, b);                      // the peers' CTA b has delivered
     __syncthreads();
     for (int e = tid; e < nelem; e += nt) {                         // ranks added in rank order: same bits everywhere
       const double s = xchg_sum(t.x, next, e0 + e);
@@ -189,7 +190,7 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
   if (rb < 0) {
     // ================= CTA 0: the scalar part, off the row CTAs' path =================
     volatile int* s_done = reinterpret_cast<volatile int*>(ssh + 1);
-    if (tid < 32) {
+    if (tid < 64) {
       UpdateArgs ua;
       ua.momvec = t.momvec; ua.L = t.L; ua.Lscratch = nullptr; ua.st = st; ua.trace = t.trace; ua.gscratch = nullptr;
       ua.p = t.p; ua.q = t.q; ua.p2 = p2; ua.q2 = ld - p2; ua.ld = ld; ua.use_x = 0;
@@ -203,6 +204,7 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
         __threadfence();
         *reinterpret_cast<volatile unsigned long long*>(flagS) = 2ull * (pass + 1) + (d ? 1ull : 0ull);
         clk[4] += global_timer_ns() - t1;
+        clk[5] += ssh->ts[0] - t1; clk[6] += ssh->ts[1] - ssh->ts[0]; clk[7] += ssh->ts[2] - ssh->ts[1];   // own sums | staging | arithmetic
       }
     }
     __syncthreads();

@@ -176,7 +176,7 @@ __device__ void update_body(const UpdateArgs& a) {
   __shared__ ScalarShared ssh;
   FitState* st = a.st;
   if (st->done) return;
-  if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) { s_done = d; if (d) raise_done(st); } }
+  if (threadIdx.x < 64) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) { s_done = d; if (d) raise_done(st); } }
   __syncthreads();
   if (s_done) return;
   // ---- loadings: W = orth(t(X) mu_T), C = orth(t(Y) mu_U)  (:732-733) ----------------------------
@@ -386,7 +386,7 @@ __global__ void __launch_bounds__(GT) em_update_grid_kernel(const UpdateArgs a) 
   double* T = a.Lscratch;
   if (rb < 0) {
     __shared__ ScalarShared ssh;
-    if (threadIdx.x < 32) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) *done_now = d; }
+    if (threadIdx.x < 64) { const int d = update_scalars<R>(a, &ssh); if (threadIdx.x == 0) *done_now = d; }
   } else {
     grid_partial_gram<R>(G, 0, a.p2, rb, nb, ph0 + ((size_t)rb * 2 + 0) * R * R, scratch);
     grid_partial_gram<R>(G, a.p2, a.ld, rb, nb, ph0 + ((size_t)rb * 2 + 1) * R * R, scratch);

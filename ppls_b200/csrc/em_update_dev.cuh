@@ -226,6 +226,19 @@ __device__ inline void xchg_wait(const XchgDev& x, unsigned long long next) {
   __syncwarp();
   __threadfence_system();
 }
+// The same wait on per-CTA flags (fused tail): flag (parity, source rank r, CTA `cta`) of THIS rank's block.
+__device__ inline void xchg_wait_cta(const XchgDev& x, unsigned long long next, int cta) {
+  const int lane = threadIdx.x & 31;
+  const unsigned long long* fl = x.cflags[x.rank] + ((next & 1ull) * XCHG_MAXW) * XCHG_MAXCTA + cta;
+  const unsigned long long t0 = global_timer_ns();
+  if (lane < x.world) {
+    while (ld_relaxed_sys(fl + (size_t)lane * XCHG_MAXCTA) < next) {
+      if (global_timer_ns() - t0 > 20000000000ull) { atomicExch(x.failed, 1); break; }   // 20 s: a peer is gone
+    }
+  }
+  __syncwarp();
+  __threadfence_system();
+}
 // element e of the summed vector, ranks added in rank order (the same bits on every rank)
 __device__ inline double xchg_sum(const XchgDev& x, unsigned long long next, long long e) {
   const double* in = x.inbox[x.rank] + (size_t)(next & 1ull) * x.world * x.slot + e;
@@ -236,25 +249,36 @@ __device__ inline double xchg_sum(const XchgDev& x, unsigned long long next, lon
 
 __device__ inline bool finite_d(double x) { return isfinite(x); }
 
-// Scalar part, executed by ONE FULL WARP (lane k < R owns component k; every sum over components is
-// added by lane 0 in component order, as the sequential reference does): loglik(theta_k), E-step
-// moments, break rule, M-step scalars.  Returns 1 (on all lanes) when the run ends with this pass.
-struct ScalarShared { double c1[MAXR], c2[MAXR], c3[MAXR], tl[MAXR], lt[MAXR], lk[MAXR]; int done; };
+// Scalar part, executed by TWO FULL WARPS (threads 0..63 of the block; lane k < R owns component k; every sum over
+// components is added by lane 0 in component order, as the sequential reference does).  Warp 1: loglik(theta_k) (logl_W +
+// loglC_fast); warp 0, at the same time: the E-step moments; then warp 0: break rule and M-step scalars.  Returns 1 (on all
+// 64 threads) when the run ends with this pass.
+// The state is STAGED in shared memory for the whole scalar part: it is a chain of a few dozen dependent reads and writes
+// of FitState fields, and each one is an L2 round trip (~0.5-1 us) when done on the global copy.  The two warps copy the
+// struct in (all loads first, then the stores: one round trip), work on the copy, and copy it back before returning (nobody
+// else writes the struct meanwhile: row blocks only read `done`, which the CALLER raises after this function).
+// Measured at C2 (r = 3) inside the fused tail: own sums 2.9 us + staging 5.0 + arithmetic 12-13 with one warp on the global
+// struct's shared copy, word-by-word staging.
+struct ScalarShared {
+  double c1[MAXR], c2[MAXR], c3[MAXR], tl[MAXR], lt[MAXR], lk[MAXR], g3[3 * MAXR * MAXR];
+  double prev_ll;
+  int done, rc;
+  unsigned long long ts[4];
+  FitState stc;
+};
 
+__device__ __forceinline__ void scal_bar64() { asm volatile("bar.sync 2, 64;" ::: "memory"); }
+
+// warp 1: log-likelihood at theta_k: logl_W :312-320 + loglC_fast loglC.cpp:331-336
 template <int R>
-__device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
-  FitState* st = a.st;
-  const int lane = threadIdx.x & 31;
-  const double* Gxx = a.momvec + (size_t)a.ld * R;
+__device__ void scal_loglik(const UpdateArgs& a, ScalarShared* sh, FitState* st, const double* Gxx) {
+  const int lane = threadIdx.x & 31, k = lane;
   const double* Gxy = Gxx + R * R;
   const double* Gyy = Gxy + R * R;
   const double N = st->Ntot, p = (double)a.p, q = (double)a.q;
   const double sE = st->sigE, sF = st->sigF, sH = st->sigH;
-  const double sE2 = sE * sE, sF2 = sF * sF, sH2 = sH * sH;
+  const double sE2 = sE * sE, sF2 = sF * sF;
   const int k_pass = st->pass;
-  const int k = lane;
-
-  // ---- log-likelihood at theta_k: logl_W :312-320 + loglC_fast loglC.cpp:331-336 ----------
   if (k < R) {
     double c1, c2, c3, Kc;
     closed_form_coef(true, st->b[k], st->t[k], sE, sF, sH, &c1, &c2, &c3, &Kc);
@@ -262,18 +286,34 @@ __device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
     sh->lk[k] = log(sF2 + Kc);
     sh->tl[k] = -c1 * Gxx[k * R + k] - 2.0 * c2 * Gxy[k * R + k] - c3 * Gyy[k * R + k];
   }
+  // (the three logarithms of the constant terms on other lanes, meanwhile)
+  double lg = 0.0;
+  if (lane == 8) lg = log(sE2);
+  if (lane == 9) lg = log(sF2);
+  if (lane == 10) lg = log(2.0 * 3.14159265358979323846);
+  const double lgE = __shfl_sync(0xffffffffu, lg, 8), lgF = __shfl_sync(0xffffffffu, lg, 9), lg2pi = __shfl_sync(0xffffffffu, lg, 10);
   __syncwarp();
   if (lane == 0) {
     double sumT = 0.0, sumK = 0.0;
     double traceL = 1.0 / sE2 * st->ssqX + 1.0 / sF2 * st->ssqY;
     for (int j = 0; j < R; ++j) { sumT += sh->lt[j]; sumK += sh->lk[j]; traceL += sh->tl[j]; }
-    const double Logdiag = sumT + (p - R) * log(sE2) + sumK + (q - R) * log(sF2);
-    const double ll = -0.5 * N * (p + q) * log(2.0 * 3.14159265358979323846) - 0.5 * N * Logdiag - 0.5 * traceL;
+    const double Logdiag = sumT + (p - R) * lgE + sumK + (q - R) * lgF;
+    const double ll = -0.5 * N * (p + q) * lg2pi - 0.5 * N * Logdiag - 0.5 * traceL;
+    sh->prev_ll = st->loglik_last;                        // loglik(theta_{k-1}) = trace[k_pass - 2]: for the break rule
     st->loglik_last = ll;
     if (k_pass >= 1) a.trace[k_pass - 1] = ll;
   }
+}
 
-  // ---- E-step second moments at theta_k: Expect_M :672-712 ----------------------------------
+// warp 0: E-step second moments at theta_k: Expect_M :672-712
+template <int R>
+__device__ void scal_estep(const UpdateArgs& a, ScalarShared* sh, FitState* st, const double* Gxx) {
+  const int lane = threadIdx.x & 31, k = lane;
+  const double* Gxy = Gxx + R * R;
+  const double* Gyy = Gxy + R * R;
+  const double N = st->Ntot, p = (double)a.p, q = (double)a.q;
+  const double sE = st->sigE, sF = st->sigF, sH = st->sigH;
+  const double sE2 = sE * sE, sF2 = sF * sF, sH2 = sH * sH;
   const double isE2 = powm2(sE), isF2 = powm2(sF);
   const double sE4 = pow4(sE), sF4 = pow4(sF), sH4 = pow4(sH);
   if (k < R) {
@@ -332,20 +372,32 @@ __device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
         ssqF += MtMf * st->CtC[l * R + kk];
       }
     }
+    // The reference sums squares (ssq(mu_E), :706), which cannot be negative; the expanded form above can cancel to a
+    // tiny negative number when the residual is ~1e-16 of ||X||^2 (noise-free data).  Clamp instead of handing sqrt a
+    // negative argument: the run then goes on, as the reference's does.
+    if (ssqE < 0.0) ssqE = 0.0;
+    if (ssqF < 0.0) ssqF = 0.0;
     const double Cee = (p * sE2 - p * sE2 + sE4 * sumc1 + ssqE / N) / p;     // :706
     const double Cff = (q * sF2 - q * sF2 + sF4 * sumc3 + ssqF / N) / q;     // :709
     st->Cee = Cee; st->Cff = Cff;
-    // ---- break rule (:792) / EMsteps exhausted -------------------------------------------------
+  }
+  __syncwarp();
+}
+
+// warp 0, after both: break rule (:792) / EMsteps exhausted, then the M-step scalars (:734-738) -> theta_{k+1}
+template <int R>
+__device__ int scal_finish(ScalarShared* sh, FitState* st) {
+  const int lane = threadIdx.x & 31, k = lane;
+  const int k_pass = st->pass;
+  if (lane == 0) {
     bool done = (k_pass >= st->max_steps);
-    if (k_pass >= 2 && (a.trace[k_pass - 1] - a.trace[k_pass - 2]) < st->atol) done = true;
+    if (k_pass >= 2 && (st->loglik_last - sh->prev_ll) < st->atol) done = true;    // (the values of trace[k-1], trace[k-2])
     if (!finite_d(st->loglik_last)) { st->status = PPLS_E_NONFINITE; done = true; }
     if (done) st->steps_done = k_pass;                   // the CALLER raises st->done (see the grid kernel)
     sh->done = done ? 1 : 0;
   }
   __syncwarp();
   if (sh->done) return 1;
-
-  // ---- M-step scalars (:734-738) -> theta_{k+1} -----------------------------------------------
   bool ok = true;
   if (k < R) {
     const double bn = st->Cut[k] * (1.0 / st->Ctt[k]);       // Cut %*% solve(Ctt) * I
@@ -370,6 +422,41 @@ __device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
     if (!ok) { st->status = PPLS_E_NONFINITE; st->steps_done = k_pass; }
   }
   return ok ? 0 : 1;
+}
+
+// Threads 0..63 of the block call this (both warps whole).
+template <int R>
+__device__ int update_scalars(const UpdateArgs& a, ScalarShared* sh) {
+  static_assert(sizeof(FitState) % 8 == 0, "FitState is copied as 8-byte words");
+  const int tid = threadIdx.x, wrp = tid >> 5;
+  constexpr int NW = (int)(sizeof(FitState) / 8), NB = (NW + 63) / 64;
+  const unsigned long long* src = reinterpret_cast<const unsigned long long*>(a.st);
+  unsigned long long* cpy = reinterpret_cast<unsigned long long*>(&sh->stc);
+  if (tid == 0) sh->ts[0] = global_timer_ns();
+  {
+    unsigned long long v[NB];
+#pragma unroll
+    for (int j = 0; j < NB; ++j) { const int e = tid + 64 * j; v[j] = (e < NW) ? src[e] : 0ull; }
+    const double gv = (tid < 3 * R * R) ? a.momvec[(size_t)a.ld * R + tid] : 0.0;      // Gxx | Gxy | Gyy (3 R^2 <= 192: see below)
+#pragma unroll
+    for (int j = 0; j < NB; ++j) { const int e = tid + 64 * j; if (e < NW) cpy[e] = v[j]; }
+    if (tid < 3 * R * R) sh->g3[tid] = gv;
+    for (int e = tid + 64; e < 3 * R * R; e += 64) sh->g3[e] = a.momvec[(size_t)a.ld * R + e];
+  }
+  scal_bar64();
+  if (tid == 0) sh->ts[1] = global_timer_ns();
+  FitState* st = &sh->stc;
+  if (wrp == 1) scal_loglik<R>(a, sh, st, sh->g3);
+  else scal_estep<R>(a, sh, st, sh->g3);
+  scal_bar64();
+  if (wrp == 0) { const int rc = scal_finish<R>(sh, st); if (tid == 0) sh->rc = rc; }
+  scal_bar64();
+  if (tid == 0) sh->ts[2] = global_timer_ns();
+  unsigned long long* dst = reinterpret_cast<unsigned long long*>(a.st);
+  for (int e = tid; e < NW; e += 64) dst[e] = cpy[e];
+  const int rc = sh->rc;
+  scal_bar64();
+  return rc;
 }
 
 }  // namespace ppls

@@ -197,8 +197,20 @@ __global__ void __maxnreg__(NCH * R <= 10 ? 96 : 255) wide_kernel(const WideArgs
           }
         }
       }
+      // release the stage only once every load from it has returned (zero_once_known, em_stream_kernel.cuh)
+      uint32_t dep;
+      if (MODE == MODE_PROJECT) {
+        dep = zero_once_known(hi_bits(wv[0][0][0]));         // (the reduction above has consumed every load already)
+      } else {
+        uint32_t hx = 0;
+#pragma unroll
+        for (int j = 0; j < NCH; ++j) hx ^= hi_bits(wv[j][0][0]) ^ hi_bits(wv[j][1][0]);
+#pragma unroll
+        for (int k = 1; k < R; ++k) hx ^= hi_bits(wv[NCH - 1][0][k]);
+        dep = zero_once_known(hx);
+      }
       __syncwarp();
-      if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s));
+      if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s) + dep);
       if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
     }
     if (MODE == MODE_ACCUM) {
@@ -281,24 +293,32 @@ __global__ void __launch_bounds__(WMU_ROWS) wide_mu_kernel(const double* __restr
   }
 }
 
-// moment vector = [ G (sum over row groups) | Gxx | Gxy | Gyy (sum over wide_mu blocks) ]
+// moment vector = [ G (sum over row groups) | Gxx | Gxy | Gyy (sum over the Gram partials) ]
+// The first blocks sum G, one thread per element; the last ones sum the Gram partials, one warp per element (the single-pass
+// form leaves one partial per row: lanes stride over them with two chains each, then a fixed-order butterfly).
 __global__ void wide_finalize_kernel(const double* __restrict__ gpart, int nrg, int64_t glen,
                                      const double* __restrict__ gram_part, int nblk, int glen2,
-                                     double* __restrict__ momvec, const FitState* st) {
+                                     double* __restrict__ momvec, const FitState* st, int nb_g) {
   if (st->done) return;
-  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e < glen) {
-    double s = 0.0;
-    for (int g = 0; g < nrg; ++g) s += gpart[(size_t)g * glen + e];
-    momvec[e] = s;
-  } else if (e < glen + glen2) {
-    const int f = (int)(e - glen);
-    double s0 = 0.0, s1 = 0.0;
-    int b = 0;
-    for (; b + 1 < nblk; b += 2) { s0 += gram_part[(size_t)b * glen2 + f]; s1 += gram_part[(size_t)(b + 1) * glen2 + f]; }
-    if (b < nblk) s0 += gram_part[(size_t)b * glen2 + f];
-    momvec[e] = s0 + s1;
+  if ((int)blockIdx.x < nb_g) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < glen) {
+      double s = 0.0;
+      for (int g = 0; g < nrg; ++g) s += gpart[(size_t)g * glen + e];
+      momvec[e] = s;
+    }
+    return;
   }
+  const int f = ((int)blockIdx.x - nb_g) * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (f >= glen2) return;
+  double s0 = 0.0, s1 = 0.0;
+  int b = lane;
+  for (; b + 32 < nblk; b += 64) { s0 += gram_part[(size_t)b * glen2 + f]; s1 += gram_part[(size_t)(b + 32) * glen2 + f]; }
+  if (b < nblk) s0 += gram_part[(size_t)b * glen2 + f];
+  double s = s0 + s1;
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) momvec[glen + f] = s;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -397,7 +417,7 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
   w->nrg = (int)((s.n + w->rows_per_rg - 1) / w->rows_per_rg);
   { const char* ep = getenv("PPLS_WIDE_PERSIST"); w->slots = (ep && *ep && atoi(ep) == 0) ? 0 : slots; }   // 0: one CTA per work item
   w->nblk_mu = (int)((s.n + WMU_ROWS - 1) / WMU_ROWS);
-  w->v2 = 0; w->nstage2 = 0; w->sm_count = sm_count;
+  w->v2 = 0; w->nstage2 = 0; w->sm_count = sm_count; w->v3 = 0;
   {
     const char* ed = getenv("PPLS_WIDE_DMMA");
     if (s.panel && !(ed && *ed && atoi(ed) == 0)) plan_wide2(s, sm_count, w);      // tensor-pipe form of both passes
@@ -408,17 +428,34 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
   return cudaSuccess;
 }
 
+// Single-pass form: the pipelined kernel, then the same fixed-order sums as the two-pass form.
+cudaError_t launch_wide_single(const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st,
+                               double* ws, const WideOffsets& o, double* momvec, cudaStream_t stream) {
+  cudaError_t e = launch_wide3(w, s, D, L, st, ws + o.ppart, ws + o.mu, ws + o.mu8, ws + o.gpart, ws + o.gram, ws + o.cnt, stream);
+  if (e != cudaSuccess) return e;
+  const int64_t glen = (int64_t)s.ld * w.R; const int glen2 = 3 * w.R * w.R;
+  const int nb_g = (int)((glen + 255) / 256);
+  wide_finalize_kernel<<<(unsigned)(nb_g + (glen2 + 7) / 8), 256, 0, stream>>>(ws + o.gpart, w.nrg, glen, ws + o.gram, w.nblk_mu, glen2,
+                                                                          momvec, st, nb_g);
+  return cudaGetLastError();
+}
+
 int64_t wide_npad(int64_t n) { return (n + 63) / 64 * 64; }      // whole tiles of either form (16 / 64 rows)
 
 size_t wide_workspace_doubles(const DataShape& s, const WidePlan& w, WideOffsets* o) {
   size_t off = 0;
   auto take = [&off](size_t cnt) { size_t at = off; off += (cnt + 1) & ~(size_t)1; return at; };   // 16-byte aligned blocks
-  o->ppart = take((size_t)(w.nslabX + w.nslabY) * s.n * w.R);
+  {
+    size_t pp = (size_t)(w.nslabX + w.nslabY) * s.n * w.R;
+    if (w.v3) pp = wide3_ring_doubles(s, w);                       // single-pass form: only the chunks in flight
+    o->ppart = take(pp);
+  }
   o->proj = take((size_t)s.n * 2 * w.R);
   o->mu = take((size_t)2 * wide_npad(s.n) * w.R);
   o->gpart = take((size_t)w.nrg * s.ld * w.R);
   o->gram = take((size_t)w.nblk_mu * 3 * w.R * w.R);
-  o->mu8 = take(w.v2 ? (size_t)2 * wide_npad(s.n) * 8 : 0);      // DMMA form: mu with the components padded to 8
+  o->mu8 = take((w.v2 || w.v3) ? (size_t)2 * wide_npad(s.n) * 8 : 0);      // DMMA forms: mu with the components padded to 8
+  o->cnt = take(w.v3 ? wide3_counter_doubles(w) : 0);               // single-pass form: chunk arrival counters
   return off;
 }
 
@@ -459,8 +496,9 @@ cudaError_t launch_wide_accum(const WidePlan& w, const DataShape& s, const doubl
   } else
   wide_lookup(w.R, w.NCH, MODE_ACCUM)<<<grid, (WIDE_WARPS + 1) * 32, wide_smem(w.R, w.NCH, w.nstage, MODE_ACCUM, s.panel), stream>>>(a);
   const int64_t glen = (int64_t)s.ld * w.R; const int glen2 = 3 * w.R * w.R;
-  wide_finalize_kernel<<<(unsigned)((glen + glen2 + 255) / 256), 256, 0, stream>>>(ws + o.gpart, w.nrg, glen, ws + o.gram, w.nblk_mu,
-                                                                              glen2, momvec, st);
+  const int nb_g = (int)((glen + 255) / 256);
+  wide_finalize_kernel<<<(unsigned)(nb_g + (glen2 + 7) / 8), 256, 0, stream>>>(ws + o.gpart, w.nrg, glen, ws + o.gram, w.nblk_mu, glen2,
+                                                                          momvec, st, nb_g);
   return cudaGetLastError();
 }
 

@@ -125,8 +125,9 @@ __global__ void __launch_bounds__((W2_WARPS + 1) * 32, 1) wide2_kernel(const Wid
             dmma884(c0, c1, x0, wb[k]);
             dmma884(d0, d1, x1, wb[k + 1]);
           }
+          const uint32_t dep = zero_once_known(hi_bits(c0) ^ hi_bits(d0));        // every load of the tile has returned
           __syncwarp();
-          if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s));
+          if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s) + dep);
           if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
           // lane (g, t) holds components 2t, 2t + 1 of tile row 8 warp + g
           const int i = 8 * warp + g;
@@ -154,8 +155,9 @@ __global__ void __launch_bounds__((W2_WARPS + 1) * 32, 1) wide2_kernel(const Wid
             dmma884(d00, d01, x10, m1);
             dmma884(d10, d11, x11, m1);
           }
+          const uint32_t dep = zero_once_known(hi_bits(c00) ^ hi_bits(c10) ^ hi_bits(d00) ^ hi_bits(d10));   // (as above)
           __syncwarp();
-          if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s));
+          if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s) + dep);
           if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
         }
         // this item's rows of G for the panel's columns (pad columns of a last panel stay out)

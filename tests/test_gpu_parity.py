@@ -134,23 +134,28 @@ def test_error_behaviour(ctx):
 
 
 @pytest.mark.parametrize("name", ["c1_wellcond_1000", "r5_odd_shapes", "r3_qr", "r8_max", "r1_p_lt_q", "r3_wide_row"])
-@pytest.mark.parametrize("panel", ["0", "1"])
-def test_golden_through_the_wide_path(ctx, name, panel, monkeypatch):
-    """The two-pass wide-row path (em_wide.cu) forced on the golden cases, with row-major and with
-    panel-major storage: same bar as the fused kernel."""
+@pytest.mark.parametrize("panel,single", [("0", "0"), ("1", "0"), ("1", "1")])
+def test_golden_through_the_wide_path(ctx, name, panel, single, monkeypatch):
+    """The wide-row path forced on the golden cases: the two-pass form with row-major (em_wide.cu) and panel-major storage
+    (em_wide2.cu, FP64 tensor pipe), and the single-pass L2-pipelined form (em_wide3.cu): same bar as the fused kernel."""
     monkeypatch.setenv("PPLS_FORCE_WIDE", "1")
     monkeypatch.setenv("PPLS_PANEL", panel)
+    monkeypatch.setenv("PPLS_WIDE_SINGLE", single)
     g = load_golden(name)
     res = _run(ctx, g["X"], g["Y"], init_of(g), int(g["r"]), int(g["EMsteps"]), float(g["atol"]), str(g["type"]))
     _compare(res, g, name)
 
 
-@pytest.mark.parametrize("shape,steps", [((300, 6000, 500, 5), 6), ((1037, 9001, 33, 3), 4), ((2000, 50000, 1000, 5), 3)])
-def test_wide_shapes_vs_fused_oracle(ctx, oracle_lib, shape, steps):
+@pytest.mark.parametrize("single", ["1", "0"])
+@pytest.mark.parametrize("shape,steps", [((300, 6000, 500, 5), 6), ((1037, 9001, 33, 3), 4), ((2000, 50000, 1000, 5), 3),
+                                         ((5000, 2500, 40, 2), 4), ((129, 80000, 300, 8), 3)])
+def test_wide_shapes_vs_fused_oracle(ctx, oracle_lib, shape, steps, single, monkeypatch):
     """Rows too wide for the fused kernel's tile (incl. BASELINE config 4 at full size: N=2000, p=50000,
-    q=1000, r=5) take the wide path by themselves; compared with the CPU restatement on the exported data."""
+    q=1000, r=5) take the wide path by themselves -- single-pass form (several row lanes when there are fewer panels than
+    SMs, up to 5 panels per CTA, ragged last chunk) and two-pass form; compared with the CPU restatement on the exported data."""
     from oracle import ppls_fused as F
     from ppls_b200 import Data, Fit, synth
+    monkeypatch.setenv("PPLS_WIDE_SINGLE", single)
     N, p, q, r = shape
     truth = synth.truth_params(p, q, r, 0.5, 0.5, 0.3)
     d = Data.synthetic(ctx, N, p, q, truth, seed=777)
