@@ -14,6 +14,66 @@
 #include <vector>
 #include <thread>
 #include <new>
+#include <mutex>
+#include <unordered_map>
+
+// ---- guarded device allocations (PPLS_GUARD=1) ---------------------------------------------------------------------
+// compute-sanitizer is not available on every pool.  With PPLS_GUARD=1 every device allocation of this file carries 4 KB
+// of 0xA5 bytes on either side; when it is freed the guards are read back and any changed byte aborts the process with
+// the size of the allocation and the offset of the damage.  Catches writes past (or before) every workspace, ring and
+// exchange buffer the engine owns; tests/test_gpu_guard.py runs every kernel family under it.  Off by default (no cost).
+namespace {
+constexpr size_t GUARD_BYTES = 4096;
+struct GuardRec { unsigned char* base; size_t bytes, padded; };
+std::mutex g_guard_mu;
+std::unordered_map<void*, GuardRec> g_guard;
+bool guard_on() {
+  static const int on = [] { const char* e = getenv("PPLS_GUARD"); return (e && atoi(e)) ? 1 : 0; }();
+  return on != 0;
+}
+cudaError_t guard_malloc(void** p, size_t bytes) {
+  if (!guard_on()) return cudaMalloc(p, bytes);
+  const size_t padded = (bytes + 255) / 256 * 256;
+  unsigned char* base = nullptr;
+  cudaError_t e = cudaMalloc(&base, padded + 2 * GUARD_BYTES);
+  if (e != cudaSuccess) return e;
+  e = cudaMemset(base, 0xA5, GUARD_BYTES);
+  if (e == cudaSuccess) e = cudaMemset(base + GUARD_BYTES + bytes, 0xA5, padded - bytes + GUARD_BYTES);
+  if (e != cudaSuccess) { cudaFree(base); return e; }
+  *p = base + GUARD_BYTES;
+  {  // PPLS_GUARD_SELFTEST=1: damage the guard on purpose (the test of the detector itself)
+    static const int selftest = [] { const char* e = getenv("PPLS_GUARD_SELFTEST"); return (e && atoi(e)) ? 1 : 0; }();
+    if (selftest) cudaMemset(base + GUARD_BYTES + bytes + 3, 0, 1);
+  }
+  std::lock_guard<std::mutex> lk(g_guard_mu);
+  g_guard[*p] = GuardRec{base, bytes, padded};
+  return cudaSuccess;
+}
+cudaError_t guard_free(void* p) {
+  if (!guard_on() || !p) return cudaFree(p);
+  GuardRec r{};
+  {
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    auto it = g_guard.find(p);
+    if (it == g_guard.end()) return cudaFree(p);
+    r = it->second;
+    g_guard.erase(it);
+  }
+  cudaDeviceSynchronize();
+  const size_t tail = r.padded - r.bytes + GUARD_BYTES;
+  std::vector<unsigned char> lo(GUARD_BYTES), hi(tail);
+  cudaMemcpy(lo.data(), r.base, GUARD_BYTES, cudaMemcpyDeviceToHost);
+  cudaMemcpy(hi.data(), r.base + GUARD_BYTES + r.bytes, tail, cudaMemcpyDeviceToHost);
+  for (size_t i = 0; i < GUARD_BYTES; ++i)
+    if (lo[i] != 0xA5) { fprintf(stderr, "[ppls] PPLS_GUARD: write %zu bytes BEFORE an allocation of %zu bytes\n", GUARD_BYTES - i, r.bytes); abort(); }
+  for (size_t i = 0; i < tail; ++i)
+    if (hi[i] != 0xA5) { fprintf(stderr, "[ppls] PPLS_GUARD: write %zu bytes PAST the end of an allocation of %zu bytes\n", i, r.bytes); abort(); }
+  return cudaFree(r.base);
+}
+template <typename T> cudaError_t guard_malloc_t(T** p, size_t bytes) { return guard_malloc(reinterpret_cast<void**>(p), bytes); }
+}  // namespace
+#define cudaMalloc(p, n) guard_malloc_t((p), (n))
+#define cudaFree(p) guard_free((void*)(p))
 
 using namespace ppls;
 

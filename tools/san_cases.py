@@ -1,7 +1,7 @@
 """Small cases of every kernel family for compute-sanitizer (one --tool per gpurun call):
     compute-sanitizer --tool memcheck|racecheck|synccheck python tools/san_cases.py [--multi]
 C1 golden (fused one-launch path, 40 steps), QR type (update kernel K2), the wide-row path on both storage layouts
-(DFMA and DMMA forms), the batched paths (K1 packs and the two-GEMM form), sequential + meta fits, variances, orth,
+(DFMA and DMMA two-pass forms, single-pass form), the batched paths (K1 packs and the two-GEMM form), sequential + meta fits, variances, orth,
 the no-alloc orth; --multi: the row-sharded fit on a 2-device single-process context (peer exchange)."""
 import os, sys
 import numpy as np
@@ -67,12 +67,19 @@ def main():
     d.close()
     w = load_golden("r3_wide_row")
     os.environ["PPLS_FORCE_WIDE"] = "1"
-    for panel, dmma in (("0", "1"), ("1", "0"), ("1", "1")):
-        os.environ["PPLS_PANEL"] = panel; os.environ["PPLS_WIDE_DMMA"] = dmma
+    for panel, dmma, single in (("0", "1", "0"), ("1", "0", "0"), ("1", "1", "0"), ("1", "1", "1")):
+        os.environ["PPLS_PANEL"] = panel; os.environ["PPLS_WIDE_DMMA"] = dmma; os.environ["PPLS_WIDE_SINGLE"] = single
         res = fit(ctx, w["X"], w["Y"], init_of(w), 3, 6)
-        print("wide panel=" + panel + " dmma=" + dmma, abs(res["loglik"][-1] / w["loglik"][5] - 1), flush=True)
-    for k in ("PPLS_FORCE_WIDE", "PPLS_PANEL", "PPLS_WIDE_DMMA"):
+        print("wide panel=" + panel + " dmma=" + dmma + " single=" + single, abs(res["loglik"][-1] / w["loglik"][5] - 1), flush=True)
+    for k in ("PPLS_FORCE_WIDE", "PPLS_PANEL", "PPLS_WIDE_DMMA", "PPLS_WIDE_SINGLE"):
         os.environ.pop(k)
+    # the single-pass wide kernel with several panels per CTA and several row lanes
+    for shape in ((300, 40000, 500, 5), (700, 6000, 500, 3)):
+        N2, p2, q2, r2 = shape
+        tr2 = synth.truth_params(p2, q2, r2, 0.5, 0.5, 0.3)
+        d2 = Data.synthetic(ctx, N2, p2, q2, tr2, seed=9)
+        f = Fit(d2, synth.start_params(tr2, 3), r2, 3, -np.inf, "SVD"); f.run()
+        print("wide single-pass", shape, f.result(False)["loglik"][-1], flush=True); f.close(); d2.close()
     rng = np.random.default_rng(0)
     G = rng.standard_normal((1500, 4))
     for typ in ("SVD", "QR"):
