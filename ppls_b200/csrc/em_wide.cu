@@ -431,10 +431,12 @@ cudaError_t plan_wide(const DataShape& s, int R, int sm_count, WidePlan* w, cons
 // Single-pass form: the pipelined kernel, then the same fixed-order sums as the two-pass form.
 cudaError_t launch_wide_single(const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st,
                                double* ws, const WideOffsets& o, double* momvec, cudaStream_t stream) {
-  cudaError_t e = launch_wide3(w, s, D, L, st, ws + o.ppart, ws + o.mu, ws + o.mu8, ws + o.gpart, ws + o.gram, ws + o.cnt, stream);
+  // one row lane: the kernel's G is final, it goes straight into the moment vector and only the Gram partials are summed
+  const bool direct = w.nrg == 1;
+  cudaError_t e = launch_wide3(w, s, D, L, st, ws + o.ppart, ws + o.mu, ws + o.mu8, direct ? momvec : ws + o.gpart, ws + o.gram, ws + o.cnt, stream);
   if (e != cudaSuccess) return e;
   const int64_t glen = (int64_t)s.ld * w.R; const int glen2 = 3 * w.R * w.R;
-  const int nb_g = (int)((glen + 255) / 256);
+  const int nb_g = direct ? 0 : (int)((glen + 255) / 256);
   wide_finalize_kernel<<<(unsigned)(nb_g + (glen2 + 7) / 8), 256, 0, stream>>>(ws + o.gpart, w.nrg, glen, ws + o.gram, w.nblk_mu, glen2,
                                                                           momvec, st, nb_g);
   return cudaGetLastError();

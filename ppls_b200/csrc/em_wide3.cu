@@ -14,8 +14,9 @@
 //                  fence this takes would stall the tensor pipe if a compute warp executed it)
 //   reducer warps  the CTA's share of the 32 one-row duties of every chunk: wait until every CTA's projections are in, sum
 //                  them in fixed order, form mu_T, mu_U and the Gram partial of the row, count the duty
-//   producer warp  bulk copies into the ring; the first read of a tile asks the L2 to keep it (evict_last), the second is
-//                  its last (evict_first); waits for the chunk's 32 duties before it issues the A tiles
+//   producer warp  bulk copies into the ring, as far ahead as the ring allows; the first read of a tile asks the L2 to keep
+//                  it (evict_last), the second is its last (evict_first)
+//   mu warp        waits for the chunk's 32 duties and stages its mu_T / mu_U tile in shared memory for the compute warps
 // Nothing stops: the waits are on per-chunk arrival counters that only grow (targets derived from the fit's pass number),
 // the compute warps never wait on another CTA directly, only on their own ring.  HBM traffic per EM iteration is ONE read of
 // the data (algorithmic bytes 8 n (p+q), half of the two-pass form; measured 884 MB at C4 against 816 MB); the second read
@@ -32,11 +33,12 @@ constexpr int W3_TR = 32;                        // rows per tile = rows per chu
 constexpr int W3_WARPS = 8;                      // compute warps
 constexpr uint32_t W3_PITCH = PANEL_PITCH * 8;   // shared-memory row pitch (bytes) = stored pitch (conflict-free fragments)
 constexpr uint32_t W3_MU_BYTES = W3_TR * 8 * 8;  // mu tile: [32 rows][8 components]
-constexpr uint32_t W3_STAGE = W3_TR * W3_PITCH + W3_MU_BYTES;
+constexpr uint32_t W3_STAGE = W3_TR * W3_PITCH;  // one tile: 32 rows of one panel
+constexpr int W3_MUSLOTS = 2;                    // chunks of mu staged ahead in shared memory ([mu_T tile | mu_U tile] each)
 constexpr int W3_WPITCH = PANEL_W + 4;           // loadings in shared memory: [8 components][132] per slot
 constexpr int W3_NRED = 32;                      // reducer duties per chunk (1 row each: 8 components x 16 sub-lanes)
 constexpr int W3_RWARPS = 4;                     // reducer warps per CTA (their own instruction stream: duties never stall the tensor pipe)
-constexpr int W3_THREADS = (W3_WARPS + 2 + W3_RWARPS) * 32;
+constexpr int W3_THREADS = (W3_WARPS + 3 + W3_RWARPS) * 32;   // compute | producer, signal, mu | reducers
 constexpr int W3_MAXSLOT = 6;
 
 struct Wide3Args {
@@ -74,15 +76,16 @@ __device__ __forceinline__ void w3_wait(const unsigned long long* c, unsigned lo
   } while (v < target);
 }
 
-struct Wide3Smem { uint32_t ring, ws, comb, xy, bars, total; };
+struct Wide3Smem { uint32_t ring, ws, mu, comb, xy, bars, total; };
 __host__ __device__ inline Wide3Smem wide3_smem(int NS, int nstage) {
   Wide3Smem s;
   uint32_t o = 0;
   s.ring = o; o += (uint32_t)nstage * W3_STAGE;
   s.ws = o;   o += (uint32_t)NS * 8u * W3_WPITCH * 8u;
+  s.mu = o;   o += (uint32_t)W3_MUSLOTS * 2u * W3_MU_BYTES;
   s.comb = o; o += 64u;                                  // 16 counters (chunk % 16) of warps that have stored a chunk's projections
   s.xy = o;   o += 64u * 8u;                             // reducer scratch: Xw, Yc of 2 rows (+ coefficients)
-  s.bars = o; o += 2u * (uint32_t)nstage * 8u;
+  s.bars = o; o += (2u * (uint32_t)nstage + 2u * W3_MUSLOTS) * 8u;     // ring full/empty, mu full/empty
   s.total = o;
   return s;
 }
@@ -107,6 +110,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
   const Wide3Smem lay = wide3_smem(NS, a.nstage);
   const uint32_t sbase = smem_u32(smem);
   const uint32_t bars = sbase + lay.bars;
+  const uint32_t mubars = bars + 16u * (uint32_t)a.nstage;          // mu full[W3_MUSLOTS], mu empty[W3_MUSLOTS]
   double* Ws = reinterpret_cast<double*>(smem + lay.ws);
   unsigned int* sig = reinterpret_cast<unsigned int*>(smem + lay.comb);
   double* xy = reinterpret_cast<double*>(smem + lay.xy);
@@ -127,7 +131,8 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
   }
   if (tid < 16) sig[tid] = 0u;
   if (tid == 0) {
-    for (int s = 0; s < a.nstage; ++s) { mbar_init(bars + 8u * s, 2); mbar_init(bars + 8u * (a.nstage + s), W3_WARPS); }
+    for (int s = 0; s < a.nstage; ++s) { mbar_init(bars + 8u * s, 1); mbar_init(bars + 8u * (a.nstage + s), W3_WARPS); }
+    for (int s = 0; s < W3_MUSLOTS; ++s) { mbar_init(mubars + 8u * s, 1); mbar_init(mubars + 8u * (W3_MUSLOTS + s), W3_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   fence_proxy_async();
@@ -135,66 +140,70 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
 
   const int nit = nch + a.lag;
   if (warp == W3_WARPS) {
-    // ------------------------------------ producer (one warp; lane 0 issues the copies) -----------------------------
-    if (ns > 0) {
+    // ------------------------------------ producer (one lane) -------------------------------------------------------
+    // Only ever waits for a free stage: the tiles of both phases are issued as far ahead as the ring allows (the chunk's
+    // mu reaches the compute warps through the mu warp, not through the ring).
+    if (lane == 0 && ns > 0) {
       uint32_t s = 0, par = 1;
       int64_t gt = 0;
-      const bool mu_generic = (a.hint & 2) != 0;
       // L2 policy: the first read of a tile should stay in the L2 until its second read LAG chunks later, which is its last
       unsigned long long pol_keep, pol_last;
       asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_keep));
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_last));
-      double mregT[8], mregU[8];                                 // the chunk's mu_T / mu_U tile, 8 values per lane (generic form)
-      auto issue = [&](int panel, int chunk, bool with_mu) {
+      auto issue = [&](int panel, int chunk, bool second) {
         const int64_t row0 = (int64_t)chunk * W3_TR;
         const int rows = (int)((a.n - row0 < W3_TR) ? (a.n - row0) : W3_TR);
         const uint32_t full = bars + 8u * s, dst = sbase + lay.ring + s * W3_STAGE;
-        const bool mu_tma = with_mu && !mu_generic;
-        if (lane == 0) {
-          if (gt >= a.nstage) mbar_wait(bars + 8u * (a.nstage + s), par);
-          mbar_expect_tx(full, (uint32_t)rows * W3_PITCH + (mu_tma ? W3_MU_BYTES : 0u));
-          if (a.hint & 1)
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
-                         ::"r"(dst), "l"(a.D + ((size_t)panel * a.n + row0) * PANEL_PITCH), "r"((uint32_t)rows * W3_PITCH), "r"(full),
-                           "l"(with_mu ? pol_last : pol_keep) : "memory");
-          else
-            bulk_g2s(dst, a.D + ((size_t)panel * a.n + row0) * PANEL_PITCH, (uint32_t)rows * W3_PITCH, full);
-          if (mu_tma)
-            bulk_g2s(dst + W3_TR * W3_PITCH, a.mu8 + ((panel >= a.npX ? (size_t)a.npad : 0) + (size_t)row0) * 8, W3_MU_BYTES, full);
-        }
-        __syncwarp();
-        if (with_mu && mu_generic) {
-          const int hsel = panel >= a.npX ? 1 : 0;
-          double* md = reinterpret_cast<double*>(smem + lay.ring + s * W3_STAGE + W3_TR * W3_PITCH);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) md[lane + 32 * j] = hsel ? mregU[j] : mregT[j];
-        }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(full);                  // second arrival: the generic stores above are in (release)
+        if (gt >= a.nstage) mbar_wait(bars + 8u * (a.nstage + s), par);
+        mbar_expect_tx(full, (uint32_t)rows * W3_PITCH);
+        if (a.hint & 1)
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                       ::"r"(dst), "l"(a.D + ((size_t)panel * a.n + row0) * PANEL_PITCH), "r"((uint32_t)rows * W3_PITCH), "r"(full),
+                         "l"(second ? pol_last : pol_keep) : "memory");
+        else
+          bulk_g2s(dst, a.D + ((size_t)panel * a.n + row0) * PANEL_PITCH, (uint32_t)rows * W3_PITCH, full);
         ++gt;
         if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
       };
-      const bool own_y = pos + (ns - 1) * a.ctas_per_lane >= a.npX;
       for (int w = 0; w < nit; ++w) {
         if (w < nch)
           for (int sl = 0; sl < ns; ++sl) issue(pos + sl * a.ctas_per_lane, c_lo + w, false);
-        if (w >= a.lag) {
-          const int chunk = c_lo + w - a.lag;
-          if (lane == 0) w3_wait(cntR + chunk, targetR);                    // the chunk's mu_T, mu_U are complete
-          __syncwarp();
-          if (mu_generic) {
-            const double* m0 = a.mu8 + (size_t)chunk * W3_TR * 8;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) mregT[j] = __ldcg(m0 + lane + 32 * j);
-            if (own_y) {
-#pragma unroll
-              for (int j = 0; j < 8; ++j) mregU[j] = __ldcg(m0 + (size_t)a.npad * 8 + lane + 32 * j);
-            }
-          } else {
-            asm volatile("fence.proxy.async;" ::: "memory");                // written by generic stores, read by the bulk copy
-          }
-          for (int sl = 0; sl < ns; ++sl) issue(pos + sl * a.ctas_per_lane, chunk, true);
+        if (w >= a.lag)
+          for (int sl = 0; sl < ns; ++sl) issue(pos + sl * a.ctas_per_lane, c_lo + w - a.lag, true);
+      }
+    }
+    return;
+  }
+  if (warp == W3_WARPS + 2) {
+    // ------------------------------------ mu warp --------------------------------------------------------------------
+    // Stages the mu_T (and, for a CTA with a Y panel, mu_U) tile of chunk c in shared memory as soon as the chunk's 32
+    // duties are counted: generic loads (written by other SMs' generic stores: no proxy crossing), W3_MUSLOTS chunks ahead.
+    if (ns > 0) {
+      const bool own_y = pos + (ns - 1) * a.ctas_per_lane >= a.npX;
+      for (int c = 0; c < nch; ++c) {
+        const int slot = c % W3_MUSLOTS;
+        if (lane == 0) {
+          if (c >= W3_MUSLOTS) mbar_wait(mubars + 8u * (W3_MUSLOTS + slot), (uint32_t)((c / W3_MUSLOTS - 1) & 1));
+          w3_wait(cntR + c_lo + c, targetR);                                // the chunk's mu_T, mu_U are complete
         }
+        __syncwarp();
+        const double* m0 = a.mu8 + (size_t)(c_lo + c) * W3_TR * 8;
+        double* md = reinterpret_cast<double*>(smem + lay.mu + (uint32_t)slot * 2u * W3_MU_BYTES);
+        double vt[8], vu[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) vt[j] = __ldcg(m0 + lane + 32 * j);
+        if (own_y) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) vu[j] = __ldcg(m0 + (size_t)a.npad * 8 + lane + 32 * j);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) md[lane + 32 * j] = vt[j];
+        if (own_y) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) md[256 + lane + 32 * j] = vu[j];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(mubars + 8u * slot);                     // (release: the stores above are in)
       }
     }
     return;
@@ -217,10 +226,10 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
     return;
   }
 
-  if (warp >= W3_WARPS + 2) {
+  if (warp >= W3_WARPS + 3) {
     // ------------------------------------ reducer warps ------------------------------------------------------------
     // One row per duty: component k = 16-lane half, 16 sub-lanes per component sum the CTAs' partials in a fixed order.
-    const int tr = tid - (W3_WARPS + 2) * 32;            // 0 .. 127
+    const int tr = tid - (W3_WARPS + 3) * 32;            // 0 .. 127
     const int k = tr >> 4, y = tr & 15;
     const bool act = k < R;
     const int ring_slots = a.lag + 1;
@@ -273,10 +282,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
         a.mu8[(size_t)row * 8 + k] = mt;
         a.mu8[(size_t)(a.npad + row) * 8 + k] = mw;
         xy[k] = xw; xy[16 + k] = yc;
-        // mu8 is read by bulk copies (async proxy) of other CTAs as soon as the chunk's counter is complete: the writer
-        // itself orders its stores ahead of both proxies before the count goes up
-        asm volatile("fence.proxy.async.global;" ::: "memory");
-        __threadfence();
+        __threadfence();                                   // the writer itself publishes its stores before the count goes up
       }
       w3_bar_red();
       for (int e = tr; e < 3 * R * R; e += W3_RWARPS * 32) {
@@ -347,14 +353,18 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
       }
     }
     // ---- A(w - lag): accumulate G from the same tiles (L2) with the chunk's mu ---------------------------------
-    if (w >= a.lag) {
+    if (w >= a.lag && ns > 0) {
+      const int c = w - a.lag, mslot = c % W3_MUSLOTS;
+      mbar_wait(mubars + 8u * mslot, (uint32_t)((c / W3_MUSLOTS) & 1));          // the mu warp has staged the chunk's mu
+      const uint32_t mbase = sbase + lay.mu + (uint32_t)mslot * 2u * W3_MU_BYTES + (uint32_t)(t * 8 + g) * 8u;
+      uint32_t dep = 0;
 #pragma unroll
       for (int sl = 0; sl < NS; ++sl) {
         if (sl < ns) {
           mbar_wait(bars + 8u * s, par);
           const uint32_t tile = sbase + lay.ring + s * W3_STAGE;
           const uint32_t xa = tile + (uint32_t)t * W3_PITCH + (uint32_t)(16 * warp + g) * 8u;
-          const uint32_t ma = tile + W3_TR * W3_PITCH + (uint32_t)(t * 8 + g) * 8u;
+          const uint32_t ma = mbase + ((pos + sl * a.ctas_per_lane >= a.npX) ? W3_MU_BYTES : 0u);   // a Y panel takes mu_U
 #pragma unroll
           for (int k = 0; k < 8; k += 2) {
             const double m0 = w3_lds(ma + k * 256), m1 = w3_lds(ma + (k + 1) * 256);
@@ -367,12 +377,13 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
           }
           // release the stage only once every load of the tile has returned (zero_once_known, em_stream_kernel.cuh): the
           // results of the last four DMMAs depend on the last loads
-          const uint32_t dep = zero_once_known(hi_bits(acc[sl][0]) ^ hi_bits(acc[sl][2]) ^ hi_bits(acc[sl][4]) ^ hi_bits(acc[sl][6]));
+          dep = zero_once_known(hi_bits(acc[sl][0]) ^ hi_bits(acc[sl][2]) ^ hi_bits(acc[sl][4]) ^ hi_bits(acc[sl][6]));
           __syncwarp();
           if (lane == 0) mbar_arrive(bars + 8u * (a.nstage + s) + dep);
           if (++s == (uint32_t)a.nstage) { s = 0; par ^= 1u; }
         }
       }
+      if (lane == 0) mbar_arrive(mubars + 8u * (W3_MUSLOTS + mslot) + dep);      // ... and the chunk's mu slot (same dependency)
     }
   }
   // ---- this lane's rows of G for my panels' columns --------------------------------------------------------------
@@ -452,7 +463,7 @@ cudaError_t launch_wide3(const WidePlan& w, const DataShape& s, const double* D,
   a.cnt = reinterpret_cast<unsigned long long*>(counters);
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.npX = s.npX; a.npanel = s.npX + s.npY; a.R = w.R;
   a.nstage = w.v3_nstage; a.lag = w.v3_lag; a.lanes = w.v3_lanes; a.ctas_per_lane = w.v3_cpl;
-  a.chunks_per_lane = w.v3_chunks_per_lane; a.nchunk = w.v3_nchunk; a.hint = w3_env("PPLS_WIDE_HINT", 3);   // bit 0: L2 eviction policies, bit 1: mu by generic loads of the producer warp
+  a.chunks_per_lane = w.v3_chunks_per_lane; a.nchunk = w.v3_nchunk; a.hint = w3_env("PPLS_WIDE_HINT", 1);   // bit 0: L2 eviction policies
   int NS = 0;
   wide3_kernel_t k = wide3_lookup(w.v3_ns, &NS);
   if (!k) return cudaErrorInvalidValue;
