@@ -273,7 +273,10 @@ int ppls_variances(ppls_ctx* ctx, const ppls_data* d, int32_t which, int32_t r, 
  * shared by all populations, B_T / sigX / sigY / sigH / sigT per population.  Populations are contiguous row blocks
  * of pop_rows[j] rows in row order.  guess: one-component start state used for every population.  Outputs: W[p],
  * C[q], params n_pop x 5 column-major (B_T, sigX, sigY, sigH, sigT), logvalues steps x n_pop ROW-major (the
- * reference's `log`, rows 2..steps+1 of logvalue; room for EMsteps rows; may be NULL), steps. */
+ * reference's `log`, rows 2..steps+1 of logvalue; room for EMsteps rows; may be NULL), steps.
+ * Row-sharded contexts (ppls_ctx_create_dist): pop_rows[j] is THIS rank's number of rows of population j (same
+ * populations in the same order on every rank, 0 where a rank holds none); the pooled sums of :481-482 are one
+ * allreduce per pass and every rank returns the same results. */
 int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, const int64_t* pop_rows, int32_t EMsteps,
                   double atol, const ppls_params* guess, double* W, double* C, double* params, double* logvalues,
                   int32_t* steps);

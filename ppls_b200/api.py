@@ -644,17 +644,24 @@ def simulC(N, W, C_, P_Yosc, P_Xosc, B_T, sigX, sigY, sigH, sigT, sigTo, sigUo, 
 
 
 def meta_PPLSi(X, Y, Ipopu, EMsteps=100, atol=1e-4, initialGuess="equal", customGuess=None,
-               ctx: Optional[Context] = None, data: Optional[Data] = None):
+               ctx: Optional[Context] = None, data: Optional[Data] = None, pop_rows=None):
     """Multi-population one-component fit -- mirror of meta_PPLSi (Package/PPLS/R/EM_W_multi.R:509-589) on the GPU
     (ppls_meta_run).  Ipopu: population label per row; rows must be grouped by population in the order of the sorted
     labels (the reference slices contiguous blocks by table(Ipopu), :455-456,:551-554).  critfunc = identity, no
-    constraints.  Returns {'W', 'C', 'params': [{'B_T','sigX','sigY','sigH','sigT'}, ...], 'log': steps x n_pop}."""
+    constraints.  Returns {'W', 'C', 'params': [{'B_T','sigX','sigY','sigH','sigT'}, ...], 'log': steps x n_pop}.
+    Row-sharded over several ranks (one process per GPU): every rank passes ITS rows and `pop_rows`, the number of its
+    rows in each population (same populations in the same order on all ranks, 0 where a rank holds none); the pooled
+    sums of :481-482 then run over all ranks (one allreduce per pass)."""
     if isinstance(initialGuess, (tuple, list)):
         initialGuess = initialGuess[0]
-    lab = np.asarray(Ipopu)
-    levels, counts = np.unique(lab, return_counts=True)
-    if not np.array_equal(lab, np.repeat(levels, counts)):
-        raise ValueError("rows must be sorted by population (contiguous blocks in the order of the sorted labels)")
+    if pop_rows is not None:
+        counts = np.asarray(pop_rows, dtype=np.int64)
+        lab = np.repeat(np.arange(len(counts)), counts)
+    else:
+        lab = np.asarray(Ipopu)
+        levels, counts = np.unique(lab, return_counts=True)
+        if not np.array_equal(lab, np.repeat(levels, counts)):
+            raise ValueError("rows must be sorted by population (contiguous blocks in the order of the sorted labels)")
     ctx = ctx or (data.ctx if data is not None else default_context())
     own = data is None
     if data is None:

@@ -1815,7 +1815,8 @@ extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, c
   if (rc) return rc;
   if (!d || !pop_rows || !guess || !W || !Cout || !params || !steps) return fail(PPLS_E_INVALID, "null argument");
   if (d->ctx != ctx) return fail(PPLS_E_INVALID, "data belongs to another context");
-  if (ctx->world != 1 || d->colshard) return fail(PPLS_E_UNSUPPORTED, "meta fit: one GPU, row-major data");
+  if (d->colshard) return fail(PPLS_E_UNSUPPORTED, "meta fit: row-sharded data only");
+  const bool multi = ctx->world > 1;          // row-sharded: pop_rows are this rank's LOCAL rows of each population (0 allowed)
   if (d->s.panel) return fail(PPLS_E_UNSUPPORTED, "meta fit: wide-row (panel-major) data is not supported");
   if (n_pop < 1 || n_pop > 64) return fail(PPLS_E_INVALID, "number of populations outside 1..64");
   if (EMsteps < 1) return fail(PPLS_E_INVALID, "EMsteps must be a strictly positive integer");
@@ -1824,7 +1825,10 @@ extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, c
   const DataShape& sh = d->s;
   const int J = n_pop;
   int64_t tot = 0;
-  for (int j = 0; j < J; ++j) { if (pop_rows[j] < 1) return fail(PPLS_E_INVALID, "empty population"); tot += pop_rows[j]; }
+  for (int j = 0; j < J; ++j) {
+    if (pop_rows[j] < (multi ? 0 : 1)) return fail(PPLS_E_INVALID, "empty population");
+    tot += pop_rows[j];
+  }
   if (tot != sh.n) return fail(PPLS_E_INVALID, "nrow(X) == length(Ipopu) is required");
   const int64_t veclen = momvec_len(sh.ld, 1);
   struct PopPlan { DataShape s; StreamPlan plan; const double* D; };
@@ -1834,6 +1838,7 @@ extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, c
   for (int j = 0; j < J; ++j) {
     pops[j].s = sh; pops[j].s.n = pop_rows[j];
     pops[j].D = d->D + (size_t)row * sh.ld;
+    if (pop_rows[j] == 0) continue;                       // (multi-GPU) none of this population's rows live here
     const char* why = "";
     if (plan_stream(pops[j].s, 1, ctx->sm_count, &pops[j].plan, &why) != cudaSuccess)
       return fail(PPLS_E_UNSUPPORTED, std::string("meta fit: no streaming plan for this shape: ") + why);
@@ -1850,15 +1855,22 @@ extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, c
   CU(cudaMalloc(&B.momvecs, (size_t)J * veclen * sizeof(double)));
   CU(cudaMalloc(&B.L, (size_t)sh.ld * sizeof(double)));
   CU(cudaMalloc(&B.trace, (size_t)(EMsteps + 1) * J * sizeof(double)));
-  CU(cudaMalloc(&B.ssq, (size_t)2 * J * sizeof(double)));
+  CU(cudaMalloc(&B.ssq, (size_t)3 * J * sizeof(double)));           // per population: ||X||^2, ||Y||^2 | row counts
   CU(cudaMalloc(&B.scr, (size_t)2 * nblocks * sizeof(double)));
   CU(cudaMalloc(&B.sts, (size_t)J * sizeof(FitState)));
   CU(cudaMemsetAsync(B.trace, 0, (size_t)(EMsteps + 1) * J * sizeof(double), ctx->stream));
   // per-population sums of squares (loglC.cpp:421,425: X.array().square().sum() of the population's rows)
-  for (int j = 0; j < J; ++j) CU(launch_ssq(pops[j].D, pops[j].s, B.ssq + 2 * j, B.scr, nblocks, ctx->stream));
-  std::vector<double> ssq((size_t)2 * J);
+  CU(cudaMemsetAsync(B.ssq, 0, (size_t)3 * J * sizeof(double), ctx->stream));
+  for (int j = 0; j < J; ++j)
+    if (pop_rows[j] > 0) CU(launch_ssq(pops[j].D, pops[j].s, B.ssq + 2 * j, B.scr, nblocks, ctx->stream));
+  std::vector<double> ssq((size_t)3 * J);
+  for (int j = 0; j < J; ++j) ssq[(size_t)2 * J + j] = (double)pop_rows[j];
+  CU(cudaMemcpyAsync(B.ssq + 2 * J, ssq.data() + 2 * J, (size_t)J * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+  if (multi) { rc = allreduce_sum(ctx, B.ssq, (size_t)3 * J); if (rc) return rc; }     // population totals over the ranks
   CU(cudaMemcpyAsync(ssq.data(), B.ssq, ssq.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
+  for (int j = 0; j < J; ++j)
+    if (ssq[(size_t)2 * J + j] < 0.5) return fail(PPLS_E_INVALID, "empty population");
   std::vector<FitState> hst(J);
   std::vector<double> L0;
   pack_loadings(sh, 1, guess->W, guess->C, L0);
@@ -1866,7 +1878,7 @@ extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, c
     FitState& h = hst[j];
     memset(&h, 0, sizeof(h));
     h.b[0] = guess->B[0]; h.t[0] = guess->sigT[0]; h.sigE = guess->sigE; h.sigF = guess->sigF; h.sigH = guess->sigH;
-    h.ssqX = ssq[2 * j]; h.ssqY = ssq[2 * j + 1]; h.Ntot = (double)pop_rows[j];
+    h.ssqX = ssq[2 * j]; h.ssqY = ssq[2 * j + 1]; h.Ntot = ssq[(size_t)2 * J + j];
     h.max_steps = EMsteps; h.atol = atol; h.R = 1; h.orth_type = PPLS_ORTH_SVD;
   }
   CU(cudaMemcpyAsync(B.sts, hst.data(), (size_t)J * sizeof(FitState), cudaMemcpyHostToDevice, ctx->stream));
@@ -1878,9 +1890,13 @@ extern "C" int ppls_meta_run(ppls_ctx* ctx, const ppls_data* d, int32_t n_pop, c
   while (!finished) {
     for (int rep = 0; rep < 8 && passes <= EMsteps; ++rep, ++passes) {
       for (int j = 0; j < J; ++j) {
+        if (pop_rows[j] == 0) { CU(cudaMemsetAsync(B.momvecs + (size_t)j * veclen, 0, (size_t)veclen * sizeof(double), ctx->stream)); continue; }
         CU(launch_em_stream(pops[j].plan, pops[j].s, pops[j].D, B.L, B.sts + j, B.partials, nullptr, nullptr, 0, ctx->stream));
         CU(launch_reduce_partials(B.partials, pops[j].plan.grid, veclen, B.momvecs + (size_t)j * veclen, B.sts + j, ctx->stream));
       }
+      // row-sharded: the pooled sums of EM_W_multi.R:481-482 run over every rank's rows (after the fit has ended the
+      // kernels above no longer rewrite the vectors and this sum scales stale values that nothing reads)
+      if (multi) { rc = allreduce_sum(ctx, B.momvecs, (size_t)J * veclen); if (rc) return rc; }
       CU(launch_meta_update(sh, J, B.momvecs, B.L, B.sts, B.trace, 0, ctx->stream));
     }
     CU(cudaMemcpyAsync(hst.data(), B.sts, (size_t)J * sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));

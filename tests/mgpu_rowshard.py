@@ -9,7 +9,7 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
-from ppls_b200 import Context, Data, Fit, PPLS, PPLS_simult, PPLS_simult_batched, synth   # noqa: E402
+from ppls_b200 import Context, Data, Fit, PPLS, PPLS_simult, PPLS_simult_batched, meta_PPLSi, synth   # noqa: E402
 
 
 def fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, xchg):
@@ -41,6 +41,12 @@ def fit_once(local, rank, world, dev, N, p, q, r, steps, truth, st, xchg):
             os.environ["PPLS_BATCH_GEMM"] = gemm
             seq["batched"].append(PPLS_simult_batched(None, None, r, inits, EMsteps=steps, atol=-np.inf, data=d))
         os.environ.pop("PPLS_BATCH_GEMM", None)
+        # multi-population fit on row shards: three populations cut so that one spans the ranks' boundary and the last
+        # rank holds none of the first (local row counts per population, zeros allowed)
+        cuts = [0, int(N * 0.31), int(N * 0.66), N]
+        local_counts = [max(0, min(hi, cuts[j + 1]) - max(lo, cuts[j])) for j in range(3)]
+        seq["meta"] = meta_PPLSi(None, None, None, 8, -np.inf, data=d, pop_rows=local_counts)
+        seq["meta_cuts"] = cuts
     d.close()
     dist.barrier()
     ctx.close()
@@ -90,7 +96,14 @@ def main():
         for gi, bres in enumerate(seq["batched"]):       # start 0 of the batched runs is the single fit above
             errs[f"batched{gi}_W"] = relmax(bres[0]["loop_state"]["W"], xa["W"])
             errs[f"batched{gi}_loglik"] = relmax(bres[0]["loglik"], xa["loglik"])
-        ok = (same_ranks and errs["loglik"] < 1e-10 and errs["seq_loglik"] < 1e-10 and errs["simult_default_loglik"] < 1e-10
+        from oracle import ppls_meta
+        cuts = seq["meta_cuts"]
+        mo = ppls_meta.meta_pplsi(X, Y, [int(c) for c in np.diff(cuts)], 8, -np.inf)
+        errs["meta_W"] = relmax(seq["meta"]["W"], mo["W"]); errs["meta_C"] = relmax(seq["meta"]["C"], mo["C"])
+        errs["meta_params"] = max(abs(seq["meta"]["params"][j][k] / mo["params"][j][k] - 1) for j in range(3)
+                                  for k in ("B_T", "sigX", "sigY", "sigH", "sigT"))
+        errs["meta_log"] = relmax(seq["meta"]["log"], np.asarray(mo["log"])[:seq["meta"]["log"].shape[0]])
+        ok = (same_ranks and errs["loglik"] < 1e-10 and errs["meta_log"] < 1e-10 and errs["seq_loglik"] < 1e-10 and errs["simult_default_loglik"] < 1e-10
               and all(v < 1e-8 for v in errs.values()) and errs["repeat"] == 0.0 and errs["vs_nccl"] < 1e-12)
         # (the NCCL form reduces the CTAs' partial vectors in another fixed order than the fused tail does, so the two agree to
         # rounding, not bit for bit; every form is bit-reproducible run to run and bit-identical across ranks)
