@@ -216,6 +216,11 @@ extern "C" int ppls_nccl_unique_id(void* id_out, size_t nbytes) {
   return PPLS_OK;
 }
 
+static unsigned long long xchg_timeout_ns() {
+  const char* e = getenv("PPLS_XCHG_TIMEOUT_MS");
+  const long long ms = (e && atoll(e) > 0) ? atoll(e) : 20000;
+  return (unsigned long long)ms * 1000000ull;
+}
 static int allreduce_sum(ppls_ctx* ctx, double* dbuf, size_t count);
 
 // Peer exchange set-up: every rank allocates [control 1 KB | inbox 2 x world x slot doubles], publishes its
@@ -281,7 +286,7 @@ static void xchg_setup(ppls_ctx* c) {
   x.epoch = (unsigned long long*)(c->xbuf + 512);
   x.counter = (unsigned int*)(c->xbuf + 520);
   x.failed = (int*)(c->xbuf + 524);
-  x.rank = c->rank; x.world = W; x.slot = (long long)XCHG_SLOT;
+  x.rank = c->rank; x.world = W; x.slot = (long long)XCHG_SLOT; x.timeout_ns = xchg_timeout_ns();
   c->xchg_on = true;
 }
 
@@ -356,7 +361,7 @@ extern "C" int ppls_ctx_create_multi(ppls_ctx** out, const int* device_ids, int 
     x.epoch = (unsigned long long*)(c->xbuf + 512);
     x.counter = (unsigned int*)(c->xbuf + 520);
     x.failed = (int*)(c->xbuf + 524);
-    x.rank = i; x.world = n_devices; x.slot = (long long)XCHG_SLOT;
+    x.rank = i; x.world = n_devices; x.slot = (long long)XCHG_SLOT; x.timeout_ns = xchg_timeout_ns();
     c->xchg_on = true;
   }
   *out = g;
@@ -514,6 +519,65 @@ static int data_finalize(ppls_ctx* ctx, ppls_data* d) {
 
 static int data_from_host_impl(ppls_ctx* ctx, const double* X, int64_t ldX, const double* Y, int64_t ldY,
                                int64_t n, int64_t p, int64_t q, int colshard, ppls_data** out);
+
+// ---- exchange recovery -------------------------------------------------------------------------------------------
+// The peer exchange keeps context-wide state (epoch, flags).  A wait that timed out (a peer died or abandoned its fit
+// mid-run) leaves `failed` set and the ranks' epochs apart, and every later fit on the context would fail or pair up the
+// wrong exchanges.  Creating a fit is collective, so that is where the ranks compare notes: everybody contributes its
+// epoch and its failed flag; if anything differs, everybody clears its own control words and flags and the ranks meet
+// again before anyone sends.  Normal cost: one 17-double allreduce per fit creation.
+static int xchg_recover_dist(ppls_ctx* ctx) {
+  if (!ctx->xchg_on || ctx->world == 1 || ctx->group) return PPLS_OK;
+  const int W = ctx->world;
+  struct { unsigned long long epoch; unsigned int counter; int failed; } hw;
+  CU(cudaMemcpyAsync(&hw, ctx->xbuf + 512, sizeof(hw), cudaMemcpyDeviceToHost, ctx->stream));
+  CU(cudaStreamSynchronize(ctx->stream));
+  std::vector<double> v((size_t)XCHG_MAXW + 1, 0.0);
+  v[ctx->rank] = (double)hw.epoch; v[XCHG_MAXW] = hw.failed ? 1.0 : 0.0;
+  double* db = nullptr;
+  CU(cudaMalloc(&db, v.size() * sizeof(double)));
+  cudaError_t e = cudaMemcpyAsync(db, v.data(), v.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+  int rc = (e == cudaSuccess) ? allreduce_sum(ctx, db, v.size()) : fail(PPLS_E_CUDA, cudaGetErrorString(e));
+  if (rc == PPLS_OK) {
+    e = cudaMemcpyAsync(v.data(), db, v.size() * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) rc = fail(PPLS_E_CUDA, cudaGetErrorString(e));
+  }
+  bool need = v[XCHG_MAXW] != 0.0;
+  for (int r = 1; r < W; ++r) need = need || v[r] != v[0];
+  if (rc == PPLS_OK && need) {
+    e = cudaMemsetAsync(ctx->xbuf, 0, XCHG_INBOX_OFFSET, ctx->stream);           // control words, flags, per-CTA flags
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) rc = fail(PPLS_E_CUDA, cudaGetErrorString(e));
+    if (rc == PPLS_OK) rc = allreduce_sum(ctx, db, 1);                            // nobody sends before everybody has cleared
+    if (rc == PPLS_OK && cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = fail(PPLS_E_CUDA, "stream sync");
+    if (getenv("PPLS_K1_VERBOSE") && atoi(getenv("PPLS_K1_VERBOSE")))
+      fprintf(stderr, "[ppls] rank %d: peer exchange state reset (a previous fit failed or was abandoned)\n", ctx->rank);
+  }
+  cudaFree(db);
+  return rc;
+}
+// The same for a multi-device context: one host thread sees every device's words.
+static int xchg_recover_group(ppls_ctx* g) {
+  bool need = false;
+  unsigned long long e0 = 0;
+  for (size_t i = 0; i < g->subs.size(); ++i) {
+    ppls_ctx* c = g->subs[i];
+    struct { unsigned long long epoch; unsigned int counter; int failed; } hw;
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaMemcpy(&hw, c->xbuf + 512, sizeof(hw), cudaMemcpyDeviceToHost));
+    if (i == 0) e0 = hw.epoch;
+    need = need || hw.failed || hw.epoch != e0;
+  }
+  if (!need) return PPLS_OK;
+  for (ppls_ctx* c : g->subs) {
+    CU(cudaSetDevice(c->device));
+    CU(cudaMemset(c->xbuf, 0, XCHG_INBOX_OFFSET));
+    CU(cudaDeviceSynchronize());
+  }
+  return PPLS_OK;
+}
 
 static bool is_group(const ppls_ctx* c) { return c && !c->subs.empty(); }
 static int no_group(const ppls_ctx* c, const char* what) {
@@ -902,6 +966,7 @@ extern "C" int ppls_fit_create(ppls_ctx* ctx, const ppls_data* d, const ppls_opt
     ppls_fit* f = new (std::nothrow) ppls_fit();
     if (!f) return fail(PPLS_E_OOM, "host allocation failed");
     f->ctx = ctx; f->data = d; f->opts = *opts; f->R = opts->r;
+    { int rr = xchg_recover_group(ctx); if (rr) { fit_free(f); return rr; } }
     for (size_t i = 0; i < ctx->subs.size(); ++i) {
       ppls_fit* part = nullptr;
       int rc = fit_create_impl(ctx->subs[i], d->shards[i], opts, init, false, nullptr, 0, nullptr, &part);
@@ -960,6 +1025,10 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     fit_free(f);
     return fail(PPLS_E_UNSUPPORTED, "multi-device context: this shape takes the wide-row path, which exchanges through NCCL -- "
                                     "use one process per GPU (ppls_ctx_create_dist)");
+  }
+  if (!f->wide && !f->cols && !seq && (size_t)f->veclen <= XCHG_SLOT) {       // this fit exchanges through the peer inboxes
+    rc = xchg_recover_dist(ctx);                                                // (collective, like this call)
+    if (rc) { fit_free(f); return rc; }
   }
   {
     const char* ef = getenv("PPLS_FUSE_TAIL");

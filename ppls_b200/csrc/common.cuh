@@ -162,6 +162,7 @@ struct XchgDev {
   int* failed;                            // local: a wait timed out (a peer died)
   int rank, world;
   long long slot;                         // doubles per (parity, source rank) slot
+  unsigned long long timeout_ns;          // a wait longer than this marks the exchange failed (20 s; PPLS_XCHG_TIMEOUT_MS)
 };
 // reduce the per-CTA partial vectors (as launch_reduce_partials) and send the result to every rank's inbox
 cudaError_t launch_xsend(const double* partials, int nparts, int64_t len, const XchgDev& x, const FitState* st,

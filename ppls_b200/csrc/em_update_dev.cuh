@@ -220,7 +220,7 @@ __device__ inline void xchg_wait(const XchgDev& x, unsigned long long next) {
   const unsigned long long t0 = global_timer_ns();
   if (lane < x.world) {
     while (ld_relaxed_sys(fl + lane) < next) {
-      if (global_timer_ns() - t0 > 20000000000ull) { atomicExch(x.failed, 1); break; }   // 20 s: a peer is gone
+      if (global_timer_ns() - t0 > x.timeout_ns) { atomicExch(x.failed, 1); break; }   // (20 s by default) a peer is gone
     }
   }
   __syncwarp();
@@ -233,7 +233,7 @@ __device__ inline void xchg_wait_cta(const XchgDev& x, unsigned long long next, 
   const unsigned long long t0 = global_timer_ns();
   if (lane < x.world) {
     while (ld_relaxed_sys(fl + (size_t)lane * XCHG_MAXCTA) < next) {
-      if (global_timer_ns() - t0 > 20000000000ull) { atomicExch(x.failed, 1); break; }   // 20 s: a peer is gone
+      if (global_timer_ns() - t0 > x.timeout_ns) { atomicExch(x.failed, 1); break; }   // (20 s by default) a peer is gone
     }
   }
   __syncwarp();

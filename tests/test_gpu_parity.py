@@ -273,6 +273,20 @@ def test_row_sharded_two_gpus_peer_exchange():
     assert r.returncode == 0 and "ROWSHARD OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
+def test_peer_exchange_recovers_from_an_abandoned_fit():
+    """A fit that one rank abandons mid-run times out on the other rank (PPLS_E_NCCL), and the next fits on the same
+    contexts are bit-identical to the one before the failure (tests/mgpu_recover.py; both forms of the exchange)."""
+    import os, subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PPLS_XCHG_TIMEOUT_MS="400")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29549", os.path.join(root, "tests", "mgpu_recover.py")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    assert r.returncode == 0 and "RECOVER OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
 def test_multi_device_context_matches_oracle_and_the_torchrun_form(tmp_path):
     """ONE process driving 2 GPUs (ppls_ctx_create_multi; what `device = 0:1` means in the R wrapper): host X, Y split
     over the devices, the EM loop with the peer exchange, results gathered -- against the oracle, against a
