@@ -21,6 +21,9 @@ import sys
 import threading
 import time
 
+# NCCL prints its version line ("NCCL version ...", NCCL_DEBUG=VERSION on some boxes) to stdout; stdout is for the ONE JSON line
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
