@@ -291,7 +291,7 @@ def bench_stream(env, name, K, W, args, want_e2e):
     from ppls_b200 import Data, Fit, synth
     torch, world, rank = env.torch, env.world, env.rank
     ctx, dev = env.ctx, env.dev
-    N, p, q, r = WORKLOADS[name]
+    N, p, q, r = WORKLOADS[name.split("_")[0]]          # "c4_rows": C4's shape, row-sharded (bench-only comparison)
     if args.rows and name == args.workload:
         N = args.rows
     free_b, _ = torch.cuda.mem_get_info(dev)
@@ -428,7 +428,9 @@ def bench_stream(env, name, K, W, args, want_e2e):
         "clocks": clocks, "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "peak_source": peak_src,
-                     "kernel": "wide_kernel x2 (project + accumulate passes)" if wide else "em_stream_kernel",
+                     "kernel": ("wide_kernel x2 (project + accumulate passes; algorithmic bytes count both)" if wide else
+                                "wide3_kernel (single pass from HBM, second read from L2; algorithmic bytes count one)"
+                                if name.startswith("c4") else "em_stream_kernel"),
                      "kernel_ms": k1_ms, "algorithmic_bytes_per_launch": bytes_pass,
                      "frac_of_nominal_8000": achieved / 8000.0,
                      "read_only_probe_gbs": read_probe},
@@ -583,7 +585,9 @@ def run_ours(args):
         main = bench_stream(env, args.workload, K, W, args, want_e2e=not args.no_e2e)
     others = {}
     if not args.no_others:
-        for name in ("c2", "c4", "c5"):
+        # at N > 1 C4 runs column-sharded (BASELINE.json's configuration) AND, for comparison, row-sharded (250 rows per GPU at
+        # N = 8 through the single-pass wide kernel, one allreduce of the (p+q) x r moment vector per iteration)
+        for name in ("c2", "c4", "c5") + (("c4_rows",) if env.world > 1 else ()):
             if name == args.workload:
                 continue
             try:
