@@ -49,6 +49,7 @@ struct Wide3Args {
   double* gpart;                 // [lanes][ld][R]            G per lane
   double* gram_part;             // [nchunk * 32][3 R^2]      Gram partials of the reducers (one per row)
   unsigned long long* cnt;       // [2][nchunk]               arrivals: CTAs whose projections are in, duties done
+  unsigned long long* trace;     // PPLS_WIDE_TRACE=1: [nchunk][12] globaltimer stamps of the chain of one chunk (else null)
   int64_t n, npad;
   int32_t ld, p2, npX, npanel, R, nstage, lag;
   int32_t lanes, ctas_per_lane, chunks_per_lane, nchunk, hint;
@@ -74,6 +75,10 @@ __device__ __forceinline__ void w3_wait(const unsigned long long* c, unsigned lo
   do {
     asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(c) : "memory");
   } while (v < target);
+}
+
+__device__ __forceinline__ void w3_stamp(unsigned long long* trace, int chunk, int what) {
+  if (trace) trace[(size_t)chunk * 12 + what] = global_timer_ns();
 }
 
 struct Wide3Smem { uint32_t ring, ws, mu, comb, xy, bars, total; };
@@ -185,6 +190,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
         if (lane == 0) {
           if (c >= W3_MUSLOTS) mbar_wait(mubars + 8u * (W3_MUSLOTS + slot), (uint32_t)((c / W3_MUSLOTS - 1) & 1));
           w3_wait(cntR + c_lo + c, targetR);                                // the chunk's mu_T, mu_U are complete
+          if (blockIdx.x == 0) w3_stamp(a.trace, c_lo + c, 5);
         }
         __syncwarp();
         const double* m0 = a.mu8 + (size_t)(c_lo + c) * W3_TR * 8;
@@ -203,7 +209,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
           for (int j = 0; j < 8; ++j) md[256 + lane + 32 * j] = vu[j];
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(mubars + 8u * slot);                     // (release: the stores above are in)
+        if (lane == 0) { mbar_arrive(mubars + 8u * slot); if (blockIdx.x == 0) w3_stamp(a.trace, c_lo + c, 6); }   // (release: the stores above are in)
       }
     }
     return;
@@ -219,8 +225,10 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
         unsigned int v;
         const uint32_t sa = sbase + lay.comb + 4u * (uint32_t)(w & 15);
         do { asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(sa) : "memory"); } while (v < (unsigned int)(W3_WARPS * ((w >> 4) + 1)));
+        if (blockIdx.x == 0) w3_stamp(a.trace, c_lo + w, 0);       // this CTA's projections of the chunk are stored
         __threadfence();
         atomicAdd(cntP + c_lo + w, 1ull);
+        if (blockIdx.x == 0) w3_stamp(a.trace, c_lo + w, 1);
       }
     }
     return;
@@ -242,7 +250,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
       const double* base = a.pring + ((size_t)(ln * ring_slots + wl % ring_slots) * a.ctas_per_lane) * 4 * W3_TR * R + (size_t)i * R + k;
       const size_t cstride = (size_t)4 * W3_TR * R, hstride = (size_t)2 * W3_TR * R, sstride = (size_t)W3_TR * R;
       const bool live = act && row < a.n;
-      if (tr == 0) w3_wait(cntP + chunk, targetP);                              // every CTA's projections of the chunk are in
+      if (tr == 0) { w3_wait(cntP + chunk, targetP); if (i == 0) w3_stamp(a.trace, chunk, 2); }   // every CTA's projections of the chunk are in
       w3_bar_red();
       double sx0 = 0.0, sx1 = 0.0, sy = 0.0;
       for (int c0 = y; c0 < nact; c0 += 160) {                                  // all loads of a sweep in flight, added in a fixed order
@@ -275,6 +283,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
       double xw = sx0 + sx1, yc = sy;
 #pragma unroll
       for (int o = 1; o < 16; o <<= 1) { xw += __shfl_xor_sync(0xffffffffu, xw, o); yc += __shfl_xor_sync(0xffffffffu, yc, o); }
+      if (tr == 0 && i == 0) w3_stamp(a.trace, chunk, 3);
       if (act && y == 0) {
         const double mt = a.st->aT[k] * xw + a.st->bT[k] * yc, mw = a.st->aU[k] * xw + a.st->bU[k] * yc;
         a.mu[(size_t)row * R + k] = mt;
@@ -290,7 +299,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
         const int oa = (which == 2 ? 16 : 0), ob = (which == 0 ? 0 : 16);      // Gxx: x,x  Gxy: x,y  Gyy: y,y
         a.gram_part[((size_t)chunk * W3_NRED + i) * 3 * R * R + e] = xy[oa + kk] * xy[ob + l];
       }
-      if (tr == 0) atomicAdd(cntR + chunk, 1ull);                               // (the Gram partials are read by the next kernel)
+      if (tr == 0) { atomicAdd(cntR + chunk, 1ull); if (i == 0) w3_stamp(a.trace, chunk, 4); }   // (the Gram partials are read by the next kernel)
       w3_bar_red();                                                             // xy is free again
     }
     return;
@@ -310,6 +319,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
     // ---- P(w): projections of my panel tiles of chunk w ------------------------------------------------------
     if (w < nch) {
       const int chunk = c_lo + w;
+      if (blockIdx.x == 0 && tid == 0) w3_stamp(a.trace, chunk, 8);             // start of the chunk's projection
       const int64_t row0 = (int64_t)chunk * W3_TR;
       const int rows = (int)((a.n - row0 < W3_TR) ? (a.n - row0) : W3_TR);
       // this CTA's slot of the ring: [half h][side X|Y][32 rows][R] -- the projections are summed over the CTA's own panels
@@ -355,7 +365,9 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
     // ---- A(w - lag): accumulate G from the same tiles (L2) with the chunk's mu ---------------------------------
     if (w >= a.lag && ns > 0) {
       const int c = w - a.lag, mslot = c % W3_MUSLOTS;
+      if (blockIdx.x == 0 && tid == 0) w3_stamp(a.trace, c_lo + c, 9);          // (about to wait for the chunk's mu)
       mbar_wait(mubars + 8u * mslot, (uint32_t)((c / W3_MUSLOTS) & 1));          // the mu warp has staged the chunk's mu
+      if (blockIdx.x == 0 && tid == 0) w3_stamp(a.trace, c_lo + c, 7);
       const uint32_t mbase = sbase + lay.mu + (uint32_t)mslot * 2u * W3_MU_BYTES + (uint32_t)(t * 8 + g) * 8u;
       uint32_t dep = 0;
 #pragma unroll
@@ -454,13 +466,29 @@ bool plan_wide3(const DataShape& s, int R, int sm_count, WidePlan* w) {
 }
 
 size_t wide3_ring_doubles(const DataShape& s, const WidePlan& w) { (void)s; return (size_t)w.v3_lanes * (w.v3_lag + 1) * w.v3_cpl * 4 * W3_TR * w.R; }
-size_t wide3_counter_doubles(const WidePlan& w) { return (size_t)2 * w.v3_nchunk; }
+size_t wide3_counter_doubles(const WidePlan& w) { return (size_t)2 * w.v3_nchunk + (w3_env("PPLS_WIDE_TRACE", 0) ? (size_t)12 * w.v3_nchunk : 0); }
+
+// PPLS_WIDE_TRACE=1: the chain of one chunk, relative to "CTA 0's projections stored" (us)
+__global__ void wide3_trace_print(const unsigned long long* tr, int nchunk, const FitState* st) {
+  if (st->pass != 3) return;
+  printf("[ppls] wide3 chain per chunk (us after CTA 0 stored its projections): published | reducer sees all | sums done | duty counted | "
+         "mu warp sees 32 duties | mu staged || CTA 0: projection start, wants mu, has mu (relative to the previous chunk's)\n");
+  for (int c = 2; c < nchunk; c += (nchunk > 24 ? nchunk / 12 : 1)) {
+    const unsigned long long* t = tr + (size_t)c * 12;
+    const double t0 = (double)t[0];
+    printf("[ppls]   chunk %3d: %5.1f | %5.1f | %5.1f | %5.1f | %5.1f | %5.1f || P start %6.1f  wants mu %6.1f  has mu %6.1f  (period %5.1f)\n", c,
+           ((double)t[1] - t0) * 1e-3, ((double)t[2] - t0) * 1e-3, ((double)t[3] - t0) * 1e-3, ((double)t[4] - t0) * 1e-3,
+           ((double)t[5] - t0) * 1e-3, ((double)t[6] - t0) * 1e-3, ((double)t[8] - t0) * 1e-3, ((double)t[9] - t0) * 1e-3, ((double)t[7] - t0) * 1e-3,
+           ((double)t[0] - (double)(t - 12)[0]) * 1e-3);
+  }
+}
 
 cudaError_t launch_wide3(const WidePlan& w, const DataShape& s, const double* D, const double* L, const FitState* st, double* pring,
                          double* mu, double* mu8, double* gpart, double* gram_part, double* counters, cudaStream_t stream) {
   Wide3Args a{};
   a.D = D; a.L = L; a.st = st; a.pring = pring; a.mu = mu; a.mu8 = mu8; a.gpart = gpart; a.gram_part = gram_part;
   a.cnt = reinterpret_cast<unsigned long long*>(counters);
+  a.trace = w3_env("PPLS_WIDE_TRACE", 0) ? a.cnt + 2 * w.v3_nchunk : nullptr;
   a.n = s.n; a.npad = wide_npad(s.n); a.ld = s.ld; a.p2 = s.p2; a.npX = s.npX; a.npanel = s.npX + s.npY; a.R = w.R;
   a.nstage = w.v3_nstage; a.lag = w.v3_lag; a.lanes = w.v3_lanes; a.ctas_per_lane = w.v3_cpl;
   a.chunks_per_lane = w.v3_chunks_per_lane; a.nchunk = w.v3_nchunk; a.hint = w3_env("PPLS_WIDE_HINT", 1);   // bit 0: L2 eviction policies
@@ -469,8 +497,10 @@ cudaError_t launch_wide3(const WidePlan& w, const DataShape& s, const double* D,
   if (!k) return cudaErrorInvalidValue;
   void* args[] = {(void*)&a};
   // cooperative: the CTAs wait on one another's chunk counters, so all of them must be resident (<= 1 per SM by construction)
-  return cudaLaunchCooperativeKernel((const void*)k, dim3(w.v3_lanes * w.v3_cpl), dim3(W3_THREADS), args,
-                                     wide3_smem(NS, w.v3_nstage).total, stream);
+  cudaError_t e = cudaLaunchCooperativeKernel((const void*)k, dim3(w.v3_lanes * w.v3_cpl), dim3(W3_THREADS), args,
+                                              wide3_smem(NS, w.v3_nstage).total, stream);
+  if (e == cudaSuccess && a.trace) wide3_trace_print<<<1, 1, 0, stream>>>(a.trace, w.v3_nchunk, st);
+  return e;
 }
 
 }  // namespace ppls
