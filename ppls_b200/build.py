@@ -23,7 +23,7 @@ UNITS = {
     "em_update.cu": ["-fmad=false"],
     "em_seq.cu": ["-fmad=false"],
     "em_var.cu": [],
-    "em_batch.cu": [],
+    "em_batch.cu": (["-DPPLS_HSTAGES=" + os.environ["PPLS_HSTAGES"]] if os.environ.get("PPLS_HSTAGES") else []),
     "data.cu": ["-fmad=false"],
     "probe.cu": [],
     "capi.cu": [],

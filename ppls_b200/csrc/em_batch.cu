@@ -216,7 +216,7 @@ struct ProjMuArgs {
   const double* D; const double* L; const double* coef; double* P; double* gpart;
   int64_t n;
   int ld, p2, q2, RP, nstart, rowtiles;
-  int dbg;                       // timing experiments only (PPLS_BGEMM_DBG): 1 = no copies, 2 = no DMMA
+  int dbg;                       // timing experiments only (PPLS_BGEMM_DBG): 1 = no copies, 2 = no DMMA, 3 = no epilogue, 4 = no Gram, 5 = no mu stores
 };
 template <int R>
 __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs a) {
@@ -331,6 +331,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs
 
     // ---- Gram blocks: entry (component c, which, l) = sum over the tile's rows of v_c * w_{start(c), l} ------------
     // rows past n were zero-filled, so they add nothing
+    if (a.dbg != 3 && a.dbg != 4)                        // (3: no epilogue at all, 4: no Gram blocks -- timing experiments)
 #pragma unroll
     for (int j = 0; j < 4; ++j)
 #pragma unroll
@@ -368,6 +369,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs
       }
 
     // ---- mu_T, mu_U of the tile, straight from the accumulators ------------------------------------------------
+    if (a.dbg != 3 && a.dbg != 5)                        // (5: no mu stores -- timing experiment)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int cl = wn + j * 8 + 2 * tig, c = cb * FT_N + cl;
@@ -398,6 +400,219 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu_kernel(const ProjMuArgs
     const int c = e / (3 * R), wl = e - c * 3 * R, w = wl / R, l = wl - w * R;
     const int st = c / R, k = c - st * R;
     if (st < a.nstart) a.gpart[((size_t)blockIdx.x * a.nstart + st) * 3 * R * R + w * R * R + k * R + l] = gacc[e];
+  }
+}
+
+// ---- the same kernel as two HALF-CTAs that work out of phase ("ping-pong") ---------------------------------------------
+// bprojmu_kernel's epilogue (Gram blocks + mu stores) is 19 % of its time (282 -> 228 us with the epilogue switched off,
+// PPLS_BGEMM_DBG=3), and the tensor pipe idles through it because all 8 consumer warps are in it together.  Here the
+// CTA is two independent halves -- consumer warpgroup h (4 warps, a 64-row x 64-component tile, the same 32 x 32 warp
+// tiles), two producer warps and a ring of its own each -- walking alternate tiles; half 1 starts half a tile late, so
+// one half's epilogue runs under the other half's K loop.  Same arithmetic per element, same fixed-order sums.
+// RESULT: slower than bprojmu_kernel (see bproj_pingpong below); kept as an opt-in experiment, parity-tested.
+constexpr int HT = 64;                       // rows of a half-CTA's tile
+#ifndef PPLS_HSTAGES
+#define PPLS_HSTAGES 3
+#endif
+constexpr int HSTAGES = PPLS_HSTAGES;
+constexpr int HSTAGE = HT * BAP + BK * FBP;  // doubles per stage of one half
+template <int R>
+__global__ void __launch_bounds__(WS_THREADS, 1) bprojmu2_kernel(const ProjMuArgs a) {
+  static_assert(8 % R == 0, "a start must not straddle a DMMA tile");
+  extern __shared__ __align__(16) double sm[];   // per half: [HSTAGES][A: HT x BAP | B: BK x FBP] | gsh [2][FT_N][3R] | coef [4][FT_N] | gacc | then the mbarriers
+  const int ncb2 = a.RP / FT_N;
+  const int rowtiles = (int)((a.n + HT - 1) / HT);
+  const int64_t ntile = (int64_t)ncb2 * rowtiles;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
+  const int nsX = (a.p2 + BK - 1) / BK, nsY = (a.q2 + BK - 1) / BK, nst = nsX + nsY;
+  const size_t half_doubles = (size_t)HSTAGES * HSTAGE + 2 * FT_N * 3 * R + 4 * FT_N + (size_t)ncb2 * FT_N * 3 * R;
+  const int half = (warp < 8) ? (warp >> 2) : ((warp - 8) >> 1);             // consumer warpgroup / producer warp pair
+  double* hs = sm + (size_t)half * half_doubles;
+  double* gsh = hs + (size_t)HSTAGES * HSTAGE;
+  double* csh = gsh + 2 * FT_N * 3 * R;
+  double* gacc = csh + 4 * FT_N;
+  const uint32_t bars0 = bsm32(sm + 2 * half_doubles);                       // [2 halves][full HSTAGES | empty HSTAGES] | start
+  const uint32_t bars = bars0 + (uint32_t)half * 2u * HSTAGES * 8u;
+  const uint32_t startbar = bars0 + 4u * HSTAGES * 8u;
+  for (int e = tid; e < 2 * ncb2 * FT_N * 3 * R; e += WS_THREADS) {
+    const int h = e / (ncb2 * FT_N * 3 * R), r2 = e - h * (ncb2 * FT_N * 3 * R);
+    (sm + (size_t)h * half_doubles + (size_t)HSTAGES * HSTAGE + 2 * FT_N * 3 * R + 4 * FT_N)[r2] = 0.0;
+  }
+  if (tid == 0) {
+    for (int h = 0; h < 2; ++h)
+      for (int b = 0; b < HSTAGES; ++b) {
+        bbar_init(bars0 + (uint32_t)(h * 2 * HSTAGES + b) * 8u, 64);                  // full: the half's 64 producer lanes
+        bbar_init(bars0 + (uint32_t)(h * 2 * HSTAGES + HSTAGES + b) * 8u, 4);         // empty: its 4 consumer warps
+      }
+    bbar_init(startbar, 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  const int64_t tfirst = 2 * (int64_t)blockIdx.x + half, tstep = 2 * (int64_t)gridDim.x;
+
+  if (warp >= 8) {
+    // ================================ producers: warps 8, 9 -> half 0; 10, 11 -> half 1 ================================
+    breg_producer();
+    const int ctid = (tid - BTHREADS) & 63;
+    uint32_t g = 0;
+    for (int64_t t = tfirst; t < ntile; t += tstep) {
+      const int cb = (int)(t % ncb2);
+      const int64_t row0 = (t / ncb2) * HT;
+      for (int s = 0; s < nst; ++s, ++g) {
+        const uint32_t slot = g % HSTAGES;
+        if (g >= HSTAGES) bbar_wait(bars + 8u * (HSTAGES + slot), (g / HSTAGES - 1u) & 1u);
+        double* As = hs + (size_t)slot * HSTAGE;
+        double* Bs = As + HT * BAP;
+        const bool sideY = s >= nsX;
+        const int c0 = sideY ? a.p2 : 0, K = sideY ? a.q2 : a.p2, k0 = (sideY ? s - nsX : s) * BK;
+        if (a.dbg != 1) {
+#pragma unroll 4
+          for (int c = 0; c < (HT * BK / 2) / 64; ++c) {            // A: 64 rows x 8 chunks of 2 columns
+            const int chunk = ctid + c * 64, r = chunk >> 3, kc = (chunk & 7) * 2;
+            const bool ok = (row0 + r < a.n) && (k0 + kc < K);
+            bcp16(As + r * BAP + kc, ok ? a.D + (size_t)(row0 + r) * a.ld + c0 + k0 + kc : a.D, ok ? 16 : 0);
+          }
+#pragma unroll 4
+          for (int c = 0; c < (BK * FT_N / 2) / 64; ++c) {          // B: 16 k x 32 pairs of components
+            const int chunk = ctid + c * 64, kk = chunk >> 5, pr = chunk & 31;
+            const bool ok = k0 + kk < K;
+            bcp16(Bs + kk * FBP + pr * 2, ok ? a.L + (size_t)(c0 + k0 + kk) * a.RP + cb * FT_N + pr * 2 : a.L, ok ? 16 : 0);
+          }
+        }
+        bbar_arrive_cpasync(bars + 8u * slot);
+      }
+    }
+    bwait<0>();
+    return;
+  }
+
+  // ==================================== consumers: warpgroup `half` ========================================
+  breg_consumer();
+  const int hw = warp & 3, htid = tid & 127;
+  const int wr = hw >> 1, wm = wr * 32, wn = (hw & 1) * 32;
+  auto hsync = [&]() { if (half == 0) asm volatile("bar.sync 1, 128;" ::: "memory"); else asm volatile("bar.sync 2, 128;" ::: "memory"); };
+  uint32_t g = 0;
+  bool first = true;
+  for (int64_t t = tfirst; t < ntile; t += tstep) {
+    const int cb = (int)(t % ncb2);
+    const int64_t row0 = (t / ncb2) * HT;
+    for (int e = htid; e < 4 * FT_N; e += 128) csh[e] = a.coef[(size_t)(e / FT_N) * a.RP + cb * FT_N + (e % FT_N)];
+    double accx[4][4][2], accy[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { accx[i][j][0] = 0.0; accx[i][j][1] = 0.0; accy[i][j][0] = 0.0; accy[i][j][1] = 0.0; }
+    if (first && half == 1 && a.dbg != 6) bbar_wait(startbar, 0); // half 0 is half way through its first tile (6: no stagger, experiment)
+    for (int s = 0; s < nst; ++s, ++g) {
+      const uint32_t slot = g % HSTAGES;
+      bbar_wait(bars + 8u * slot, (g / HSTAGES) & 1u);
+      const double* As = hs + (size_t)slot * HSTAGE;
+      const double* ar = As + (wm + gid) * BAP + tig;
+      const double* br = As + HT * BAP + tig * FBP + wn + gid;
+      const bool sideY = s >= nsX;
+      const int kleft = (sideY ? a.q2 - (s - nsX) * BK : a.p2 - s * BK);
+      const int nk4 = kleft >= BK ? BK / 4 : (kleft + 3) >> 2;
+      if (a.dbg != 2)
+#pragma unroll
+      for (int k4 = 0; k4 < BK / 4; ++k4) {
+        if (k4 < nk4) {
+          double af[4], bf[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) af[i] = ar[i * 8 * BAP + k4 * 4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) bf[j] = br[k4 * 4 * FBP + j * 8];
+          if (!sideY) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) bdmma(accx[i][j], af[i], bf[j]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) bdmma(accy[i][j], af[i], bf[j]);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        bbar_arrive(bars + 8u * (HSTAGES + slot));
+        if (first && half == 0 && s == nst / 2) bbar_arrive(startbar);
+      }
+    }
+    first = false;
+    hsync();                                   // the fold of the previous tile has read gsh; csh is complete
+
+    // NOTE: a warp's 32 x 32 tile is rows wm + {0, 8, 16, 24} + gid -- but a half tile has only 64 rows and 2 row warps,
+    // so i runs over the warp's FOUR 8-row blocks as in the full-size kernel.
+    if (a.dbg != 3 && a.dbg != 4)
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        double gg[3][R];
+#pragma unroll
+        for (int l = 0; l < R; ++l) { gg[0][l] = 0.0; gg[1][l] = 0.0; gg[2][l] = 0.0; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const double xw = accx[i][j][e], yc = accy[i][j][e];
+#pragma unroll
+          for (int l = 0; l < R; ++l) {
+            double xl, yl;
+            if constexpr (R == 1) { xl = xw; yl = yc; }
+            else if constexpr (R == 2) { xl = accx[i][j][l]; yl = accy[i][j][l]; }
+            else {
+              const int c8 = 2 * tig + e, cl = c8 - (c8 % R) + l, src = (lane & ~3) | (cl >> 1);
+              const double x0 = __shfl_sync(0xffffffffu, accx[i][j][0], src), x1 = __shfl_sync(0xffffffffu, accx[i][j][1], src);
+              const double y0 = __shfl_sync(0xffffffffu, accy[i][j][0], src), y1 = __shfl_sync(0xffffffffu, accy[i][j][1], src);
+              xl = (cl & 1) ? x1 : x0; yl = (cl & 1) ? y1 : y0;
+            }
+            gg[0][l] = fma(xw, xl, gg[0][l]); gg[1][l] = fma(xw, yl, gg[1][l]); gg[2][l] = fma(yc, yl, gg[2][l]);
+          }
+        }
+#pragma unroll
+        for (int w = 0; w < 3; ++w)
+#pragma unroll
+          for (int l = 0; l < R; ++l) {
+            double v = gg[w][l];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (gid == 0) gsh[((size_t)wr * FT_N + wn + j * 8 + 2 * tig + e) * 3 * R + w * R + l] = v;
+          }
+      }
+    if (a.dbg != 3 && a.dbg != 5)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int cl = wn + j * 8 + 2 * tig, c = cb * FT_N + cl;
+      const double2 aT = *reinterpret_cast<const double2*>(csh + cl), bT = *reinterpret_cast<const double2*>(csh + FT_N + cl);
+      const double2 aU = *reinterpret_cast<const double2*>(csh + 2 * FT_N + cl), bU = *reinterpret_cast<const double2*>(csh + 3 * FT_N + cl);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t row = row0 + wm + i * 8 + gid;
+        if (row >= a.n) continue;
+        double* out = a.P + (size_t)row * 2 * a.RP + c;
+        const double x0 = accx[i][j][0], x1 = accx[i][j][1], y0 = accy[i][j][0], y1 = accy[i][j][1];
+        *reinterpret_cast<double2*>(out) = make_double2(aT.x * x0 + bT.x * y0, aT.y * x1 + bT.y * y1);
+        *reinterpret_cast<double2*>(out + a.RP) = make_double2(aU.x * x0 + bU.x * y0, aU.y * x1 + bU.y * y1);
+      }
+    }
+    hsync();
+    for (int e = htid; e < FT_N * 3 * R; e += 128) {
+      double tsum = 0.0;
+#pragma unroll
+      for (int q = 0; q < 2; ++q) tsum += gsh[(size_t)q * FT_N * 3 * R + e];
+      gacc[(size_t)cb * FT_N * 3 * R + e] += tsum;
+    }
+  }
+  // a half that never got a tile must still release the other: (half 0 always has one when half 1 has)
+  asm volatile("bar.sync 3, 256;" ::: "memory");              // both halves' sums are complete
+  const double* g0 = sm + (size_t)HSTAGES * HSTAGE + 2 * FT_N * 3 * R + 4 * FT_N;
+  const double* g1 = g0 + half_doubles;
+  for (int e = tid; e < ncb2 * FT_N * 3 * R; e += BTHREADS) {
+    const int c = e / (3 * R), wl = e - c * 3 * R, w = wl / R, l = wl - w * R;
+    const int st = c / R, k = c - st * R;
+    if (st < a.nstart) a.gpart[((size_t)blockIdx.x * a.nstart + st) * 3 * R * R + w * R * R + k * R + l] = g0[e] + g1[e];
   }
 }
 
@@ -676,7 +891,32 @@ static cudaError_t launch_bprojmu_r(const ProjMuArgs& fa, const BGemmPlan& p, cu
   bprojmu_kernel<R><<<(unsigned)grid, WS_THREADS, smem, stream>>>(fa);
   return cudaGetLastError();
 }
+// PPLS_BPROJ_PP=1: two half-CTAs out of phase (bprojmu2_kernel); default: one 128-row tile per CTA at a time (bprojmu_kernel).
+// Measured at C5: 307-318 us against 281 us -- the half-size tiles cost more (twice the loadings traffic and per-stage
+// hand-offs per flop) than the overlapped epilogue returns, with or without the stagger, with 3 or 4 stages.
+static int bproj_pingpong() {
+  const char* e = getenv("PPLS_BPROJ_PP");
+  return (e && *e) ? (atoi(e) != 0) : 0;
+}
+template <int R>
+static cudaError_t launch_bprojmu2_r(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
+  const size_t half = (size_t)HSTAGES * HSTAGE + 2 * FT_N * 3 * R + 4 * FT_N + (size_t)(p.RP / FT_N) * FT_N * 3 * R;
+  const size_t smem = (2 * half + 4 * HSTAGES + 1) * sizeof(double);
+  if (smem > 227 * 1024) return launch_bprojmu_r<R>(fa, p, stream);
+  cudaError_t e = cudaFuncSetAttribute((const void*)bprojmu2_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  bprojmu2_kernel<R><<<(unsigned)p.nchunk, WS_THREADS, smem, stream>>>(fa);
+  return cudaGetLastError();
+}
 static cudaError_t launch_bprojmu(const ProjMuArgs& fa, const BGemmPlan& p, cudaStream_t stream) {
+  if (bproj_pingpong() && bgemm_ws())
+    switch (p.R) {
+      case 1: return launch_bprojmu2_r<1>(fa, p, stream);
+      case 2: return launch_bprojmu2_r<2>(fa, p, stream);
+      case 4: return launch_bprojmu2_r<4>(fa, p, stream);
+      case 8: return launch_bprojmu2_r<8>(fa, p, stream);
+      default: return cudaErrorInvalidValue;
+    }
   switch (p.R) {
     case 1: return launch_bprojmu_r<1>(fa, p, stream);
     case 2: return launch_bprojmu_r<2>(fa, p, stream);

@@ -213,11 +213,12 @@ def test_batched_multistart_matches_single_runs(ctx, oracle_lib, shape, S, steps
 @pytest.mark.parametrize("shape,S", [((3001, 200, 50, 2), 64), ((1111, 50, 20, 1), 80), ((900, 136, 100, 4), 20), ((700, 300, 140, 8), 20),
                                      # more (row tile, component block) tiles than SMs: every CTA of the persistent kernel walks several
                                      ((20011, 72, 40, 2), 64), ((30000, 40, 24, 4), 40)])
-@pytest.mark.parametrize("stages,ws", [("2", "1"), ("3", "1"), ("4", "1"), ("3", "0")])
-def test_batched_fused_projection_matches_unfused(ctx, shape, S, stages, ws):
+@pytest.mark.parametrize("stages,ws,pp", [("2", "1", "0"), ("3", "1", "0"), ("4", "1", "0"), ("3", "0", "0"), ("3", "1", "1")])
+def test_batched_fused_projection_matches_unfused(ctx, shape, S, stages, ws, pp):
     """em_batch.cu: the fused projection + posterior-mean + Gram kernel (r divides 8) against the separate
     bproj/bmu kernels, for every cp.async depth of the accumulate GEMM, warp-specialised (producer warp +
-    mbarriers) and __syncthreads forms: same EM trajectory up to rounding."""
+    mbarriers) and __syncthreads forms, and the fused kernel as one 128-row tile per CTA (the default) or as two half-CTAs out of phase
+    (pp = 1, an experiment that measured slower): same EM trajectory up to rounding."""
     import os
     from ppls_b200 import Data, PPLS_simult_batched, synth
     N, p, q, r = shape
@@ -225,8 +226,9 @@ def test_batched_fused_projection_matches_unfused(ctx, shape, S, stages, ws):
     d = Data.synthetic(ctx, N, p, q, truth, seed=77)
     inits = [synth.start_params(truth, seed=300 + s, noise=0.4 + 0.05 * s) for s in range(S)]
     outs = {}
-    old = {k: os.environ.get(k) for k in ("PPLS_BATCH_FUSED", "PPLS_BACC_STAGES", "PPLS_BGEMM_WS")}
+    old = {k: os.environ.get(k) for k in ("PPLS_BATCH_FUSED", "PPLS_BACC_STAGES", "PPLS_BGEMM_WS", "PPLS_BPROJ_PP")}
     try:
+        os.environ["PPLS_BPROJ_PP"] = pp
         for fused in ("0", "1"):
             os.environ["PPLS_BATCH_FUSED"] = fused
             os.environ["PPLS_BACC_STAGES"] = stages if fused == "1" else "2"
