@@ -47,7 +47,7 @@ struct Wide3Args {
   double* mu;                    // [2][npad][R]              mu_T, mu_U (kept for ppls_fit_result)
   double* mu8;                   // [2][npad][8]              the same, components padded to 8 (operand of the A tiles)
   double* gpart;                 // [lanes][ld][R]            G per lane
-  double* gram_part;             // [nchunk * 32][3 R^2]      Gram partials of the reducers (one per row)
+  double* gram_part;             // [CTAs][3 R^2]             Gram partials of the reducers (one per CTA: its duties' rows)
   unsigned long long* cnt;       // [2][nchunk]               arrivals: CTAs whose projections are in, duties done
   unsigned long long* trace;     // PPLS_WIDE_TRACE=1: [nchunk][12] globaltimer stamps of the chain of one chunk (else null)
   int64_t n, npad;
@@ -243,6 +243,7 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
     const int ring_slots = a.lag + 1;
     const int nact = (a.npanel < a.ctas_per_lane) ? a.npanel : a.ctas_per_lane;          // CTAs of the lane that own panels
     const int nyown = (a.npanel - a.npX < a.ctas_per_lane) ? a.npanel - a.npX : a.ctas_per_lane;   // ... that own Y panels
+    double gs[2] = {0.0, 0.0};                         // this CTA's Gram sums over its duties: elements tr and tr + 128 of [3][R][R]
     for (int d = pos; d < nch * W3_NRED; d += a.ctas_per_lane) {                // my duties, in the order the chunks complete
       const int wl = d / W3_NRED, i = d - wl * W3_NRED;
       const int chunk = c_lo + wl;
@@ -294,13 +295,23 @@ __global__ void __launch_bounds__(W3_THREADS, 1) wide3_kernel(const Wide3Args a)
         __threadfence();                                   // the writer itself publishes its stores before the count goes up
       }
       w3_bar_red();
-      for (int e = tr; e < 3 * R * R; e += W3_RWARPS * 32) {
-        const int which = e / (R * R), kl = e - which * R * R, kk = kl / R, l = kl - kk * R;
-        const int oa = (which == 2 ? 16 : 0), ob = (which == 0 ? 0 : 16);      // Gxx: x,x  Gxy: x,y  Gyy: y,y
-        a.gram_part[((size_t)chunk * W3_NRED + i) * 3 * R * R + e] = xy[oa + kk] * xy[ob + l];
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const int e = tr + m * W3_RWARPS * 32;
+        if (e < 3 * R * R) {
+          const int which = e / (R * R), kl = e - which * R * R, kk = kl / R, l = kl - kk * R;
+          const int oa = (which == 2 ? 16 : 0), ob = (which == 0 ? 0 : 16);    // Gxx: x,x  Gxy: x,y  Gyy: y,y
+          gs[m] += xy[oa + kk] * xy[ob + l];                                   // (rows past n have xw = yc = 0)
+        }
       }
       if (tr == 0) { atomicAdd(cntR + chunk, 1ull); if (i == 0) w3_stamp(a.trace, chunk, 4); }   // (the Gram partials are read by the next kernel)
       w3_bar_red();                                                             // xy is free again
+    }
+    // one Gram partial per CTA (its duties in their fixed order), summed over the CTAs by wide_finalize_kernel
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const int e = tr + m * W3_RWARPS * 32;
+      if (e < 3 * R * R) a.gram_part[(size_t)blockIdx.x * 3 * R * R + e] = gs[m];
     }
     return;
   }
@@ -457,8 +468,8 @@ bool plan_wide3(const DataShape& s, int R, int sm_count, WidePlan* w) {
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k, W3_THREADS, smem) != cudaSuccess || occ < 1) { cudaGetLastError(); return false; }
   w->v3 = 1; w->v3_lanes = lanes; w->v3_cpl = cpl; w->v3_lag = lag; w->v3_nstage = nstage; w->v3_ns = NS;
   w->v3_chunks_per_lane = (int)((nchunk + lanes - 1) / lanes); w->v3_nchunk = (int)nchunk;
-  // what the shared finalize kernel sees: one G per lane, 32 Gram partials per chunk
-  w->nrg = lanes; w->nblk_mu = (int)nchunk * W3_NRED;
+  // what the shared finalize kernel sees: one G per lane, one Gram partial per CTA
+  w->nrg = lanes; w->nblk_mu = lanes * cpl;
   if (w3_env("PPLS_K1_VERBOSE", 0))
     fprintf(stderr, "[ppls] wide plan (single pass, L2-pipelined): %d panels, %d lane(s) x %d CTAs, <= %d panels per CTA, %lld chunks of %d rows, "
                     "lag %d, %d stages, %zu B shared memory\n", npanel, lanes, cpl, ns, (long long)nchunk, W3_TR, lag, nstage, smem);
