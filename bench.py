@@ -21,8 +21,16 @@ import sys
 import threading
 import time
 
-# NCCL prints its version line ("NCCL version ...", NCCL_DEBUG=VERSION on some boxes) to stdout; stdout is for the ONE JSON line
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout is for the ONE JSON line.  Native libraries print there too (NCCL's "NCCL version ..." line under NCCL_DEBUG=VERSION,
+# which ignores NCCL_DEBUG_FILE), so the real stdout is kept aside for emit() and file descriptor 1 is pointed at stderr.
+sys.stdout.flush()
+_JSON_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(obj):
+    os.write(_JSON_FD, (json.dumps(obj) + "\n").encode())
+
 
 import numpy as np
 
@@ -634,7 +642,7 @@ def run_ours(args):
             out["parity"] = parity
         if others:
             out["other_workloads"] = others
-        print(json.dumps(out), flush=True)
+        emit(out)
     env.close()
 
 
@@ -675,7 +683,7 @@ def run_reference(args):
            "cpu_baseline": {"value": value, "unit": UNIT, "cores": blas, "kind": "port", "sample": sample,
                             "seconds_per_step_sample": per_iter},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def main():
