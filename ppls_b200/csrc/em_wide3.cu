@@ -13,7 +13,7 @@
 //   signal warp    publishes "this CTA's projections of chunk w are stored" to the chunk's arrival counter (the gpu-scope
 //                  fence this takes would stall the tensor pipe if a compute warp executed it)
 //   reducer warps  the CTA's share of the 32 one-row duties of every chunk: wait until every CTA's projections are in, sum
-//                  them in fixed order, form mu_T, mu_U and the Gram partial of the row, count the duty
+//                  them in fixed order, form mu_T, mu_U, add the row's Gram terms to the CTA's Gram partial, count the duty
 //   producer warp  bulk copies into the ring, as far ahead as the ring allows; the first read of a tile asks the L2 to keep
 //                  it (evict_last), the second is its last (evict_first)
 //   mu warp        waits for the chunk's 32 duties and stages its mu_T / mu_U tile in shared memory for the compute warps
