@@ -1048,8 +1048,8 @@ static int fit_create_impl(ppls_ctx* ctx, const ppls_data* d, const ppls_opts* o
     const size_t tb = stream_tail_scratch_doubles(f->plan) * sizeof(double);
     e = cudaMalloc(&f->tail_scratch, tb);
     if (e == cudaSuccess) e = cudaMemsetAsync(f->tail_scratch, 0, tb, ctx->stream);     // barrier words, clocks
-    if (e == cudaSuccess) e = cudaMallocHost(&f->clk_host, 8 * sizeof(unsigned long long));
-    if (e == cudaSuccess) memset(f->clk_host, 0, 8 * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMallocHost(&f->clk_host, 12 * sizeof(unsigned long long));
+    if (e == cudaSuccess) memset(f->clk_host, 0, 12 * sizeof(unsigned long long));
   }
   if (e == cudaSuccess) e = cudaMalloc(&f->Lscratch, Lbytes);
   if (e == cudaSuccess && !f->wide) e = cudaMalloc(&f->partials, (size_t)f->plan.grid * f->veclen * sizeof(double));
@@ -1120,7 +1120,7 @@ static int fit_poll(ppls_fit* f) {
   { int rc0 = ctx_activate(ctx); if (rc0) return rc0; }
   CU(cudaMemcpyAsync(f->st_host, f->st, sizeof(FitState), cudaMemcpyDeviceToHost, ctx->stream));
   if (f->fused)
-    CU(cudaMemcpyAsync(f->clk_host, f->tail_scratch + stream_tail_clock_offset(f->plan), 8 * sizeof(unsigned long long),
+    CU(cudaMemcpyAsync(f->clk_host, f->tail_scratch + stream_tail_clock_offset(f->plan), 12 * sizeof(unsigned long long),
                        cudaMemcpyDeviceToHost, ctx->stream));
   CU(cudaStreamSynchronize(ctx->stream));
   if (f->fused) {       // device clocks (globaltimer) of the fused launches: streaming phase | reduction + exchange + update
@@ -1131,6 +1131,10 @@ static int fit_poll(ppls_fit* f) {
       fprintf(stderr, "[ppls] fused tail per launch (us): streaming %.1f | tail %.1f = CTA 0: own sums %.1f + staging %.1f + scalar arithmetic %.1f (+ flag) ...\n",
               f->clk_host[0] * 1e-3 / f->clk_host[2], f->clk_host[1] * 1e-3 / f->clk_host[2], f->clk_host[5] * 1e-3 / f->clk_host[2],
               f->clk_host[6] * 1e-3 / f->clk_host[2], f->clk_host[7] * 1e-3 / f->clk_host[2]);
+    if (getenv("PPLS_TAIL_VERBOSE") && f->clk_host[2] && f->clk_host[8])
+      fprintf(stderr, "[ppls]   exchange inside 'own sums' (us): reduce + peer stores %.1f | fence + flags %.1f | wait for the peers %.1f | sum of the ranks %.1f\n",
+              f->clk_host[8] * 1e-3 / f->clk_host[2], f->clk_host[9] * 1e-3 / f->clk_host[2], f->clk_host[10] * 1e-3 / f->clk_host[2],
+              f->clk_host[11] * 1e-3 / f->clk_host[2]);
   }
   for (auto& pr : f->ev_tail) {       // .first is the K1 end event (owned by ev_k1, recycled below)
     float ms = 0.f;

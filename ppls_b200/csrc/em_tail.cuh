@@ -174,16 +174,21 @@ __device__ __noinline__ void stream_tail(const TailArgs& t, const double* partia
               [&](int e, double s, int y) { for (int r = y; r < t.x.world; r += 8) t.x.inbox[r][off + e] = s; });
     // CTA b of every rank owns the SAME elements: it needs CTA b of the peers only -- per-CTA flags, no grid barrier.
     __syncthreads();                                                // the whole CTA's peer stores are issued
+    unsigned long long tx = 0;                                      // (CTA 0, thread 0: stamps of the exchange, clk[8..11])
+    if (b == 0 && tid == 0) { tx = global_timer_ns(); clk[8] += tx - t1; }
     if (tid < t.x.world) {
       __threadfence_system();                                       // (cumulative over the bar.sync: orders them before the flag)
       st_relaxed_sys(t.x.cflags[tid] + ((next & 1ull) * XCHG_MAXW + t.x.rank) * XCHG_MAXCTA + b, next);
     }
+    if (b == 0 && tid == 0) { const unsigned long long ty = global_timer_ns(); clk[9] += ty - tx; tx = ty; }
     if (tid < 32) xchg_wait_cta(t.x, next, b);                      // the peers' CTA b has delivered
+    if (b == 0 && tid == 0) { const unsigned long long ty = global_timer_ns(); clk[10] += ty - tx; tx = ty; }
     __syncthreads();
     for (int e = tid; e < nelem; e += nt) {                         // ranks added in rank order: same bits everywhere
       const double s = xchg_sum(t.x, next, e0 + e);
       mine[e] = s; t.momvec[e0 + e] = s;
     }
+    if (b == 0 && tid == 0) clk[11] += global_timer_ns() - tx;
   }
   __syncthreads();
 
