@@ -212,19 +212,19 @@ __device__ inline void st_relaxed_sys(unsigned long long* p, unsigned long long 
   asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 // ONE WARP (all 32 lanes call): wait until every rank's vector of exchange `next` has landed in the local
-// inbox.  Lane r polls rank r's flag (relaxed loads, all ranks in parallel); one system-scope fence then
-// orders the inbox reads of the whole block (the caller's __syncthreads follows) after the flags.
+// inbox.  Lane r polls rank r's flag (acquire loads at system scope, all ranks in parallel), which orders the inbox
+// reads of the whole block (the caller's __syncthreads follows) after the flags.
 __device__ inline void xchg_wait(const XchgDev& x, unsigned long long next) {
   const int lane = threadIdx.x & 31;
   const unsigned long long* fl = x.flags[x.rank] + (next & 1ull) * XCHG_MAXW;
   const unsigned long long t0 = global_timer_ns();
   if (lane < x.world) {
-    while (ld_relaxed_sys(fl + lane) < next) {
-      if (global_timer_ns() - t0 > x.timeout_ns) { atomicExch(x.failed, 1); break; }   // (20 s by default) a peer is gone
+    unsigned int spins = 0;                                  // acquire polls: see xchg_wait_cta
+    while (ld_acquire_sys(fl + lane) < next) {
+      if ((++spins & 15u) == 0u && global_timer_ns() - t0 > x.timeout_ns) { atomicExch(x.failed, 1); break; }   // (20 s by default) a peer is gone
     }
   }
   __syncwarp();
-  __threadfence_system();
 }
 // The same wait on per-CTA flags (fused tail): flag (parity, source rank r, CTA `cta`) of THIS rank's block.
 __device__ inline void xchg_wait_cta(const XchgDev& x, unsigned long long next, int cta) {
