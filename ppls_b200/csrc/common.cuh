@@ -186,6 +186,9 @@ struct BGemmPlan {
   int RP, R, nstart;            // components of the group (multiple of 128), per start, starts in the group
   int ncb, nbx, nby, ntiles, rowtiles, unified;
   int nsplit; int64_t rows_per_split;
+  // the column block that straddles the X|Y boundary costs more per row (it stages mu_T and mu_U and multiplies the tile pair
+  // on the boundary twice): it gets MORE, shorter row splits so that all CTAs of the single wave end together
+  int mixed_db; int nsplit_mixed; int64_t rows_per_split_mixed;       // mixed_db < 0: no such block / even splits
   int nchunk; int64_t rows_per_chunk;
   int fused;                    // projection + mu + Gram blocks in one kernel (R divides 8): nchunk = rowtiles
   int sm_count;

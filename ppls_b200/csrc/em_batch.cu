@@ -619,7 +619,8 @@ __global__ void __launch_bounds__(WS_THREADS, 1) bprojmu2_kernel(const ProjMuArg
 // ---- partial[split][tile] = D[:, col block]' mu_side[:, comp block] over the split's rows ----------------------
 struct AccArgs {
   const double* D; const double* MU; double* partial;
-  int64_t n, rows_per_split;
+  int64_t n, rows_per_split, rows_per_split_mixed;
+  int ntiles, nsplit, nsplit_mixed, mixed_db;   // 1-D grid: the plain tiles' splits (tile fastest), then the mixed block's
   int ld, p2, q2, RP, nbx, nby, ncb;     // column blocks of X / Y (BT wide), comp blocks
   int unified;                           // 1: blocks run over the whole row [0, ld); a block may straddle the X|Y boundary
   int dbg;                               // timing experiments only (PPLS_BGEMM_DBG): 1 = no copies, 2 = no DMMA
@@ -627,7 +628,24 @@ struct AccArgs {
 template <int NST, bool WS>
 __global__ void __launch_bounds__(WS ? WS_THREADS : BTHREADS, 1) baccum_kernel(const AccArgs a) {
   extern __shared__ __align__(16) double sm[];    // [NST stages][3 operands: D, mu, mu_U (mixed block only)][BK][BP]
-  const int tile = blockIdx.x, cb = tile % a.ncb, db = tile / a.ncb;       // db: data column block
+  // CTA -> (tile, row split): plain tiles first (tile index fastest), then the tiles of the straddling column block
+  int tile, split;
+  int64_t rps;
+  {
+    const int n_mixed = a.mixed_db >= 0 ? a.ncb : 0, n_plain = a.ntiles - n_mixed, bid = (int)blockIdx.x;
+    if (bid < n_plain * a.nsplit) {
+      const int pt = bid % n_plain;
+      split = bid / n_plain;
+      tile = (a.mixed_db >= 0 && pt >= a.mixed_db * a.ncb) ? pt + a.ncb : pt;
+      rps = a.rows_per_split;
+    } else {
+      const int r = bid - n_plain * a.nsplit;
+      split = r / n_mixed;
+      tile = a.mixed_db * a.ncb + r % n_mixed;
+      rps = a.rows_per_split_mixed;
+    }
+  }
+  const int cb = tile % a.ncb, db = tile / a.ncb;                           // db: data column block
   // separate mode: X blocks, then Y blocks, each side padded to the tile.  unified mode (p2 % 8 == 0): blocks over
   // the whole row; in the block that straddles the X|Y boundary every 8-column DMMA tile still lies on one side,
   // so it takes its B fragment from mu_T or from mu_U (both staged) -- C5: 250 -> 256 columns instead of 384.
@@ -643,8 +661,8 @@ __global__ void __launch_bounds__(WS ? WS_THREADS : BTHREADS, 1) baccum_kernel(c
     cend = side ? a.ld : a.p2;
   }
   const double* Bbase = a.MU + (size_t)side * a.RP + (size_t)cb * BT;       // mixed: side = 0 here, mu_U = Bbase + RP
-  const int64_t r0 = (int64_t)blockIdx.y * a.rows_per_split;
-  const int64_t r1 = (r0 + a.rows_per_split < a.n) ? r0 + a.rows_per_split : a.n;
+  const int64_t r0 = (int64_t)split * rps;
+  const int64_t r1 = (r0 + rps < a.n) ? r0 + rps : a.n;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, gid = lane >> 2, tig = lane & 3;
   const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;         // this warp's data columns / components of the tile
   const int nst = (r1 > r0) ? (int)((r1 - r0 + BK - 1) / BK) : 0;
@@ -773,7 +791,7 @@ __global__ void __launch_bounds__(WS ? WS_THREADS : BTHREADS, 1) baccum_kernel(c
       multiply(s);
     }
   }
-  double* out = a.partial + ((size_t)blockIdx.y * gridDim.x + tile) * BT * BT;
+  double* out = a.partial + ((size_t)split * a.ntiles + tile) * BT * BT;
 #pragma unroll
   for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -785,7 +803,7 @@ __global__ void __launch_bounds__(WS ? WS_THREADS : BTHREADS, 1) baccum_kernel(c
 // blocks of every start summed over the row chunks and written on the block diagonal (nothing else is read).
 struct FinArgs {
   const double* partial; const double* gpart; double* momvec;
-  int nsplit, ntiles, ncb, nbx, ld, p2, RP, R, nstart, nchunk, unified;
+  int nsplit, ntiles, ncb, nbx, ld, p2, RP, R, nstart, nchunk, unified, mixed_db, nsplit_mixed;
 };
 __global__ void __launch_bounds__(256) bfinal_kernel(const FinArgs a) {
   __shared__ double sh[8][33];
@@ -800,7 +818,8 @@ __global__ void __launch_bounds__(256) bfinal_kernel(const FinArgs a) {
     const int side = j >= a.p2, jj = a.unified ? j : (side ? j - a.p2 : j);
     const int db = (a.unified ? 0 : (side ? a.nbx : 0)) + jj / BT, cb = c / BT, tile = db * a.ncb + cb;
     const size_t off = (size_t)tile * BT * BT + (size_t)(jj % BT) * BT + (c % BT);
-    for (int sp = threadIdx.y; sp < a.nsplit; sp += 8) s0 += a.partial[(size_t)sp * a.ntiles * BT * BT + off];
+    const int ns_t = (db == a.mixed_db) ? a.nsplit_mixed : a.nsplit;
+    for (int sp = threadIdx.y; sp < ns_t; sp += 8) s0 += a.partial[(size_t)sp * a.ntiles * BT * BT + off];
     dst = e;
   } else if (e < nall) {
     const size_t f = e - ng;
@@ -844,6 +863,27 @@ void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGe
   rps = (rps + BK - 1) / BK * BK;
   p->nsplit = (int)((s.n + rps - 1) / rps);
   p->rows_per_split = rps;
+  p->mixed_db = -1; p->nsplit_mixed = p->nsplit; p->rows_per_split_mixed = rps;
+  {
+    // uneven splits for the straddling block (PPLS_BACC_MIXW = its cost per row relative to a plain block; 1 = even splits)
+    const char* em = getenv("PPLS_BACC_MIXW");
+    const double c = (em && *em) ? atof(em) : 1.2;
+    const bool has_mixed = p->unified && (s.p2 % BT != 0) && (s.p2 < s.ld);
+    const int n_mixed = p->ncb, n_plain = p->ntiles - p->ncb;
+    const int64_t total = (int64_t)p->nsplit * p->ntiles;
+    if (has_mixed && c > 1.0 && total <= sm_count && n_plain >= 1) {
+      int64_t nsp = (int64_t)((double)total / ((double)n_plain + c * (double)n_mixed));
+      if (nsp < 1) nsp = 1;
+      int64_t nsm = (total - nsp * n_plain) / n_mixed;
+      if (nsm > max_ns) nsm = max_ns;
+      if (nsm >= nsp && nsm >= 1) {
+        int64_t rp = ((s.n + nsp - 1) / nsp + BK - 1) / BK * BK, rm = ((s.n + nsm - 1) / nsm + BK - 1) / BK * BK;
+        p->mixed_db = s.p2 / BT;
+        p->nsplit = (int)((s.n + rp - 1) / rp); p->rows_per_split = rp;
+        p->nsplit_mixed = (int)((s.n + rm - 1) / rm); p->rows_per_split_mixed = rm;
+      }
+    }
+  }
   // mu kernel: (32/R starts per warp) x row chunks, about 8 blocks per SM
   const int sb = (nstart + (32 / R) - 1) / (32 / R);
   int64_t nc = (4 * (int64_t)sm_count + sb - 1) / sb;
@@ -867,7 +907,7 @@ void plan_bgemm(const DataShape& s, int RP, int R, int nstart, int sm_count, BGe
 }
 size_t bgemm_workspace_doubles(const DataShape& s, const BGemmPlan& p) {
   return (size_t)s.n * 2 * p.RP                                   // P / mu
-         + (size_t)p.nsplit * p.ntiles * BT * BT                   // accumulate partials
+         + (size_t)(p.nsplit > p.nsplit_mixed ? p.nsplit : p.nsplit_mixed) * p.ntiles * BT * BT     // accumulate partials
          + (size_t)p.nchunk * p.nstart * 3 * p.R * p.R;            // Gram partials
 }
 
@@ -930,7 +970,7 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
                               double* ws, double* momvec_pack, cudaStream_t stream) {
   double* P = ws;
   double* partial = P + (size_t)s.n * 2 * p.RP;
-  double* gpart = partial + (size_t)p.nsplit * p.ntiles * BT * BT;
+  double* gpart = partial + (size_t)(p.nsplit > p.nsplit_mixed ? p.nsplit : p.nsplit_mixed) * p.ntiles * BT * BT;
   const char* es = getenv("PPLS_BACC_STAGES");
   const int nstg = (es && *es) ? atoi(es) : BACC_STAGES_DEFAULT;
   if (nstg < 2 || nstg > 4) return cudaErrorInvalidValue;
@@ -971,15 +1011,20 @@ cudaError_t launch_bgemm_pass(const BGemmPlan& p, const DataShape& s, const doub
   }
   AccArgs aa{};
   aa.D = D; aa.MU = P; aa.partial = partial; aa.n = s.n; aa.rows_per_split = p.rows_per_split;
+  aa.rows_per_split_mixed = p.rows_per_split_mixed; aa.ntiles = p.ntiles; aa.nsplit = p.nsplit; aa.nsplit_mixed = p.nsplit_mixed;
+  aa.mixed_db = p.mixed_db;
   aa.ld = s.ld; aa.p2 = s.p2; aa.q2 = s.q2; aa.RP = p.RP; aa.nbx = p.nbx; aa.nby = p.nby; aa.ncb = p.ncb; aa.unified = p.unified;
   { const char* ed = getenv("PPLS_BGEMM_DBG"); aa.dbg = (ed && *ed) ? atoi(ed) : 0; }
   {
     void* kargs[] = {(void*)&aa};
-    e = cudaLaunchKernel(bacc, dim3(p.ntiles, p.nsplit), dim3(wsp ? WS_THREADS : BTHREADS), kargs, smemB, stream);
+    const int n_mixed = p.mixed_db >= 0 ? p.ncb : 0;
+    const unsigned grid = (unsigned)((p.ntiles - n_mixed) * p.nsplit + n_mixed * p.nsplit_mixed);
+    e = cudaLaunchKernel(bacc, dim3(grid), dim3(wsp ? WS_THREADS : BTHREADS), kargs, smemB, stream);
     if (e != cudaSuccess) return e;
   }
   FinArgs f{};
   f.partial = partial; f.gpart = gpart; f.momvec = momvec_pack; f.nsplit = p.nsplit; f.ntiles = p.ntiles; f.ncb = p.ncb;
+  f.mixed_db = p.mixed_db; f.nsplit_mixed = p.nsplit_mixed;
   f.nbx = p.nbx; f.ld = s.ld; f.p2 = s.p2; f.RP = p.RP; f.R = p.R; f.nstart = p.nstart; f.nchunk = p.nchunk; f.unified = p.unified;
   const size_t ne = (size_t)s.ld * p.RP + (size_t)p.nstart * 3 * p.R * p.R;
   bfinal_kernel<<<(unsigned)((ne + 31) / 32), dim3(32, 8), 0, stream>>>(f);

@@ -1,17 +1,10 @@
 #!/bin/bash
+# session Q (1 GPU): uneven row splits of the batched accumulate kernel: parity, C5 by weight
 set -u
 OUT=gpurun_out/r02q
 mkdir -p $OUT
-for DBG in 0 7 8 5; do
-  PPLS_BGEMM_DBG=$DBG ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"bprojmu|baccum" -c 8 --csv --log-file $OUT/st_$DBG.csv python tools/dbg_c5.py > /dev/null 2>&1
-  python - <<PY
-import csv, collections
-try:
-    rows=[r for r in csv.reader(open("$OUT/st_$DBG.csv")) if len(r)>10 and r[0].isdigit()]
-    agg=collections.defaultdict(list)
-    for r in rows: agg[r[4].split('(')[0][:30]].append(float(r[-1].replace(',','')))
-    print("dbg $DBG:", {k: [round(x/1e3,1) for x in v[-3:]] for k,v in agg.items()})
-except Exception as e:
-    print("dbg $DBG: no data", e)
-PY
+timeout 900 python -m pytest tests/test_gpu_parity.py tests/test_gpu_fullsize.py -m gpu -q -x -k "batched" > $OUT/pytest_batched.log 2>&1; echo "pytest batched rc=$?"; tail -2 $OUT/pytest_batched.log | cut -c1-300
+for W in 1.0 1.1 1.2 1.3; do
+PPLS_BACC_MIXW=$W timeout 300 python bench.py --workload c5 --steps 30 --warmup 5 --no-cpu --no-e2e --no-others 2>/dev/null | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); print('c5 mixw $W:', round(d['value'],1), 'batch-it/s ms/step', round(d['ms_per_step'],4), 'frac', round(d['roofline']['frac'],3))"
 done
